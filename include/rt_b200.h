@@ -1,0 +1,252 @@
+/*
+ * rt_b200.h — C ABI of the B200-native backend for the `raytrace` path-tracing loop.
+ *
+ * This is the drop-in boundary for ONE hot path of UnaryPlus/raytrace:
+ *     raytrace :: ToRandom m => CameraSettings -> Geometry m Material -> StdGen -> A.Matrix D Color
+ *     (reference: src/Graphics/Ray.hs:121-238)
+ * The reference has no FFI at all (raytrace.cabal:30-49); its "plugin interface" is the
+ * combinator vocabulary exported by Graphics.Ray.* (Ray.hs:7-20, Geometry.hs:5-16,
+ * Material.hs:3-6, Texture.hs:2-5).  A front end (Haskell `foreign import ccall`, the Python
+ * mirror in raytrace_b200/, or plain C++) reifies those combinators as a DESCRIPTION TREE and
+ * hands it over with the calls below; the library validates it, flattens it into device
+ * buffers, builds the BVH with the reference's split policy (Geometry.hs:369-377) and renders
+ * with hand-written sm_100a CUDA kernels.
+ *
+ * Conventions
+ *   - plain C, `extern "C"`, POD structs, caller-owned pointers (the library copies what it
+ *     needs during the call), no C++ exceptions or aborts across the boundary;
+ *   - every entry point returns an RtStatus; rt_last_error() gives a thread-local message;
+ *   - scenes with user-defined Haskell closures (Material / Texture / planeShape predicate /
+ *     background that cannot be classified) are REJECTED with RT_ERR_USER_DEFINED — there is
+ *     no CPU fallback anywhere in this library;
+ *   - all inputs are double (the reference's numeric type, Core.hs:29-31); the device
+ *     computes in fp32 (fp64 only for the large-radius sphere discriminant).
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_B200_VERSION 0x00010000u
+
+typedef enum RtStatus {
+  RT_OK = 0,
+  RT_ERR_INVALID_ARG = 1,     /* null pointer, bad id, bad enum                            */
+  RT_ERR_EMPTY_BVH = 2,       /* `bvhTree []` — reference: error "bvhTree: empty list" (Geometry.hs:371) */
+  RT_ERR_USER_DEFINED = 3,    /* user-defined material/texture/shape/background: explicit rejection */
+  RT_ERR_NON_EUCLIDEAN = 4,   /* `transform` with a non-Euclidean matrix (Geometry.hs:379-381) */
+  RT_ERR_TYPE = 5,            /* description tree ill-typed (e.g. root without material)    */
+  RT_ERR_CUDA = 6,            /* CUDA runtime failure                                       */
+  RT_ERR_NO_DEVICE = 7,       /* no sm_100 device visible                                   */
+  RT_ERR_NOT_COMMITTED = 8,   /* render before commit                                       */
+  RT_ERR_PARSE = 9,           /* .obj parse error (message mirrors Geometry.hs:230-285)     */
+  RT_ERR_UNSUPPORTED = 10     /* valid reference construct this build cannot flatten yet    */
+} RtStatus;
+
+/* ---- textures: Graphics.Ray.Texture (Texture.hs:15-79) ------------------------------- */
+typedef enum RtTextureKind {
+  RT_TEX_CONSTANT = 1,  /* constantTexture c0                       Texture.hs:18-19 */
+  RT_TEX_CHECKER = 2,   /* checkerTexture i0 i1 c0 c1               Texture.hs:45-53 */
+  RT_TEX_IMAGE = 3,     /* imageTexture (linear RGB, rows top→down) Texture.hs:31-41 */
+  RT_TEX_NOISE = 4,     /* noiseTexture i0 freq shift c0 c1         Texture.hs:56-67 */
+  RT_TEX_MARBLE = 5,    /* marbleTexture dir freq shift             Texture.hs:70-79 */
+  RT_TEX_USER = 6       /* solidTexture / uvTexture / Texture with a user closure → rejected */
+} RtTextureKind;
+
+typedef struct RtTextureDesc {
+  int32_t kind;
+  int32_t i0, i1;       /* checker: n_u, n_v; noise: number of layers k */
+  int32_t width, height;/* image */
+  double freq;          /* noise / marble */
+  double c0[3], c1[3];  /* colours */
+  double shift[3];      /* noise / marble */
+  double dir[3];        /* marble stripe direction */
+  const float* image;   /* width*height*3 linear-light floats, row 0 = top row (readImage, Ray.hs:241-245) */
+} RtTextureDesc;
+
+/* ---- materials: Graphics.Ray.Material (Material.hs:41-129) ---------------------------- */
+typedef enum RtMaterialKind {
+  RT_MAT_LIGHT = 1,           /* lightSource tex           Material.hs:41-42  */
+  RT_MAT_PITCH_BLACK = 2,     /* pitchBlack                Material.hs:46-47  */
+  RT_MAT_LAMBERTIAN = 3,      /* lambertian tex            Material.hs:51-53  */
+  RT_MAT_LOMMEL_SEELIGER = 4, /* lommelSeeliger tex        Material.hs:56-61  */
+  RT_MAT_MIRROR = 5,          /* mirror tex                Material.hs:64-67  */
+  RT_MAT_METAL = 6,           /* metal param tex           Material.hs:72-78  */
+  RT_MAT_DIELECTRIC = 7,      /* dielectric param          Material.hs:89-106 */
+  RT_MAT_TRANSPARENT = 8,     /* transparent tex           Material.hs:109-112 */
+  RT_MAT_ISOTROPIC = 9,       /* isotropic tex             Material.hs:116-118 */
+  RT_MAT_ANISOTROPIC = 10,    /* anisotropic param tex     Material.hs:124-129 */
+  RT_MAT_USER = 11            /* `Material` built from a user closure → rejected */
+} RtMaterialKind;
+
+typedef struct RtMaterialDesc {
+  int32_t kind;
+  uint32_t texture;     /* id from rt_scene_add_texture (ignored by pitchBlack / dielectric) */
+  double param;         /* metal: fuzz; dielectric: ior; anisotropic: g */
+} RtMaterialDesc;
+
+/* ---- geometry description tree: Graphics.Ray.Geometry (Geometry.hs:42-456) ------------ */
+typedef enum RtNodeKind {
+  RT_NODE_SPHERE = 1,         /* sphere v[0] s[0]                          Geometry.hs:58-94   */
+  RT_NODE_PARALLELOGRAM = 2,  /* parallelogram q=v[0] u=v[1] v=v[2]        Geometry.hs:147-151 */
+  RT_NODE_TRIANGLE = 3,       /* triangle (v[0],uv[0]) (v[1],uv[1]) (v[2],uv[2])  Geometry.hs:169-176 */
+  RT_NODE_CUBOID = 4,         /* cuboid box: lo=v[0], hi=v[1]              Geometry.hs:154-166 */
+  RT_NODE_MESH = 5,           /* triangleMesh (Mesh verts uvs faces)       Geometry.hs:179-184,288-294 */
+  RT_NODE_GROUP = 6,          /* group children                            Geometry.hs:336-347 */
+  RT_NODE_BVH_NODE = 7,       /* bvhNode children[0] children[1]           Geometry.hs:352-363 */
+  RT_NODE_BVH_TREE = 8,       /* bvhTree children                          Geometry.hs:369-377 */
+  RT_NODE_TRANSFORM = 9,      /* transform m children[0]                   Geometry.hs:382-391 */
+  RT_NODE_MOVING = 10,        /* moving v[0] v[1] children[0]              Geometry.hs:449-456 */
+  RT_NODE_MEDIUM = 11,        /* constantMedium s[0] children[0]           Geometry.hs:298-330 */
+  RT_NODE_WITH_MATERIAL = 12, /* material <$ children[0]                   Geometry.hs:44-47   */
+  RT_NODE_PURE = 13,          /* pureGeometry children[0]                  Geometry.hs:50-51   */
+  RT_NODE_USER = 14           /* planeShape with user predicate / raw Geometry closure → rejected */
+} RtNodeKind;
+
+typedef struct RtNodeDesc {
+  int32_t kind;
+  uint32_t material;          /* WITH_MATERIAL: id from rt_scene_add_material */
+  uint32_t n_children;
+  uint32_t n_verts, n_uvs, n_faces;   /* MESH */
+  const uint32_t* children;   /* node ids, in the reference's list order */
+  const double* verts;        /* MESH: n_verts*3 */
+  const double* uvs;          /* MESH: n_uvs*2 (may be NULL when n_uvs == 0) */
+  const int32_t* faces;       /* MESH: n_faces*6 = (v0,t0,v1,t1,v2,t2), 0-based, t = -1 for Nothing */
+  double v[3][3];             /* vector slots, see RtNodeKind */
+  double s[2];                /* scalar slots: sphere radius / medium density */
+  double uv[3][2];            /* TRIANGLE texture coordinates */
+  double m[16];               /* TRANSFORM: M44 row-major, bottom row 0 0 0 1 */
+} RtNodeDesc;
+
+/* ---- camera: CameraSettings (Ray.hs:40-98), field for field --------------------------- */
+typedef enum RtBackgroundKind {
+  RT_BG_CONSTANT = 1,   /* const c0                                  (default, Ray.hs:94)   */
+  RT_BG_YGRADIENT = 2   /* (1-a)*c0 + a*c1, a = 0.5*(dir.y+1)        (sky / grayFade, test/Main.hs:19-28) */
+} RtBackgroundKind;
+
+typedef struct RtRedirectTarget {   /* one element of cs_redirectTargets (Ray.hs:64) */
+  double p;
+  double q[3], s0[3], s1[3];
+} RtRedirectTarget;
+
+typedef struct RtCamera {
+  double center[3];             /* cs_center  */
+  double look_at[3];            /* cs_lookAt  */
+  double up[3];                 /* cs_up      */
+  double vfov;                  /* cs_vfov (radians) */
+  double aspect_ratio;          /* cs_aspectRatio */
+  double defocus_angle;         /* cs_defocusAngle */
+  double focus_dist;            /* cs_focusDist */
+  double bg_c0[3], bg_c1[3];    /* cs_background, classified by the front end */
+  int32_t bg_kind;
+  int32_t image_width;          /* cs_imageWidth */
+  int32_t samples_per_pixel;    /* cs_samplesPerPixel */
+  int32_t max_recursion_depth;  /* cs_maxRecursionDepth */
+  int32_t n_redirect_targets;   /* length cs_redirectTargets */
+  int32_t _pad;
+  const RtRedirectTarget* redirect_targets;
+} RtCamera;
+
+typedef struct RtStats {
+  uint64_t samples;        /* camera paths started                                               */
+  uint64_t rays;           /* path segments that reached a closest-hit query (Ray.hs:178)         */
+  uint64_t launches;       /* kernels launched by this call                                       */
+  uint32_t iterations;     /* wavefront iterations                                                */
+  uint32_t pool;           /* live-ray pool size used                                             */
+  double ms_total;         /* device time of the render (CUDA events), copies excluded            */
+  double ms_traverse;      /* device time spent in the traversal/closest-hit kernel               */
+  double ms_shade;         /* device time spent in the shading/scatter/compaction kernel          */
+  double ms_raygen;        /* device time spent in camera-ray generation                          */
+  double ms_copy;          /* host<->device copies done by this call                              */
+} RtStats;
+
+typedef struct RtSceneInfo {
+  uint32_t n_prims, n_spheres, n_planars;
+  uint32_t n_bvh_nodes;       /* 32-byte nodes uploaded */
+  uint32_t n_media, n_materials, n_textures, n_xforms;
+  uint32_t surface_root;
+  uint32_t max_depth;         /* deepest root→leaf path in the device tree */
+  uint64_t device_bytes;      /* scene bytes resident in HBM */
+} RtSceneInfo;
+
+typedef struct RtScene RtScene;
+
+/* library */
+uint32_t rt_version(void);
+const char* rt_last_error(void);
+int32_t rt_device_count(int32_t* n);                 /* sm_100 devices visible */
+
+/* scene building (description tree) */
+int32_t rt_scene_create(RtScene** out);
+int32_t rt_scene_destroy(RtScene* scene);
+int32_t rt_scene_add_texture(RtScene* scene, const RtTextureDesc* desc, uint32_t* id);
+int32_t rt_scene_add_material(RtScene* scene, const RtMaterialDesc* desc, uint32_t* id);
+int32_t rt_scene_add_node(RtScene* scene, const RtNodeDesc* desc, uint32_t* id);
+/* Perlin tables of Noise.hs:52-92; the three permutation tables default to the reference's
+ * literals, the gradient table to a SplitMix restatement of `mkStdGen 666` (parity unpinned). */
+int32_t rt_scene_set_noise_tables(RtScene* scene, const int32_t* perm_x, const int32_t* perm_y,
+                                  const int32_t* perm_z, const double* gradients /*256*3*/);
+
+/* validate + flatten + build BVH (host only; no GPU needed) */
+int32_t rt_scene_commit(RtScene* scene, uint32_t root);
+int32_t rt_scene_info(const RtScene* scene, RtSceneInfo* info);
+/* read back the flattened host-side buffers (tests: BVH shape equality with the oracle) */
+int32_t rt_scene_get_bvh(const RtScene* scene, float* nodes /*n_bvh_nodes*8, may be NULL*/,
+                         uint32_t* prim_canonical_id /*n_prims, may be NULL*/);
+
+/* upload to a device (one scene may be resident on several devices) */
+int32_t rt_scene_upload(RtScene* scene, int32_t device);
+
+/* camera helper: imageHeight = round-half-even (W / aspect)  (Ray.hs:123) */
+int32_t rt_image_height(const RtCamera* cam, int32_t* height);
+
+/*
+ * Render global sample indices [first_sample, first_sample + n_samples) of every pixel.
+ * rgb_out: HOST buffer, H*W*3 floats, row-major, row 0 = top (index (j :. i), Ray.hs:238),
+ *          linear RGB, unclamped, already divided by cam->samples_per_pixel.
+ * rgb_sumsq_out: optional HOST buffer, same shape: Σ x² per channel (not divided).
+ */
+int32_t rt_render(RtScene* scene, int32_t device, const RtCamera* cam, uint64_t seed,
+                  uint64_t first_sample, uint64_t n_samples, float* rgb_out,
+                  float* rgb_sumsq_out, RtStats* stats);
+
+/*
+ * Same, accumulating UN-normalised sums into DEVICE buffers owned by the caller (e.g. a torch
+ * tensor), on the caller's stream; used by the one-process-per-GPU sample-sharded path where
+ * an NCCL reduce follows.  d_sum / d_sumsq must be zero-initialised by the caller.
+ */
+int32_t rt_render_device(RtScene* scene, int32_t device, const RtCamera* cam, uint64_t seed,
+                         uint64_t first_sample, uint64_t n_samples, float* d_sum,
+                         float* d_sumsq /*nullable*/, void* cuda_stream, RtStats* stats);
+
+/* Deterministic pixel-centre primary rays (no lens, given shutter time): canonical primitive
+ * id (0xFFFFFFFF = miss, 0xFFFFFFFE = medium) and hit distance per pixel.  HOST buffers H*W. */
+int32_t rt_probe_primary(RtScene* scene, int32_t device, const RtCamera* cam, double time,
+                         uint32_t* prim_id_out, float* t_out);
+
+/* tuning knobs (0 = default) */
+int32_t rt_set_pool_size(RtScene* scene, uint32_t n_paths);
+
+/* image output step after the path (writeImage / writeImageSqrt, Ray.hs:248-260):
+ * linear RGB float → 8-bit with the sRGB OETF (mode 0) or sqrt gamma (mode 1), clamped. */
+int32_t rt_tonemap_u8(int32_t device, const float* rgb_host, int32_t n_pixels, int32_t mode,
+                      uint8_t* rgb8_host);
+
+/* .obj loader with the rules of parseObj (Geometry.hs:207-285). Buffers are owned by the
+ * returned handle. */
+typedef struct RtMesh RtMesh;
+int32_t rt_obj_parse(const char* text, size_t len, RtMesh** out);
+int32_t rt_mesh_sizes(const RtMesh* mesh, uint32_t* n_verts, uint32_t* n_uvs, uint32_t* n_faces);
+int32_t rt_mesh_data(const RtMesh* mesh, const double** verts, const double** uvs,
+                     const int32_t** faces);
+int32_t rt_mesh_destroy(RtMesh* mesh);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */

@@ -1,0 +1,109 @@
+// rt_device.h — flattened scene records shared by the host flattener (rt_flatten.cpp) and the
+// CUDA kernels (rt_kernels.cu).  Everything here is what lives in HBM after rt_scene_upload.
+//
+// Layout summary (DESIGN.md §"Data layout in HBM"):
+//   nodes   : 32-byte BVH nodes, 2 x float4 {lo.xyz, a} {hi.xyz, b}; siblings adjacent (one 64 B
+//             fetch tests both children).  inner: a = index of first child, b = 0;
+//             leaf : a = first primitive, b = kLeafBit | primitive count.
+//   prims   : 64-byte records, 4 x float4; index order = the reference's evaluation order
+//             (group: list order, Geometry.hs:340-345; bvhNode: left first, :356-361), so
+//             "lower index wins an exact tie" reproduces the reference's tie rules.
+//             sphere : {c.xyz, r}        {-}                {-}                  {meta}
+//             planar : {q.xyz, n.x} {n.y, n.z, wa.xy} {wa.z, wb.xyz} {meta}
+//                      with wa = v x nS, wb = nS x u (planar coords a = wa.(p-q), b = wb.(p-q);
+//                      Geometry.hs:130-131 rewritten by the scalar triple product)
+//             meta   : {type|flags, geom id, xform id, material id} as uint32 bit patterns
+//   tri_uv  : per primitive 2 x float4 {uv0, uv1} {uv2, -, -} (triangles only)
+#pragma once
+#include <stdint.h>
+
+namespace rtb {
+
+constexpr uint32_t kNone = 0xFFFFFFFFu;
+constexpr uint32_t kLeafBit = 0x80000000u;
+constexpr uint32_t kMediumBase = 0xFFFF0000u;  // hit.prim >= kMediumBase: medium (prim - base)
+constexpr int kStackDepth = 32;                // shared-memory short stack entries per thread
+constexpr int kMaxTargets = 8;                 // cs_redirectTargets entries supported on device
+constexpr int kMaxMedia = 16;
+
+// primitive type / flag bits (meta.x)
+constexpr uint32_t PRIM_SPHERE = 0u;
+constexpr uint32_t PRIM_PGRAM = 1u;
+constexpr uint32_t PRIM_TRI = 2u;
+constexpr uint32_t PRIM_TYPE_MASK = 3u;
+constexpr uint32_t PRIM_FLAG_BIG = 4u;      // large-radius sphere: fp64 discriminant
+constexpr uint32_t PRIM_FLAG_MOVING = 8u;   // stays in local space; ray is mapped by xform(time)
+constexpr uint32_t PRIM_FLAG_UVXFORM = 16u; // sphere under a rotation: uv needs the local normal
+
+struct DNode {  // 32 bytes
+  float lo[3];
+  uint32_t a;
+  float hi[3];
+  uint32_t b;
+};
+
+struct DXform {  // world->local: o' = Ainv*o + binv0 + time*binv1 ; local->world normal: A*n
+  float Ainv[9];
+  float binv0[3], binv1[3];
+  float A[9];
+};
+
+struct DMaterial {  // Material.hs
+  int32_t kind;     // RtMaterialKind
+  uint32_t texture;
+  float param;
+  int32_t _pad;
+};
+
+struct DTexture {   // Texture.hs
+  int32_t kind;     // RtTextureKind
+  int32_t i0, i1;   // checker n_u n_v / noise layers
+  int32_t w, h;     // image size
+  uint32_t image_offset;  // first texel (float4) in the image pool
+  float freq;
+  float c0[3], c1[3], shift[3], dir[3];
+};
+
+struct DMedium {    // constantMedium, Geometry.hs:298-330
+  float neg_inv_density;
+  uint32_t root;        // node pair index of the boundary tree
+  uint32_t material;
+  uint32_t geom_lo, geom_hi;  // geom-id range of the boundary primitives (dense ids)
+};
+
+struct DTarget {    // RedirectTarget, Ray.hs:112-118 (+ its parallelogram record for the pdf probe)
+  float p, cumulative;
+  float origin[3], U[3], V[3], crs[3];
+  float n[3], wa[3], wb[3];
+};
+
+struct DCamera {    // Ray.hs:123-155, evaluated in double on the host, stored fp32
+  int32_t W, H, spp, max_depth;
+  float center[3], top_left[3], pixel_u[3], pixel_v[3], defocus_u[3], defocus_v[3];
+  int32_t has_defocus;
+  int32_t bg_kind;
+  float bg0[3], bg1[3];
+  int32_t n_targets;
+  float rem_prob;
+  DTarget targets[kMaxTargets];
+};
+
+struct DScene {     // device pointers of one uploaded scene
+  const float4* nodes;
+  const float4* prims;
+  const float4* tri_uv;
+  const DXform* xforms;
+  const DMaterial* materials;
+  const DTexture* textures;
+  const float4* texels;
+  const uint32_t* canonical;   // prim index -> canonical primitive id (probe output)
+  const float* noise_grad;     // 256*3
+  const uint8_t* noise_perm;   // 3*256
+  DMedium media[kMaxMedia];
+  uint32_t n_media;
+  uint32_t surface_root;       // node pair index or kNone
+  uint32_t has_noise;
+  uint32_t n_prims;
+};
+
+}  // namespace rtb

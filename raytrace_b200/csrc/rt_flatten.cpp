@@ -1,0 +1,789 @@
+// rt_flatten.cpp — description tree → flattened device scene (host side, double precision).
+//
+// Replaces, for the GPU path, what the reference does implicitly by nesting closures
+// (src/Graphics/Ray/Geometry.hs): every combinator of the tree is resolved HERE, once:
+//   * `transform` / `moving` chains (Geometry.hs:382-391, 449-456) collapse into one affine map
+//     o' = Ainv*o + binv0 + time*binv1 per leaf; static chains are baked into world-space
+//     primitives, moving ones keep the primitive local and flag it;
+//   * `<$` (Geometry.hs:44-47): the OUTERMOST material wins (fmap (const m) applied last);
+//   * `constantMedium` (Geometry.hs:298-330) nodes are hoisted out of the surface tree: closest
+//     hit is order independent, so "surfaces first, then each medium on (tmin, t_best)" gives
+//     the same distribution as the reference's left-to-right `group` fold;
+//   * `bvhTree` (Geometry.hs:369-377) is built with the reference's policy — axis = longestDim
+//     of the joined box with argMax's tie rule (Core.hs:43-46,143-144), STABLE sort on the bbox
+//     midpoint (Core.hs:87-88), left gets n div 2 — on the reference's own bounding boxes;
+//   * `group` (Geometry.hs:336-347), a linear scan in the reference, becomes a BVH built by the
+//     same policy (or one multi-primitive leaf when small): identical results, fewer tests;
+//   * primitives are numbered in the reference's evaluation order so that "lower index wins an
+//     exact tie" equals the reference's tie rules (earlier child / left child wins).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <functional>
+#include <limits>
+
+#include "rt_host.h"
+
+namespace rtb {
+namespace {
+
+constexpr double kInf = std::numeric_limits<double>::infinity();
+
+struct D3 {
+  double x = 0, y = 0, z = 0;
+};
+inline D3 operator+(D3 a, D3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline D3 operator-(D3 a, D3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline D3 operator*(double s, D3 a) { return {s * a.x, s * a.y, s * a.z}; }
+inline double dot(D3 a, D3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline D3 cross(D3 a, D3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline D3 mk(const double* p) { return {p[0], p[1], p[2]}; }
+inline double get(D3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+
+struct BoxD {
+  double lo[3] = {kInf, kInf, kInf}, hi[3] = {-kInf, -kInf, -kInf};
+  void add(D3 p) {
+    for (int k = 0; k < 3; k++) { lo[k] = std::min(lo[k], get(p, k)); hi[k] = std::max(hi[k], get(p, k)); }
+  }
+  void join(const BoxD& b) {
+    for (int k = 0; k < 3; k++) { lo[k] = std::min(lo[k], b.lo[k]); hi[k] = std::max(hi[k], b.hi[k]); }
+  }
+  void pad(double e) {
+    for (int k = 0; k < 3; k++) { lo[k] -= e; hi[k] += e; }
+  }
+  bool empty() const { return lo[0] > hi[0]; }
+};
+inline int longest_dim(const BoxD& b) {  // Core.hs:143-144 + argMax Core.hs:43-46
+  double x = b.hi[0] - b.lo[0], y = b.hi[1] - b.lo[1], z = b.hi[2] - b.lo[2];
+  if (x > y) return x > z ? 0 : 2;
+  return y > z ? 1 : 2;
+}
+
+// affine map p -> M*p + c0 + time*c1
+struct Affine {
+  double M[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+  double c0[3] = {0, 0, 0}, c1[3] = {0, 0, 0};
+  D3 lin(D3 v) const { return {M[0] * v.x + M[1] * v.y + M[2] * v.z, M[3] * v.x + M[4] * v.y + M[5] * v.z, M[6] * v.x + M[7] * v.y + M[8] * v.z}; }
+  D3 pt(D3 p, double time) const {
+    D3 r = lin(p);
+    return {r.x + c0[0] + time * c1[0], r.y + c0[1] + time * c1[1], r.z + c0[2] + time * c1[2]};
+  }
+};
+// (outer ∘ inner)(p) = outer(inner(p)); motion terms stay linear in time because the linear
+// parts do not depend on time.
+Affine compose(const Affine& outer, const Affine& inner) {
+  Affine r;
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) {
+      double s = 0;
+      for (int k = 0; k < 3; k++) s += outer.M[i * 3 + k] * inner.M[k * 3 + j];
+      r.M[i * 3 + j] = s;
+    }
+  D3 a0 = outer.lin(mk(inner.c0)), a1 = outer.lin(mk(inner.c1));
+  r.c0[0] = a0.x + outer.c0[0]; r.c0[1] = a0.y + outer.c0[1]; r.c0[2] = a0.z + outer.c0[2];
+  r.c1[0] = a1.x + outer.c1[0]; r.c1[1] = a1.y + outer.c1[1]; r.c1[2] = a1.z + outer.c1[2];
+  return r;
+}
+
+struct XfState {          // accumulated transform of the current subtree
+  Affine fwd;             // local -> world
+  Affine inv;             // world -> local
+  bool identity = true, moving = false;
+  std::vector<uint32_t> chain;  // description node ids of the transform/moving nodes above
+};
+
+struct HPrim {            // one primitive instance (double precision, final space)
+  uint32_t type = PRIM_SPHERE, flags = 0;
+  D3 c;                   // sphere centre / planar q
+  double r = 0;
+  D3 n, wa, wb;           // planar
+  double uv[3][2] = {{0, 0}, {1, 0}, {0, 1}};
+  uint32_t geom = kNone, xform = 0, material = kNone, canonical = kNone;
+  BoxD box;               // world-space box (swept over the shutter for moving instances)
+  uint32_t index = kNone; // final device index (reference evaluation order)
+};
+
+// reference-shaped tree: exactly the structure the reference would evaluate
+struct RNode {
+  enum Kind { LEAF, GROUP, BVH } kind = LEAF;
+  BoxD ref_box;                     // the reference's bounding box of this sub-geometry
+  uint32_t prim = kNone;            // LEAF: index into Builder::prims
+  std::vector<int> children;        // GROUP: list order; BVH: {left, right}
+};
+
+// device-shaped tree
+struct HNode {
+  BoxD box;
+  int left = -1, right = -1;        // inner
+  uint32_t first = 0, count = 0;    // leaf: final primitive indices [first, first+count)
+};
+
+struct FlattenError {
+  int32_t status;
+  std::string msg;
+};
+
+struct Builder {
+  Scene& sc;
+  std::vector<HPrim> prims;
+  std::vector<RNode> rnodes;
+  std::vector<HNode> hnodes;
+  std::map<std::vector<uint32_t>, uint32_t> xform_ids;
+  std::vector<XfState> xforms;      // index = xform id (0 = identity)
+  std::map<std::pair<uint32_t, uint32_t>, uint32_t> canon_first;   // (desc node, sub) -> canonical
+  std::map<std::tuple<uint32_t, uint32_t, uint32_t>, uint32_t> geom_ids;
+  uint32_t next_canonical = 0;
+  struct MediumRec { double density; int rtree; uint32_t material; };
+  std::vector<MediumRec> media;
+  std::vector<char> mat_used, tex_used;
+  int depth_guard = 0;
+
+  explicit Builder(Scene& s) : sc(s) {
+    XfState id;
+    xforms.push_back(id);
+    xform_ids[{}] = 0;
+  }
+
+  [[noreturn]] void fail(int32_t st, const std::string& m) { throw FlattenError{st, m}; }
+
+  uint32_t canonical_for(uint32_t node, uint32_t sub) {
+    auto key = std::make_pair(node, sub);
+    auto it = canon_first.find(key);
+    if (it != canon_first.end()) return it->second;
+    uint32_t id = next_canonical++;
+    canon_first[key] = id;
+    return id;
+  }
+  uint32_t geom_for(uint32_t node, uint32_t sub, uint32_t xf) {
+    auto key = std::make_tuple(node, sub, xf);
+    auto it = geom_ids.find(key);
+    if (it != geom_ids.end()) return it->second;
+    uint32_t id = (uint32_t)geom_ids.size();
+    geom_ids[key] = id;
+    return id;
+  }
+  uint32_t xform_id(const XfState& x) {
+    if (x.identity) return 0;
+    auto it = xform_ids.find(x.chain);
+    if (it != xform_ids.end()) return it->second;
+    uint32_t id = (uint32_t)xforms.size();
+    xforms.push_back(x);
+    xform_ids[x.chain] = id;
+    return id;
+  }
+
+  int new_rnode(RNode::Kind k) {
+    rnodes.emplace_back();
+    rnodes.back().kind = k;
+    return (int)rnodes.size() - 1;
+  }
+
+  // ---- primitives ---------------------------------------------------------------------------
+  void use_material(uint32_t m) {
+    if (m == kNone) return;
+    if (m >= sc.materials.size()) fail(RT_ERR_INVALID_ARG, "material id out of range");
+    const RtMaterialDesc& d = sc.materials[m];
+    if (d.kind == RT_MAT_USER)
+      fail(RT_ERR_USER_DEFINED, "scene uses a user-defined Material closure; only the library's own "
+                                "materials (Material.hs:41-129) can be flattened — no CPU fallback");
+    if (d.kind < RT_MAT_LIGHT || d.kind > RT_MAT_USER) fail(RT_ERR_INVALID_ARG, "unknown material kind");
+    mat_used[m] = 1;
+    if (d.kind != RT_MAT_PITCH_BLACK && d.kind != RT_MAT_DIELECTRIC) {
+      if (d.texture >= sc.textures.size()) fail(RT_ERR_INVALID_ARG, "texture id out of range");
+      int tk = sc.textures[d.texture].d.kind;
+      if (tk == RT_TEX_USER)
+        fail(RT_ERR_USER_DEFINED, "scene uses a user-defined Texture closure (solidTexture / uvTexture / "
+                                  "Texture); only Texture.hs:18-79's constructors can be flattened — no CPU fallback");
+      if (tk < RT_TEX_CONSTANT || tk > RT_TEX_USER) fail(RT_ERR_INVALID_ARG, "unknown texture kind");
+      tex_used[d.texture] = 1;
+    }
+  }
+
+  int leaf_for(HPrim&& p, const BoxD& ref_box) {
+    prims.push_back(std::move(p));
+    int r = new_rnode(RNode::LEAF);
+    rnodes[r].prim = (uint32_t)prims.size() - 1;
+    rnodes[r].ref_box = ref_box;
+    return r;
+  }
+
+  void finish_prim(HPrim& p, const XfState& xf, uint32_t node, uint32_t sub, uint32_t material, const BoxD& local_box) {
+    p.xform = xform_id(xf);
+    p.geom = geom_for(node, sub, p.xform);
+    p.canonical = canonical_for(node, sub);
+    p.material = material;
+    // world box: corners of the local box mapped forward (at both shutter ends when moving)
+    BoxD wb;
+    for (int i = 0; i < 8; i++) {
+      D3 c{(i & 1) ? local_box.hi[0] : local_box.lo[0], (i & 2) ? local_box.hi[1] : local_box.lo[1], (i & 4) ? local_box.hi[2] : local_box.lo[2]};
+      wb.add(xf.fwd.pt(c, 0));
+      if (xf.moving) wb.add(xf.fwd.pt(c, 1));
+    }
+    p.box = wb;
+    if (xf.moving) p.flags |= PRIM_FLAG_MOVING;
+  }
+
+  int make_sphere(uint32_t node, uint32_t sub, D3 c, double r, const XfState& xf, uint32_t material) {
+    HPrim p;
+    p.type = PRIM_SPHERE;
+    BoxD ref;  // Geometry.hs:60-61
+    ref.add({c.x - r, c.y - r, c.z - r});
+    ref.add({c.x + r, c.y + r, c.z + r});
+    BoxD local = ref;
+    if (xf.moving) { p.c = c; }
+    else { p.c = xf.fwd.pt(c, 0); }
+    p.r = r;
+    finish_prim(p, xf, node, sub, material, local);
+    if (!xf.moving) {  // exact world box of a sphere under a Euclidean map
+      BoxD wb;
+      wb.add({p.c.x - std::fabs(r), p.c.y - std::fabs(r), p.c.z - std::fabs(r)});
+      wb.add({p.c.x + std::fabs(r), p.c.y + std::fabs(r), p.c.z + std::fabs(r)});
+      p.box = wb;
+      // uv (sphereUV, Geometry.hs:100-104) is a function of the LOCAL outward normal
+      bool rot = false;
+      for (int i = 0; i < 9; i++) if (std::fabs(xf.fwd.M[i] - ((i % 4 == 0) ? 1.0 : 0.0)) > 1e-15) rot = true;
+      if (rot) p.flags |= PRIM_FLAG_UVXFORM;
+    } else p.flags |= PRIM_FLAG_UVXFORM;
+    // fp32 cannot hold |oc|^2 - r^2 for large radii next to small scene detail → fp64 discriminant
+    if (std::fabs(r) >= 64.0) p.flags |= PRIM_FLAG_BIG;
+    return leaf_for(std::move(p), ref);
+  }
+
+  // planeShape (Geometry.hs:117-144) for the two library shapes
+  int make_planar(uint32_t node, uint32_t sub, bool tri, D3 q, D3 u, D3 v, const double uv[3][2], const XfState& xf, uint32_t material) {
+    HPrim p;
+    p.type = tri ? PRIM_TRI : PRIM_PGRAM;
+    D3 cp = cross(u, v);
+    double ncp = std::sqrt(dot(cp, cp));
+    D3 n{0, 0, 0}, wa{0, 0, 0}, wb{0, 0, 0};
+    if (ncp > 0 && std::isfinite(ncp)) {
+      n = (1.0 / ncp) * cp;
+      D3 nS = (1.0 / ncp) * n;
+      wa = cross(v, nS);   // a = nS . ((p-q) x v) = (p-q) . (v x nS)
+      wb = cross(nS, u);   // b = nS . (u x (p-q)) = (p-q) . (nS x u)
+    }  // degenerate shape: normal is NaN in the reference → `abs denom > 1e-8` is False → never hit
+    BoxD hull;
+    hull.add(q); hull.add(q + u); hull.add(q + v);
+    if (!tri) hull.add(q + u + v);
+    BoxD ref = hull;
+    ref.pad(0.0001);       // Geometry.hs:144
+    if (xf.moving) { p.c = q; p.n = n; p.wa = wa; p.wb = wb; }
+    else { p.c = xf.fwd.pt(q, 0); p.n = xf.fwd.lin(n); p.wa = xf.fwd.lin(wa); p.wb = xf.fwd.lin(wb); }
+    if (uv) std::memcpy(p.uv, uv, sizeof p.uv);
+    finish_prim(p, xf, node, sub, material, hull);
+    return leaf_for(std::move(p), ref);
+  }
+
+  // ---- reference-policy BVH over RNodes (Geometry.hs:369-377) ------------------------------------
+  int bvh_tree(std::vector<int> obs) {
+    if (obs.size() == 1) return obs[0];
+    BoxD all;
+    for (int o : obs) all.join(rnodes[o].ref_box);
+    int d = longest_dim(all);
+    std::stable_sort(obs.begin(), obs.end(), [&](int a, int b) {
+      const BoxD& A = rnodes[a].ref_box;
+      const BoxD& B = rnodes[b].ref_box;
+      return (A.lo[d] + A.hi[d]) / 2 < (B.lo[d] + B.hi[d]) / 2;
+    });
+    size_t n = obs.size() / 2;
+    std::vector<int> left(obs.begin(), obs.begin() + n), right(obs.begin() + n, obs.end());
+    int l = bvh_tree(std::move(left));
+    int r = bvh_tree(std::move(right));
+    int node = new_rnode(RNode::BVH);
+    rnodes[node].children = {l, r};
+    rnodes[node].ref_box = rnodes[l].ref_box;
+    rnodes[node].ref_box.join(rnodes[r].ref_box);
+    return node;
+  }
+
+  // ---- description tree walk ------------------------------------------------------------------------
+  // Returns the RNode of the SURFACE geometry of this subtree (-1 when it has none, e.g. a medium) and
+  // the reference's bounding box of the whole subtree in *ref_box.
+  int walk(uint32_t id, const XfState& xf, uint32_t material, BoxD* ref_box) {
+    if (id >= sc.nodes.size()) fail(RT_ERR_INVALID_ARG, "node id out of range");
+    if (++depth_guard > 4096) fail(RT_ERR_INVALID_ARG, "description tree too deep (cycle?)");
+    const HostNode& n = sc.nodes[id];
+    int result = -1;
+    BoxD rb;
+    switch (n.kind) {
+      case RT_NODE_SPHERE: {
+        result = make_sphere(id, 0, mk(n.v[0]), n.s[0], xf, material);
+        rb = rnodes[result].ref_box;
+        break;
+      }
+      case RT_NODE_PARALLELOGRAM: {
+        result = make_planar(id, 0, false, mk(n.v[0]), mk(n.v[1]), mk(n.v[2]), nullptr, xf, material);
+        rb = rnodes[result].ref_box;
+        break;
+      }
+      case RT_NODE_TRIANGLE: {
+        D3 p0 = mk(n.v[0]);
+        result = make_planar(id, 0, true, p0, mk(n.v[1]) - p0, mk(n.v[2]) - p0, n.uv, xf, material);
+        rb = rnodes[result].ref_box;
+        break;
+      }
+      case RT_NODE_CUBOID: {  // Geometry.hs:154-166: face order front, back, left, right, top, bottom
+        double xmin = n.v[0][0], ymin = n.v[0][1], zmin = n.v[0][2], xmax = n.v[1][0], ymax = n.v[1][1], zmax = n.v[1][2];
+        D3 dx{xmax - xmin, 0, 0}, dy{0, ymax - ymin, 0}, dz{0, 0, zmax - zmin};
+        D3 mdx = -1.0 * dx, mdz = -1.0 * dz;
+        struct F { D3 q, u, v; } faces[6] = {
+            {{xmin, ymin, zmax}, dx, dy}, {{xmax, ymin, zmin}, mdx, dy}, {{xmin, ymin, zmin}, dz, dy},
+            {{xmax, ymin, zmax}, mdz, dy}, {{xmin, ymax, zmax}, dx, mdz}, {{xmin, ymin, zmin}, dx, dz}};
+        int g = new_rnode(RNode::GROUP);
+        std::vector<int> ch;
+        for (uint32_t f = 0; f < 6; f++) {
+          int leaf = make_planar(id, f, false, faces[f].q, faces[f].u, faces[f].v, nullptr, xf, material);
+          ch.push_back(leaf);
+          rb.join(rnodes[leaf].ref_box);
+        }
+        rnodes[g].children = ch;
+        rnodes[g].ref_box = rb;
+        result = g;
+        break;
+      }
+      case RT_NODE_MESH: {  // triangleMesh, Geometry.hs:288-294
+        size_t nf = n.faces.size() / 6;
+        if (nf == 0) fail(RT_ERR_EMPTY_BVH, "bvhTree: empty list");
+        static const double def_uv[3][2] = {{0, 0}, {1, 0}, {0, 1}};
+        std::vector<int> tris;
+        tris.reserve(nf);
+        size_t nv = n.verts.size() / 3, nt = n.uvs.size() / 2;
+        for (size_t f = 0; f < nf; f++) {
+          const int32_t* fi = &n.faces[6 * f];
+          double uv[3][2];
+          D3 p[3];
+          for (int k = 0; k < 3; k++) {
+            int32_t vi = fi[2 * k], ti = fi[2 * k + 1];
+            if (vi < 0 || (size_t)vi >= nv) fail(RT_ERR_INVALID_ARG, "mesh vertex index out of range");
+            if (ti >= 0 && (size_t)ti >= nt) fail(RT_ERR_INVALID_ARG, "mesh uv index out of range");
+            p[k] = mk(&n.verts[3 * vi]);
+            uv[k][0] = ti >= 0 ? n.uvs[2 * ti] : def_uv[k][0];
+            uv[k][1] = ti >= 0 ? n.uvs[2 * ti + 1] : def_uv[k][1];
+          }
+          tris.push_back(make_planar(id, (uint32_t)f, true, p[0], p[1] - p[0], p[2] - p[0], uv, xf, material));
+        }
+        result = bvh_tree(std::move(tris));
+        rb = rnodes[result].ref_box;
+        break;
+      }
+      case RT_NODE_GROUP:
+      case RT_NODE_BVH_TREE:
+      case RT_NODE_BVH_NODE: {
+        if (n.kind == RT_NODE_BVH_NODE && n.children.size() != 2) fail(RT_ERR_INVALID_ARG, "bvhNode needs exactly two children");
+        if (n.children.empty()) {
+          if (n.kind == RT_NODE_BVH_TREE) fail(RT_ERR_EMPTY_BVH, "bvhTree: empty list");
+          fail(RT_ERR_INVALID_ARG, "group: empty list (boxJoin of an empty list)");
+        }
+        std::vector<int> ch;
+        for (uint32_t c : n.children) {
+          BoxD cb;
+          int r = walk(c, xf, material, &cb);
+          rb.join(cb);
+          if (r >= 0) { rnodes[r].ref_box = cb; ch.push_back(r); }
+        }
+        if (ch.empty()) { result = -1; break; }
+        if (n.kind == RT_NODE_GROUP) {
+          if (ch.size() == 1) { result = ch[0]; break; }
+          int g = new_rnode(RNode::GROUP);
+          rnodes[g].children = ch;
+          result = g;
+        } else if (n.kind == RT_NODE_BVH_TREE) {
+          result = bvh_tree(ch);
+        } else {
+          if (ch.size() == 1) { result = ch[0]; break; }
+          int b = new_rnode(RNode::BVH);
+          rnodes[b].children = ch;
+          result = b;
+        }
+        break;
+      }
+      case RT_NODE_TRANSFORM: {  // Geometry.hs:382-391
+        if (n.children.size() != 1) fail(RT_ERR_INVALID_ARG, "transform needs one child");
+        const double* m = n.m;
+        if (std::fabs(m[12]) > 1e-12 || std::fabs(m[13]) > 1e-12 || std::fabs(m[14]) > 1e-12 || std::fabs(m[15] - 1) > 1e-12)
+          fail(RT_ERR_NON_EUCLIDEAN, "transform: bottom row of the matrix must be 0 0 0 1");
+        Affine f;
+        for (int r = 0; r < 3; r++) { for (int c = 0; c < 3; c++) f.M[r * 3 + c] = m[r * 4 + c]; f.c0[r] = m[r * 4 + 3]; }
+        for (int i = 0; i < 3; i++)
+          for (int j = 0; j < 3; j++) {
+            double s = 0;
+            for (int k = 0; k < 3; k++) s += f.M[k * 3 + i] * f.M[k * 3 + j];
+            if (std::fabs(s - (i == j ? 1.0 : 0.0)) > 1e-9)
+              fail(RT_ERR_NON_EUCLIDEAN, "transform: matrix is not Euclidean (rotation/reflection + translation); "
+                                         "use transformVertices for scaling (Geometry.hs:379-381,434)");
+          }
+        Affine g;  // inverse of a Euclidean map: M^T, -M^T c
+        for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) g.M[i * 3 + j] = f.M[j * 3 + i];
+        D3 t = g.lin(mk(f.c0));
+        g.c0[0] = -t.x; g.c0[1] = -t.y; g.c0[2] = -t.z;
+        XfState x2;
+        x2.fwd = compose(xf.fwd, f);
+        x2.inv = compose(g, xf.inv);
+        x2.identity = false;
+        x2.moving = xf.moving;
+        x2.chain = xf.chain;
+        x2.chain.push_back(id);
+        BoxD cb;
+        result = walk(n.children[0], x2, material, &cb);
+        for (int i = 0; i < 8; i++) {  // boxHull of the mapped corners (Geometry.hs:386-387)
+          D3 c{(i & 4) ? cb.hi[0] : cb.lo[0], (i & 2) ? cb.hi[1] : cb.lo[1], (i & 1) ? cb.hi[2] : cb.lo[2]};
+          rb.add(f.pt(c, 0));
+        }
+        break;
+      }
+      case RT_NODE_MOVING: {  // Geometry.hs:449-456: shift = (1-time) v0 + time v1
+        if (n.children.size() != 1) fail(RT_ERR_INVALID_ARG, "moving needs one child");
+        Affine f, g;
+        for (int k = 0; k < 3; k++) { f.c0[k] = n.v[0][k]; f.c1[k] = n.v[1][k] - n.v[0][k]; g.c0[k] = -f.c0[k]; g.c1[k] = -f.c1[k]; }
+        XfState x2;
+        x2.fwd = compose(xf.fwd, f);
+        x2.inv = compose(g, xf.inv);
+        x2.identity = false;
+        x2.moving = true;
+        x2.chain = xf.chain;
+        x2.chain.push_back(id);
+        BoxD cb;
+        result = walk(n.children[0], x2, material, &cb);
+        for (int k = 0; k < 3; k++) {
+          rb.lo[k] = std::min(cb.lo[k] + n.v[0][k], cb.lo[k] + n.v[1][k]);
+          rb.hi[k] = std::max(cb.hi[k] + n.v[0][k], cb.hi[k] + n.v[1][k]);
+        }
+        break;
+      }
+      case RT_NODE_MEDIUM: {  // Geometry.hs:298-330 — hoisted
+        if (n.children.size() != 1) fail(RT_ERR_INVALID_ARG, "constantMedium needs one child");
+        if (material == kNone) fail(RT_ERR_TYPE, "constantMedium without a material (expected `material <$ constantMedium ...`)");
+        if (!(n.s[0] > 0)) fail(RT_ERR_INVALID_ARG, "constantMedium: density must be positive");
+        BoxD cb;
+        int b = walk(n.children[0], xf, kNone, &cb);
+        if (b < 0) fail(RT_ERR_INVALID_ARG, "constantMedium: boundary has no surface");
+        rnodes[b].ref_box = cb;
+        media.push_back({n.s[0], b, material});
+        rb = cb;
+        result = -1;
+        break;
+      }
+      case RT_NODE_WITH_MATERIAL: {  // outermost `<$` wins
+        if (n.children.size() != 1) fail(RT_ERR_INVALID_ARG, "<$ needs one child");
+        uint32_t m = material;
+        if (m == kNone) { m = n.material; use_material(m); }
+        result = walk(n.children[0], xf, m, &rb);
+        break;
+      }
+      case RT_NODE_PURE: {
+        if (n.children.size() != 1) fail(RT_ERR_INVALID_ARG, "pureGeometry needs one child");
+        result = walk(n.children[0], xf, material, &rb);
+        break;
+      }
+      case RT_NODE_USER:
+        fail(RT_ERR_USER_DEFINED, "scene uses a user-defined shape (planeShape with a custom predicate or a raw "
+                                  "Geometry closure); only the library's own shapes can be flattened — no CPU fallback");
+      default: fail(RT_ERR_INVALID_ARG, "unknown node kind");
+    }
+    --depth_guard;
+    *ref_box = rb;
+    return result;
+  }
+
+  // ---- numbering in the reference's evaluation order ---------------------------------------------------
+  uint32_t next_index = 0;
+  void number(int r, bool surface) {
+    RNode& n = rnodes[r];
+    if (n.kind == RNode::LEAF) {
+      HPrim& p = prims[n.prim];
+      if (surface && p.material == kNone)
+        fail(RT_ERR_TYPE, "raytrace: world is a Geometry m () — attach materials with `<$` (Ray.hs:121)");
+      p.index = next_index++;
+      return;
+    }
+    for (int c : n.children) number(c, surface);
+  }
+
+  // ---- device-shaped tree --------------------------------------------------------------------------------
+  static constexpr uint32_t kLeafMax = 8;
+  bool all_single_leaves(const RNode& n) const {
+    for (int c : n.children) if (rnodes[c].kind != RNode::LEAF) return false;
+    return true;
+  }
+  int median_build(std::vector<int> hs) {  // the reference's split policy on device boxes
+    if (hs.size() == 1) return hs[0];
+    BoxD all;
+    for (int h : hs) all.join(hnodes[h].box);
+    int d = longest_dim(all);
+    std::stable_sort(hs.begin(), hs.end(), [&](int a, int b) {
+      return (hnodes[a].box.lo[d] + hnodes[a].box.hi[d]) / 2 < (hnodes[b].box.lo[d] + hnodes[b].box.hi[d]) / 2;
+    });
+    size_t n = hs.size() / 2;
+    std::vector<int> l(hs.begin(), hs.begin() + n), r(hs.begin() + n, hs.end());
+    int li = median_build(std::move(l)), ri = median_build(std::move(r));
+    hnodes.emplace_back();
+    int me = (int)hnodes.size() - 1;
+    hnodes[me].left = li; hnodes[me].right = ri;
+    hnodes[me].box = hnodes[li].box;
+    hnodes[me].box.join(hnodes[ri].box);
+    return me;
+  }
+  int to_device(int r) {
+    const RNode n = rnodes[r];  // copy: hnodes/rnodes may grow
+    if (n.kind == RNode::LEAF) {
+      hnodes.emplace_back();
+      int me = (int)hnodes.size() - 1;
+      hnodes[me].first = prims[n.prim].index; hnodes[me].count = 1;
+      hnodes[me].box = prims[n.prim].box;
+      return me;
+    }
+    if (n.kind == RNode::GROUP && n.children.size() <= kLeafMax && all_single_leaves(n)) {
+      hnodes.emplace_back();       // e.g. a cuboid: one leaf of 6 parallelograms (contiguous indices)
+      int me = (int)hnodes.size() - 1;
+      hnodes[me].first = prims[rnodes[n.children[0]].prim].index;
+      hnodes[me].count = (uint32_t)n.children.size();
+      for (int c : n.children) hnodes[me].box.join(prims[rnodes[c].prim].box);
+      return me;
+    }
+    std::vector<int> hs;
+    for (int c : n.children) hs.push_back(to_device(c));
+    if (n.kind == RNode::BVH) {
+      hnodes.emplace_back();
+      int me = (int)hnodes.size() - 1;
+      hnodes[me].left = hs[0]; hnodes[me].right = hs[1];
+      hnodes[me].box = hnodes[hs[0]].box;
+      hnodes[me].box.join(hnodes[hs[1]].box);
+      return me;
+    }
+    return median_build(std::move(hs));  // GROUP → BVH (results identical to the linear scan)
+  }
+
+  static float round_down(double x) { float f = (float)x; return (double)f > x ? std::nextafterf(f, -INFINITY) : f; }
+  static float round_up(double x) { float f = (float)x; return (double)f < x ? std::nextafterf(f, INFINITY) : f; }
+  void write_node(DNode& d, const HNode& h) {
+    double m = 0;
+    for (int k = 0; k < 3; k++) m = std::max(m, std::max(std::fabs(h.box.lo[k]), std::fabs(h.box.hi[k])));
+    double pad = 1e-5 * m + 1e-6;  // slab test runs in fp32: keep boxes conservative
+    for (int k = 0; k < 3; k++) { d.lo[k] = round_down(h.box.lo[k] - pad); d.hi[k] = round_up(h.box.hi[k] + pad); }
+  }
+  // emit the pair (l, r) at nodes[at], nodes[at+1]; r < 0 → never-hit dummy
+  uint32_t emit_pair(FlatScene& fs, int l, int r, uint32_t depth, uint32_t& max_depth) {
+    uint32_t at = (uint32_t)fs.nodes.size();
+    fs.nodes.emplace_back();
+    fs.nodes.emplace_back();
+    max_depth = std::max(max_depth, depth);
+    int ids[2] = {l, r};
+    for (int k = 0; k < 2; k++) {
+      DNode d;
+      if (ids[k] < 0) {  // sibling slot of a root: a leaf with zero primitives, parked far away
+        for (int j = 0; j < 3; j++) { d.lo[j] = 3.0e38f; d.hi[j] = 3.0e38f; }
+        d.a = 0; d.b = kLeafBit;
+      } else {
+        const HNode h = hnodes[ids[k]];
+        write_node(d, h);
+        if (h.left >= 0) { d.b = 0; d.a = emit_pair(fs, h.left, h.right, depth + 1, max_depth); }
+        else { d.a = h.first; d.b = kLeafBit | h.count; }
+      }
+      fs.nodes[at + k] = d;
+    }
+    return at;
+  }
+
+  void pack_prims(FlatScene& fs) {
+    size_t n = prims.size();
+    fs.prims.assign(n * 16, 0.f);
+    fs.tri_uv.assign(n * 8, 0.f);
+    fs.canonical.assign(n, kNone);
+    for (const HPrim& p : prims) {
+      if (p.index == kNone) continue;
+      float* o = &fs.prims[(size_t)p.index * 16];
+      if (p.type == PRIM_SPHERE) {
+        o[0] = (float)p.c.x; o[1] = (float)p.c.y; o[2] = (float)p.c.z; o[3] = (float)p.r;
+        // fp64 copy for the large-radius path: hi parts in o[0..3], lo parts in o[4..7]
+        o[4] = (float)(p.c.x - (double)o[0]); o[5] = (float)(p.c.y - (double)o[1]); o[6] = (float)(p.c.z - (double)o[2]);
+        o[7] = (float)(p.r - (double)o[3]);
+        fs.n_spheres++;
+      } else {
+        o[0] = (float)p.c.x; o[1] = (float)p.c.y; o[2] = (float)p.c.z;
+        o[3] = (float)p.n.x; o[4] = (float)p.n.y; o[5] = (float)p.n.z;
+        o[6] = (float)p.wa.x; o[7] = (float)p.wa.y; o[8] = (float)p.wa.z;
+        o[9] = (float)p.wb.x; o[10] = (float)p.wb.y; o[11] = (float)p.wb.z;
+        fs.n_planars++;
+      }
+      uint32_t meta[4] = {p.type | p.flags, p.geom, p.xform, p.material};
+      std::memcpy(o + 12, meta, 16);
+      float* u = &fs.tri_uv[(size_t)p.index * 8];
+      for (int k = 0; k < 3; k++) { u[2 * k] = (float)p.uv[k][0]; u[2 * k + 1] = (float)p.uv[k][1]; }
+      fs.canonical[p.index] = p.canonical;
+    }
+  }
+};
+
+void fill_d3(float* o, const double* v) { o[0] = (float)v[0]; o[1] = (float)v[1]; o[2] = (float)v[2]; }
+
+}  // namespace
+
+uint64_t FlatScene::bytes() const {
+  return nodes.size() * sizeof(DNode) + prims.size() * 4 + tri_uv.size() * 4 + canonical.size() * 4 +
+         xforms.size() * sizeof(DXform) + materials.size() * sizeof(DMaterial) + textures.size() * sizeof(DTexture) +
+         texels.size() * 4 + noise_grad.size() * 4 + noise_perm.size();
+}
+
+// ---- default Perlin tables (Noise.hs:52-92) ---------------------------------------------------------------
+// The three permutation tables are the reference's literals.  The gradient table is what
+// `evalState (replicateM 256 randomUnitVector) (mkStdGen 666)` yields under a restatement of
+// SplitMix (the `random` package is not part of the reference tree: PARITY UNPINNED — a Haskell
+// front end passes its own table through rt_scene_set_noise_tables).
+namespace {
+const uint8_t kPX[256] = {
+    179, 60, 35, 16, 220, 94, 67, 236, 106, 112, 65, 166, 83, 101, 246, 140, 219, 186, 113, 88, 153, 70, 34, 63, 157, 210, 212, 188, 54, 74, 23, 161,
+    28, 137, 126, 107, 183, 58, 134, 127, 211, 225, 17, 123, 150, 243, 160, 68, 75, 239, 173, 221, 89, 109, 61, 72, 159, 80, 154, 18, 214, 144, 197, 24,
+    105, 32, 84, 226, 136, 29, 139, 97, 230, 167, 165, 238, 27, 14, 50, 193, 46, 253, 240, 111, 69, 196, 130, 102, 104, 118, 204, 12, 169, 202, 142, 25,
+    245, 215, 149, 138, 185, 48, 223, 247, 47, 98, 143, 26, 87, 251, 103, 52, 234, 232, 218, 205, 92, 228, 162, 85, 122, 191, 242, 164, 129, 192, 255, 231,
+    147, 91, 178, 213, 176, 36, 120, 155, 241, 222, 177, 20, 152, 141, 51, 171, 250, 95, 71, 119, 254, 172, 53, 146, 135, 124, 125, 163, 235, 99, 7, 22,
+    100, 229, 93, 174, 3, 189, 116, 66, 217, 158, 237, 55, 151, 0, 148, 45, 86, 64, 216, 43, 252, 121, 200, 115, 39, 184, 82, 56, 9, 181, 62, 2,
+    81, 209, 44, 79, 19, 110, 41, 10, 194, 15, 132, 224, 249, 96, 233, 117, 49, 203, 5, 37, 11, 59, 168, 114, 90, 131, 31, 145, 40, 206, 13, 187,
+    133, 207, 4, 199, 170, 78, 30, 182, 248, 21, 6, 227, 57, 180, 73, 42, 128, 175, 108, 33, 244, 201, 198, 77, 195, 8, 38, 190, 76, 156, 208, 1};
+const uint8_t kPY[256] = {
+    252, 123, 131, 151, 243, 143, 12, 247, 196, 179, 99, 0, 178, 109, 71, 160, 93, 205, 127, 38, 142, 117, 152, 124, 166, 95, 200, 121, 15, 17, 10, 190,
+    116, 158, 173, 75, 248, 191, 197, 58, 70, 184, 226, 146, 6, 239, 165, 113, 218, 34, 83, 77, 74, 5, 176, 85, 112, 147, 59, 66, 14, 31, 2, 21,
+    198, 108, 255, 11, 36, 156, 96, 73, 1, 189, 126, 50, 220, 16, 249, 23, 139, 135, 141, 92, 159, 4, 119, 174, 171, 253, 86, 227, 251, 172, 7, 149,
+    207, 212, 224, 44, 187, 91, 175, 84, 28, 211, 180, 195, 52, 98, 244, 125, 138, 54, 210, 201, 209, 219, 133, 240, 9, 202, 199, 42, 51, 48, 104, 154,
+    88, 53, 64, 105, 242, 63, 223, 222, 67, 238, 32, 134, 72, 62, 101, 150, 94, 161, 19, 236, 215, 97, 206, 22, 188, 230, 170, 18, 13, 162, 129, 90,
+    246, 130, 35, 46, 43, 213, 29, 76, 241, 61, 30, 136, 235, 87, 114, 68, 183, 177, 250, 132, 3, 122, 110, 145, 81, 78, 232, 69, 60, 80, 216, 65,
+    164, 237, 157, 203, 25, 221, 254, 181, 8, 182, 214, 24, 40, 102, 37, 106, 228, 39, 229, 163, 111, 186, 245, 55, 41, 225, 234, 49, 45, 231, 107, 103,
+    168, 153, 47, 56, 118, 120, 137, 155, 148, 82, 33, 204, 79, 169, 144, 20, 27, 128, 192, 217, 100, 208, 115, 140, 233, 89, 193, 185, 167, 57, 26, 194};
+const uint8_t kPZ[256] = {
+    153, 90, 163, 138, 20, 136, 79, 100, 93, 38, 185, 31, 193, 43, 161, 2, 30, 37, 87, 6, 127, 207, 96, 51, 27, 227, 203, 215, 155, 190, 106, 94,
+    65, 183, 114, 71, 74, 219, 245, 39, 140, 216, 195, 191, 3, 214, 13, 23, 168, 179, 218, 133, 102, 53, 194, 124, 166, 108, 116, 246, 35, 109, 220, 121,
+    205, 110, 83, 242, 252, 231, 25, 128, 61, 57, 187, 222, 189, 228, 148, 101, 239, 162, 48, 150, 55, 174, 178, 42, 200, 160, 58, 206, 11, 92, 204, 67,
+    8, 113, 34, 172, 181, 177, 66, 16, 243, 159, 197, 135, 249, 241, 28, 147, 158, 139, 176, 88, 29, 149, 254, 226, 192, 201, 202, 186, 69, 45, 72, 199,
+    107, 99, 209, 10, 230, 217, 247, 89, 50, 129, 15, 64, 248, 167, 180, 146, 210, 169, 4, 81, 97, 238, 5, 237, 125, 236, 95, 9, 104, 221, 32, 86,
+    165, 134, 224, 182, 198, 234, 253, 59, 164, 52, 60, 208, 103, 22, 46, 188, 54, 12, 1, 112, 144, 137, 47, 156, 98, 78, 18, 82, 175, 225, 19, 184,
+    244, 49, 120, 157, 130, 70, 80, 251, 212, 250, 119, 118, 196, 223, 105, 68, 84, 21, 145, 173, 56, 235, 91, 17, 126, 76, 131, 117, 152, 111, 33, 36,
+    233, 141, 122, 85, 7, 123, 44, 62, 115, 26, 0, 40, 229, 211, 213, 63, 143, 77, 14, 24, 142, 154, 73, 132, 171, 41, 170, 240, 75, 151, 232, 255};
+
+// SplitMix64 as a small generator object
+class SplitMix {
+ public:
+  explicit SplitMix(uint64_t n) : state_(finalize(n)), gamma_(odd_gamma(n + kGolden)) {}
+  uint64_t word() { state_ += gamma_; return finalize(state_); }
+  double unit() { return (double)(word() >> 11) * 0x1.0p-53; }
+  double range(double lo, double hi) { return lo + (hi - lo) * unit(); }
+ private:
+  static constexpr uint64_t kGolden = 0x9e3779b97f4a7c15ULL;
+  static uint64_t finalize(uint64_t z) {
+    z ^= z >> 33; z *= 0xff51afd7ed558ccdULL;
+    z ^= z >> 33; z *= 0xc4ceb9fe1a85ec53ULL;
+    return z ^ (z >> 33);
+  }
+  static uint64_t odd_gamma(uint64_t z) {
+    z ^= z >> 30; z *= 0xbf58476d1ce4e5b9ULL;
+    z ^= z >> 27; z *= 0x94d049bb133111ebULL;
+    z = (z ^ (z >> 31)) | 1ULL;
+    return __builtin_popcountll(z ^ (z >> 1)) < 24 ? z ^ 0xaaaaaaaaaaaaaaaaULL : z;
+  }
+  uint64_t state_, gamma_;
+};
+}  // namespace
+
+void default_noise_tables(int32_t perm[3][256], double grad[256][3]) {
+  for (int i = 0; i < 256; i++) { perm[0][i] = kPX[i]; perm[1][i] = kPY[i]; perm[2][i] = kPZ[i]; }
+  SplitMix g(666);
+  for (int i = 0; i < 256; i++) {
+    for (;;) {  // randomUnitVector, Core.hs:54-60
+      double x = g.range(-1, 1), y = g.range(-1, 1), z = g.range(-1, 1);
+      double q = x * x + y * y + z * z;
+      if (1e-8 <= q && q <= 1) {
+        double s = std::sqrt(q);
+        grad[i][0] = x / s; grad[i][1] = y / s; grad[i][2] = z / s;
+        break;
+      }
+    }
+  }
+}
+
+int32_t flatten_scene(Scene& sc, uint32_t root) {
+  try {
+    Builder b(sc);
+    b.mat_used.assign(sc.materials.size(), 0);
+    b.tex_used.assign(sc.textures.size(), 0);
+    XfState id;
+    BoxD rb;
+    int surf = b.walk(root, id, kNone, &rb);
+    if (surf >= 0) b.number(surf, true);
+    for (auto& m : b.media) b.number(m.rtree, false);
+    if (b.media.size() > (size_t)kMaxMedia) b.fail(RT_ERR_UNSUPPORTED, "more than 16 constantMedium volumes in one scene");
+
+    FlatScene fs;
+    uint32_t max_depth = 0;
+    if (surf >= 0) {
+      int h = b.to_device(surf);
+      fs.surface_root = b.emit_pair(fs, h, -1, 1, max_depth);
+    }
+    for (size_t i = 0; i < b.media.size(); i++) {
+      int h = b.to_device(b.media[i].rtree);
+      DMedium& dm = fs.media[i];
+      dm.neg_inv_density = (float)(-(1.0 / b.media[i].density));
+      dm.root = b.emit_pair(fs, h, -1, 1, max_depth);
+      dm.material = b.media[i].material;
+      dm.geom_lo = dm.geom_hi = 0;
+    }
+    fs.n_media = (uint32_t)b.media.size();
+    fs.max_depth = max_depth;
+    if (max_depth + 1 > (uint32_t)kStackDepth)
+      b.fail(RT_ERR_UNSUPPORTED, "flattened BVH is deeper than the shared-memory traversal stack (32 levels)");
+    b.pack_prims(fs);
+
+    fs.xforms.resize(b.xforms.size());
+    for (size_t i = 0; i < b.xforms.size(); i++) {
+      DXform& d = fs.xforms[i];
+      const XfState& x = b.xforms[i];
+      for (int k = 0; k < 9; k++) { d.Ainv[k] = (float)x.inv.M[k]; d.A[k] = (float)x.fwd.M[k]; }
+      fill_d3(d.binv0, x.inv.c0);
+      fill_d3(d.binv1, x.inv.c1);
+    }
+    fs.materials.resize(sc.materials.size());
+    for (size_t i = 0; i < sc.materials.size(); i++) {
+      fs.materials[i].kind = sc.materials[i].kind;
+      fs.materials[i].texture = sc.materials[i].texture;
+      fs.materials[i].param = (float)sc.materials[i].param;
+      fs.materials[i]._pad = 0;
+    }
+    fs.textures.resize(sc.textures.size());
+    for (size_t i = 0; i < sc.textures.size(); i++) {
+      const HostTexture& t = sc.textures[i];
+      DTexture& d = fs.textures[i];
+      std::memset(&d, 0, sizeof d);
+      d.kind = t.d.kind; d.i0 = t.d.i0; d.i1 = t.d.i1; d.freq = (float)t.d.freq;
+      fill_d3(d.c0, t.d.c0); fill_d3(d.c1, t.d.c1); fill_d3(d.shift, t.d.shift); fill_d3(d.dir, t.d.dir);
+      if (!b.tex_used[i]) continue;
+      if (t.d.kind == RT_TEX_IMAGE) {
+        if (t.d.width <= 0 || t.d.height <= 0 || t.image.empty()) b.fail(RT_ERR_INVALID_ARG, "imageTexture: empty image");
+        d.w = t.d.width; d.h = t.d.height;
+        d.image_offset = (uint32_t)(fs.texels.size() / 4);
+        size_t n = (size_t)d.w * d.h;
+        fs.texels.reserve(fs.texels.size() + n * 4);
+        for (size_t k = 0; k < n; k++) {
+          fs.texels.push_back(t.image[3 * k]); fs.texels.push_back(t.image[3 * k + 1]);
+          fs.texels.push_back(t.image[3 * k + 2]); fs.texels.push_back(0.f);
+        }
+      }
+      if (t.d.kind == RT_TEX_NOISE || t.d.kind == RT_TEX_MARBLE) fs.has_noise = 1;
+    }
+    fs.noise_grad.resize(256 * 3);
+    fs.noise_perm.resize(3 * 256);
+    for (int i = 0; i < 256; i++) {
+      for (int k = 0; k < 3; k++) {
+        fs.noise_grad[3 * i + k] = (float)sc.grad[i][k];
+        fs.noise_perm[k * 256 + i] = (uint8_t)(sc.perm[k][i] & 255);
+      }
+    }
+    sc.flat = std::move(fs);
+    sc.committed = true;
+    return RT_OK;
+  } catch (const FlattenError& e) {
+    set_error(e.msg);
+    return e.status;
+  } catch (const std::exception& e) {
+    set_error(std::string("internal error: ") + e.what());
+    return RT_ERR_INVALID_ARG;
+  }
+}
+
+}  // namespace rtb

@@ -1,0 +1,79 @@
+// rt_host.h — host-side scene object behind the C ABI (include/rt_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/rt_b200.h"
+#include "rt_device.h"
+
+namespace rtb {
+
+void set_error(const std::string& msg);  // thread-local last-error string
+
+struct HostTexture {
+  RtTextureDesc d;
+  std::vector<float> image;  // w*h*3 linear floats (copied at add time)
+};
+
+struct HostNode {  // one node of the description tree, copied at add time
+  int32_t kind = 0;
+  uint32_t material = 0;
+  std::vector<uint32_t> children;
+  double v[3][3] = {};
+  double s[2] = {};
+  double uv[3][2] = {};
+  double m[16] = {};
+  std::vector<double> verts, uvs;
+  std::vector<int32_t> faces;
+};
+
+// flattened, device-ready scene (host copy)
+struct FlatScene {
+  std::vector<DNode> nodes;
+  std::vector<float> prims;      // 16 floats per primitive
+  std::vector<float> tri_uv;     // 8 floats per primitive
+  std::vector<uint32_t> canonical;
+  std::vector<DXform> xforms;
+  std::vector<DMaterial> materials;
+  std::vector<DTexture> textures;
+  std::vector<float> texels;     // 4 floats per texel
+  std::vector<float> noise_grad; // 256*3
+  std::vector<uint8_t> noise_perm; // 3*256
+  DMedium media[kMaxMedia];
+  uint32_t n_media = 0;
+  uint32_t surface_root = kNone;
+  uint32_t has_noise = 0;
+  uint32_t n_spheres = 0, n_planars = 0;
+  uint32_t max_depth = 0;
+  uint64_t bytes() const;
+};
+
+struct DeviceScene;   // rt_kernels.cu: uploaded buffers + render workspace of one device
+
+struct Scene {
+  std::vector<HostTexture> textures;
+  std::vector<RtMaterialDesc> materials;
+  std::vector<HostNode> nodes;
+  int32_t perm[3][256];
+  double grad[256][3];
+  bool committed = false;
+  FlatScene flat;
+  uint32_t pool_size = 0;  // 0 = default
+  std::map<int, DeviceScene*> devices;
+  Scene();
+  ~Scene();
+};
+
+// rt_flatten.cpp
+int32_t flatten_scene(Scene& scene, uint32_t root);
+void default_noise_tables(int32_t perm[3][256], double grad[256][3]);
+
+// rt_kernels.cu
+void destroy_device_scene(DeviceScene* d);
+
+}  // namespace rtb

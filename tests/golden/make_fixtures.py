@@ -1,0 +1,50 @@
+"""Generate the committed fixtures under tests/golden/ from the reference tree.
+
+Run HERE (the authoring container, where /root/reference exists):
+    python tests/golden/make_fixtures.py
+Nothing in tests/, smoke() or bench.py reads /root/reference at run time; they read the
+.npz files this script writes.
+
+  assets/pawn.npz, assets/bunny.npz  — images/*.obj parsed by the pure-Python restatement of
+                                       parseObj (oracle/obj_oracle.py; Geometry.hs:207-285)
+  assets/earthmap.npz                — images/earthmap.jpg decoded by PIL to 8-bit sRGB
+                                       (readImage's decode step, Ray.hs:241-245; the sRGB→linear
+                                       step is applied at load time)
+  png/<name>.npz                     — the reference's golden renders, decoded to 8-bit RGB:
+                                       example_image (README scene, seed 100, 50 spp, writeImage),
+                                       cornell_box_noisy / cornell_box_redirect (200 spp, writeImageSqrt),
+                                       pawn_demo (500x500, 400 spp, depth 20, writeImage)
+"""
+import os
+import sys
+
+import numpy as np
+from PIL import Image
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+from oracle.obj_oracle import parse_obj  # noqa: E402
+
+REF = "/root/reference"
+
+
+def main():
+    os.makedirs(os.path.join(HERE, "assets"), exist_ok=True)
+    os.makedirs(os.path.join(HERE, "png"), exist_ok=True)
+    for name in ("pawn", "bunny"):
+        with open(f"{REF}/images/{name}.obj") as f:
+            v, t, fc = parse_obj(f.read())
+        np.savez_compressed(os.path.join(HERE, "assets", f"{name}.npz"), verts=v, uvs=t, faces=fc)
+        print(name, v.shape, t.shape, fc.shape)
+    img = np.asarray(Image.open(f"{REF}/images/earthmap.jpg").convert("RGB"), dtype=np.uint8)
+    np.savez_compressed(os.path.join(HERE, "assets", "earthmap.npz"), rgb8=img)
+    print("earthmap", img.shape)
+    for name in ("example_image", "cornell_box_noisy", "cornell_box_redirect", "pawn_demo"):
+        a = np.asarray(Image.open(f"{REF}/{name}.png").convert("RGB"), dtype=np.uint8)
+        np.savez_compressed(os.path.join(HERE, "png", f"{name}.npz"), rgb8=a)
+        print(name, a.shape)
+
+
+if __name__ == "__main__":
+    main()
