@@ -63,7 +63,7 @@ def lib():
     L.orc_image_height.argtypes = [C.POINTER(F.RtCamera)]
     L.orc_render.argtypes = [vp, C.POINTER(F.RtCamera), C.c_uint64, C.c_int32, C.c_int32, dp, dp,
                              C.POINTER(OrcCounters)]
-    L.orc_probe_primary.argtypes = [vp, C.POINTER(F.RtCamera), C.c_double, u32p, dp]
+    L.orc_probe_primary.argtypes = [vp, C.POINTER(F.RtCamera), C.c_double, C.c_double, C.c_double, u32p, dp]
     L.orc_perlin.argtypes = [vp, C.c_double, C.c_double, C.c_double]
     L.orc_perlin.restype = C.c_double
     L.orc_fractal.argtypes = [vp, C.c_int32, C.c_double, C.c_double, C.c_double]
@@ -210,15 +210,38 @@ class OracleScene:
             return mean, sq, cnt.as_dict()
         return mean, cnt.as_dict()
 
-    def probe_primary(self, settings: CameraSettings, time: float = 0.5):
+    def probe_primary(self, settings: CameraSettings, time: float = 0.5, dx: float = 0.5, dy: float = 0.5):
         cam = self.camera(settings)
         h, w = imageHeight(settings), settings.cs_imageWidth
         ids = np.zeros((h, w), np.uint32)
         ts = np.zeros((h, w), np.float64)
-        self._check(self.L.orc_probe_primary(self.h, C.byref(cam), float(time),
+        self._check(self.L.orc_probe_primary(self.h, C.byref(cam), float(time), float(dx), float(dy),
                                              ids.ctypes.data_as(C.POINTER(C.c_uint32)),
                                              ts.ctypes.data_as(C.POINTER(C.c_double))))
         return ids, ts
+
+    def probe_stable(self, settings: CameraSettings, time: float = 0.5, delta: float = None, t_tol: float = 1e-4,
+                     eps_rad: float = 2e-6):
+        """Centre probe plus the mask of WELL-CONDITIONED pixels: the oracle's own answer (primitive id, and t
+        within t_tol relative) does not change when the probe ray is tilted by ±eps_rad (2e-6 rad ~ 16 fp32 ulps of
+        a direction component; `delta` overrides it in pixel units).  A pixel that passes has a condition number
+        (dt/t)/dtheta < t_tol/eps_rad = 50, so fp32 input rounding alone (~1.2e-7 rad) cannot move t by 1e-5.
+        Pixels whose centre ray runs through a primitive edge or grazes a silhouette fail this; their reference
+        answer is fp64 rounding noise (README scene column 46: a = 2.2e-16 on the mirror's edge)."""
+        import math
+        if delta is None:
+            h = imageHeight(settings)
+            pixel_angle = 2.0 * math.tan(settings.cs_vfov / 2.0) / h
+            delta = eps_rad / pixel_angle
+        ids, ts = self.probe_primary(settings, time)
+        stable = np.ones(ids.shape, bool)
+        for ox, oy in ((-delta, 0.0), (delta, 0.0), (0.0, -delta), (0.0, delta)):
+            i2, t2 = self.probe_primary(settings, time, 0.5 + ox, 0.5 + oy)
+            stable &= i2 == ids
+            hit = (ids != 0xFFFFFFFF) & (i2 == ids)
+            with np.errstate(invalid="ignore", divide="ignore"):
+                stable &= ~hit | (np.abs(t2 - ts) <= t_tol * np.abs(ts))
+        return ids, ts, stable
 
     def perlin(self, x, y, z) -> float:
         return float(self.L.orc_perlin(self.h, x, y, z))

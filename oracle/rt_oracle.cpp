@@ -1039,13 +1039,15 @@ int32_t orc_render(void* sp, const RtCamera* rc, uint64_t seed, int32_t spp_over
 }
 
 // Deterministic probe: pixel-centre ray from cs_center (no lens sample), media skipped.
-int32_t orc_probe_primary(void* sp, const RtCamera* rc, double time, uint32_t* ids, double* ts) {
+// (dx, dy) = sub-pixel position of the probe ray (0.5, 0.5 = pixel centre); offsets near the centre are used by
+// the tests to find pixels whose answer is ill-conditioned (ray through an edge / silhouette).
+int32_t orc_probe_primary(void* sp, const RtCamera* rc, double time, double dx, double dy, uint32_t* ids, double* ts) {
   Scene& s = *(Scene*)sp;
   if (!s.root) { s.error = "oracle: not committed"; return RT_ERR_NOT_COMMITTED; }
   Camera cam = makeCamera(*rc);
   for (int j = 0; j < cam.H; j++)
     for (int i = 0; i < cam.W; i++) {
-      V3 target = cam.topLeft + ((double)i + 0.5) * cam.pixelU + ((double)j + 0.5) * cam.pixelV;
+      V3 target = cam.topLeft + ((double)i + dx) * cam.pixelU + ((double)j + dy) * cam.pixelV;
       Ray ray{cam.center, normalize(target - cam.center)};
       Ctx ctx;
       ctx.rng = mkStdGen(0);

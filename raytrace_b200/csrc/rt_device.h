@@ -79,6 +79,8 @@ struct DTarget {    // RedirectTarget, Ray.hs:112-118 (+ its parallelogram recor
 
 struct DCamera {    // Ray.hs:123-155, evaluated in double on the host, stored fp32
   int32_t W, H, spp, max_depth;
+  // top_left is stored RELATIVE to the camera centre (|.| ~ focus distance), so that pixel offsets are not
+  // rounded at world-coordinate magnitude (Cornell: 278 → 3e-6 direction error otherwise)
   float center[3], top_left[3], pixel_u[3], pixel_v[3], defocus_u[3], defocus_v[3];
   int32_t has_defocus;
   int32_t bg_kind;

@@ -250,7 +250,10 @@ struct Builder {
   }
 
   // planeShape (Geometry.hs:117-144) for the two library shapes
-  int make_planar(uint32_t node, uint32_t sub, bool tri, D3 q, D3 u, D3 v, const double uv[3][2], const XfState& xf, uint32_t material) {
+  // `corners` (triangles): the three vertices as given, so that the bounding box equals the reference's
+  // `boxHull [p0, p1, p2]` bit for bit (p0 + (p1 - p0) need not round back to p1).
+  int make_planar(uint32_t node, uint32_t sub, bool tri, D3 q, D3 u, D3 v, const double uv[3][2], const XfState& xf, uint32_t material,
+                  const D3* corners = nullptr) {
     HPrim p;
     p.type = tri ? PRIM_TRI : PRIM_PGRAM;
     D3 cp = cross(u, v);
@@ -263,8 +266,8 @@ struct Builder {
       wb = cross(nS, u);   // b = nS . (u x (p-q)) = (p-q) . (nS x u)
     }  // degenerate shape: normal is NaN in the reference → `abs denom > 1e-8` is False → never hit
     BoxD hull;
-    hull.add(q); hull.add(q + u); hull.add(q + v);
-    if (!tri) hull.add(q + u + v);
+    if (corners) { hull.add(corners[0]); hull.add(corners[1]); hull.add(corners[2]); }
+    else { hull.add(q); hull.add(q + u); hull.add(q + v); if (!tri) hull.add(q + u + v); }
     BoxD ref = hull;
     ref.pad(0.0001);       // Geometry.hs:144
     if (xf.moving) { p.c = q; p.n = n; p.wa = wa; p.wb = wb; }
@@ -317,8 +320,8 @@ struct Builder {
         break;
       }
       case RT_NODE_TRIANGLE: {
-        D3 p0 = mk(n.v[0]);
-        result = make_planar(id, 0, true, p0, mk(n.v[1]) - p0, mk(n.v[2]) - p0, n.uv, xf, material);
+        D3 pc[3] = {mk(n.v[0]), mk(n.v[1]), mk(n.v[2])};
+        result = make_planar(id, 0, true, pc[0], pc[1] - pc[0], pc[2] - pc[0], n.uv, xf, material, pc);
         rb = rnodes[result].ref_box;
         break;
       }
@@ -360,7 +363,7 @@ struct Builder {
             uv[k][0] = ti >= 0 ? n.uvs[2 * ti] : def_uv[k][0];
             uv[k][1] = ti >= 0 ? n.uvs[2 * ti + 1] : def_uv[k][1];
           }
-          tris.push_back(make_planar(id, (uint32_t)f, true, p[0], p[1] - p[0], p[2] - p[0], uv, xf, material));
+          tris.push_back(make_planar(id, (uint32_t)f, true, p[0], p[1] - p[0], p[2] - p[0], uv, xf, material, p));
         }
         result = bvh_tree(std::move(tris));
         rb = rnodes[result].ref_box;

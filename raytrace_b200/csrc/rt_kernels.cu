@@ -1,0 +1,694 @@
+// rt_kernels.cu — the wavefront path tracer (sm_100a) and the CUDA half of the C ABI.
+//
+// One render = a loop of four kernels over a pool of P live paths:
+//   k_raygen   : refill the free tail of the current queue with camera rays (Ray.hs:157-172,229),
+//                Philox counter RNG keyed by (seed; pixel, global sample, bounce, block)
+//   k_traverse : closest hit per live ray — BVH traversal with __ldg float4 node-pair fetches and a
+//                shared-memory short stack; media boundary queries + free-flight sampling
+//   k_shade    : material / texture / redirect-mixture evaluation, radiance accumulation, and
+//                warp-ballot/popc stream compaction of the surviving rays into the next queue
+//   k_advance  : one thread; swaps queue counters (keeps the loop free of host round trips)
+// The host reads the control block back only once per batch of iterations.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "rt_host.h"
+#include "rt_shade.cuh"
+
+namespace rtb {
+
+#define RT_CUDA(expr)                                                                            \
+  do {                                                                                           \
+    cudaError_t e_ = (expr);                                                                     \
+    if (e_ != cudaSuccess) {                                                                     \
+      set_error(std::string(#expr) + ": " + cudaGetErrorString(e_));                             \
+      return RT_ERR_CUDA;                                                                        \
+    }                                                                                            \
+  } while (0)
+
+constexpr int kTraverseBlock = 128;
+constexpr int kShadeBlock = 128;
+constexpr int kRaygenBlock = 256;
+
+struct Ctl {                      // device-resident control block of one render
+  unsigned long long next_item;   // next (sample, pixel) work item to start
+  unsigned long long total_items;
+  unsigned long long rays;        // path segments traversed so far
+  unsigned int n_cur, n_next;
+  unsigned int iterations, pool;
+};
+
+struct Queue {                    // SoA live-ray queue (56 B per path)
+  float4* o;                      // origin.xyz, shutter time
+  float4* d;                      // direction.xyz, origin geometry id (bits)
+  float4* thr;                    // throughput.rgb, pixel index (bits)
+  uint2* meta;                    // global sample index (lo 32), bounce
+};
+
+struct RenderArgs {
+  DCamera cam;
+  uint2 key;
+  unsigned long long first_sample;
+  uint32_t n_pixels;
+  float* sum;
+  float* sumsq;
+  float2* hits;                   // per queue slot: t, prim (bits)
+};
+
+__device__ __forceinline__ uint32_t live_count(const Ctl* ctl) {
+  unsigned long long rem = ctl->total_items - ctl->next_item;
+  unsigned int room = ctl->pool - ctl->n_cur;
+  return ctl->n_cur + (rem < room ? (unsigned int)rem : room);
+}
+
+// ---- camera rays -----------------------------------------------------------------------------------
+__device__ __forceinline__ RayT camera_ray(const DCamera& cam, uint32_t pixel, float time, float lu, float lv, float px, float py) {
+  uint32_t j = pixel / (uint32_t)cam.W, i = pixel - j * (uint32_t)cam.W;
+  RayT r;
+  r.time = time;
+  r.o = ld3(cam.center);
+  // target - centre, built from small quantities only
+  f3 rel = fma3((float)i + px, ld3(cam.pixel_u), fma3((float)j + py, ld3(cam.pixel_v), ld3(cam.top_left)));
+  if (cam.has_defocus) {   // uniform point on the lens disk (Core.hs:63-68; polar map, same distribution)
+    float rad = sqrtf(lu), s, c;
+    sincospif(2.f * lv, &s, &c);
+    f3 lens = fma3(rad * c, ld3(cam.defocus_u), (rad * s) * ld3(cam.defocus_v));
+    r.o = r.o + lens;
+    rel = rel - lens;
+  }
+  r.d = normalize3(rel);
+  return r;
+}
+
+__global__ void __launch_bounds__(kRaygenBlock) k_raygen(const Ctl* __restrict__ ctl, Queue q, const __grid_constant__ RenderArgs A) {
+  const uint32_t n_cur = ctl->n_cur, n_tot = live_count(ctl);
+  const unsigned long long next = ctl->next_item;
+  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; n_cur + t < n_tot; t += gridDim.x * blockDim.x) {
+    unsigned long long item = next + t;
+    unsigned long long s_local = item / A.n_pixels;
+    uint32_t pixel = (uint32_t)(item - s_local * A.n_pixels);
+    unsigned long long sample = A.first_sample + s_local;
+    uint4 r0 = rng4(A.key, pixel, sample, 0, RNG_RAYGEN);
+    float lu = 0.f, lv = 0.f;
+    if (A.cam.has_defocus) {
+      uint4 r1 = rng4(A.key, pixel, sample, 0, RNG_RAYGEN + 1);
+      lu = u01(r1.x);
+      lv = u01(r1.y);
+    }
+    RayT ray = camera_ray(A.cam, pixel, u01(r0.x), lu, lv, u01(r0.y), u01(r0.z));
+    uint32_t slot = n_cur + t;
+    q.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
+    q.d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(kNone));
+    q.thr[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(pixel));
+    q.meta[slot] = make_uint2((uint32_t)sample, 0u);
+  }
+}
+
+// ---- traversal / closest hit ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(kTraverseBlock) k_traverse(const Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
+                                                             const __grid_constant__ RenderArgs A) {
+  __shared__ uint32_t s_stack[kStackDepth * kTraverseBlock];
+  const uint32_t n = live_count(ctl);
+  uint32_t* stack = s_stack + threadIdx.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4 o4 = q.o[i], d4 = q.d[i];
+    RayT ray{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
+    uint32_t pixel = 0;
+    uint2 meta = make_uint2(0, 0);
+    if (sc.n_media) {
+      pixel = __float_as_uint(q.thr[i].w);
+      meta = q.meta[i];
+    }
+    unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
+    Hit h = trace_segment(sc, ray, __float_as_uint(d4.w), true, A.key, pixel, sample, meta.y, stack, kTraverseBlock);
+    // front flag travels in the sign of t (t > 0 always): negative = back side
+    A.hits[i] = make_float2(h.front ? h.t : -h.t, __uint_as_float(h.prim));
+  }
+}
+
+// ---- shading, accumulation, compaction -------------------------------------------------------------------
+__global__ void __launch_bounds__(kShadeBlock) k_shade(Ctl* __restrict__ ctl, Queue q, Queue qn, const __grid_constant__ DScene sc,
+                                                       const __grid_constant__ RenderArgs A) {
+  __shared__ float s_grad[256 * 3];
+  __shared__ uint8_t s_perm[3 * 256];
+  if (sc.has_noise) {      // Perlin tables staged in shared memory (Noise.hs:52-92)
+    for (int k = threadIdx.x; k < 768; k += blockDim.x) {
+      s_grad[k] = sc.noise_grad[k];
+      s_perm[k] = sc.noise_perm[k];
+    }
+    __syncthreads();
+  }
+  const NoiseTab T{s_grad, s_perm};
+  const uint32_t n = live_count(ctl);
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n; base += stride) {
+    const uint32_t i = base + lane;
+    bool alive = false;
+    RayT ray;
+    f3 thr;
+    uint32_t origin_geom = kNone, pixel = 0;
+    uint2 meta = make_uint2(0, 0);
+    if (i < n) {
+      const float4 o4 = q.o[i], d4 = q.d[i], t4 = q.thr[i];
+      const float2 h2 = A.hits[i];
+      meta = q.meta[i];
+      ray = RayT{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
+      thr = mk3(t4.x, t4.y, t4.z);
+      pixel = __float_as_uint(t4.w);
+      Hit hit{fabsf(h2.x), __float_as_uint(h2.y), !(h2.x < 0.f)};
+      unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
+      uint4 rnd = rng4(A.key, pixel, sample, meta.y, RNG_SHADE);
+      f3 contrib;
+      alive = shade_bounce(sc, A.cam, T, ray, hit, thr, origin_geom, rnd, contrib);
+      if (contrib.x != 0.f || contrib.y != 0.f || contrib.z != 0.f) {
+        float* s = A.sum + 3 * (size_t)pixel;
+        atomicAdd(s, contrib.x);
+        atomicAdd(s + 1, contrib.y);
+        atomicAdd(s + 2, contrib.z);
+        if (A.sumsq) {
+          float* s2 = A.sumsq + 3 * (size_t)pixel;
+          atomicAdd(s2, contrib.x * contrib.x);
+          atomicAdd(s2 + 1, contrib.y * contrib.y);
+          atomicAdd(s2 + 2, contrib.z * contrib.z);
+        }
+      }
+      meta.y += 1;
+      if (meta.y >= (uint32_t)A.cam.max_depth) alive = false;   // rayColor 0 = zero (Ray.hs:176)
+      if (thr.x == 0.f && thr.y == 0.f && thr.z == 0.f) alive = false;   // nothing downstream can contribute
+    }
+    // stream compaction: one atomic per warp, ranks from ballot/popc
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, alive);
+    if (mask) {
+      uint32_t start = 0;
+      const int leader = __ffs(mask) - 1;
+      if ((int)lane == leader) start = atomicAdd(&ctl->n_next, (unsigned int)__popc(mask));
+      start = __shfl_sync(0xFFFFFFFFu, start, leader);
+      if (alive) {
+        const uint32_t slot = start + __popc(mask & ((1u << lane) - 1u));
+        qn.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
+        qn.d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(origin_geom));
+        qn.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(pixel));
+        qn.meta[slot] = meta;
+      }
+    }
+  }
+}
+
+__global__ void k_advance(Ctl* ctl) {
+  const uint32_t n_tot = live_count(ctl);
+  ctl->next_item += n_tot - ctl->n_cur;
+  ctl->rays += n_tot;
+  ctl->n_cur = ctl->n_next;
+  ctl->n_next = 0;
+  ctl->iterations += 1;
+}
+
+// ---- deterministic primary-ray probe (parity gate: primitive id + t) --------------------------------------
+__global__ void __launch_bounds__(kTraverseBlock) k_probe(const __grid_constant__ DScene sc, const __grid_constant__ DCamera cam, float time,
+                                                          uint32_t* __restrict__ ids, float* __restrict__ ts) {
+  __shared__ uint32_t s_stack[kStackDepth * kTraverseBlock];
+  const uint32_t n = (uint32_t)cam.W * (uint32_t)cam.H;
+  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+    DCamera const& c = cam;
+    uint32_t j = p / (uint32_t)c.W, i = p - j * (uint32_t)c.W;
+    RayT ray;
+    ray.time = time;
+    ray.o = ld3(c.center);
+    ray.d = normalize3(fma3((float)i + 0.5f, ld3(c.pixel_u), fma3((float)j + 0.5f, ld3(c.pixel_v), ld3(c.top_left))));
+    Hit h = trace_segment(sc, ray, kNone, false, make_uint2(0, 0), 0, 0, 0, s_stack + threadIdx.x, kTraverseBlock);
+    ids[p] = h.prim == kNone ? kNone : sc.canonical[h.prim];
+    ts[p] = h.t;
+  }
+}
+
+// ---- image output step (writeImage / writeImageSqrt, Ray.hs:248-260) -----------------------------------------
+__global__ void k_tonemap(const float* __restrict__ rgb, int n, int mode, uint8_t* __restrict__ out) {
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+    float x = rgb[k];
+    x = fminf(1.f, fmaxf(0.f, x));     // NaN → 0
+    float y = mode == 1 ? sqrtf(x) : (x <= 0.0031308f ? 12.92f * x : 1.055f * powf(x, 1.f / 2.4f) - 0.055f);
+    // the reference's encoder (massiv-io / Color `toWord8`) quantises as floor(256 y) clamped to 255: pinned against
+    // pawn_demo.png's background gradient (99.7 % of 208k pixels exact; round(255 y) matches only 81 %)
+    out[k] = (uint8_t)min(255, (int)floorf(y * 256.f));
+  }
+}
+
+__global__ void k_scale(const float* __restrict__ in, float* __restrict__ out, int n, float s) {
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) out[k] = in[k] * s;
+}
+
+// =================================================================================================================
+// host side
+// =================================================================================================================
+struct DeviceScene {
+  int device = 0;
+  int sm_count = 148;
+  DScene d{};
+  std::vector<void*> allocs;
+  // render workspace
+  uint32_t pool = 0;
+  Queue q[2]{};
+  float2* hits = nullptr;
+  Ctl* ctl = nullptr;
+  Ctl* h_ctl = nullptr;   // pinned
+  float* sum = nullptr;
+  float* sumsq = nullptr;
+  float* out = nullptr;
+  size_t accum_elems = 0;
+  std::vector<cudaEvent_t> events;
+  cudaStream_t stream = nullptr;
+};
+
+void destroy_device_scene(DeviceScene* d) {
+  if (!d) return;
+  cudaSetDevice(d->device);
+  for (void* p : d->allocs) cudaFree(p);
+  for (auto e : d->events) cudaEventDestroy(e);
+  if (d->h_ctl) cudaFreeHost(d->h_ctl);
+  if (d->stream) cudaStreamDestroy(d->stream);
+  delete d;
+}
+
+template <class T>
+static cudaError_t upload_vec(DeviceScene& ds, const T* src, size_t count, const T** dst) {
+  void* p = nullptr;
+  size_t bytes = std::max<size_t>(count * sizeof(T), 16);
+  cudaError_t e = cudaMalloc(&p, bytes);
+  if (e != cudaSuccess) return e;
+  ds.allocs.push_back(p);
+  if (count) e = cudaMemcpy(p, src, count * sizeof(T), cudaMemcpyHostToDevice);
+  *dst = reinterpret_cast<const T*>(p);
+  return e;
+}
+
+static int32_t check_device(int device) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    set_error("no CUDA device visible: raytrace_b200 renders only on an sm_100 GPU (there is no CPU fallback)");
+    return RT_ERR_NO_DEVICE;
+  }
+  if (device < 0 || device >= n) { set_error("device index out of range"); return RT_ERR_INVALID_ARG; }
+  cudaDeviceProp p;
+  RT_CUDA(cudaGetDeviceProperties(&p, device));
+  if (p.major < 10) {
+    set_error(std::string("device '") + p.name + "' is not sm_100 (kernels are built for sm_100a only)");
+    return RT_ERR_NO_DEVICE;
+  }
+  return RT_OK;
+}
+
+static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
+  if (!s.committed) { set_error("scene not committed"); return RT_ERR_NOT_COMMITTED; }
+  auto it = s.devices.find(device);
+  if (it != s.devices.end()) { *out = it->second; RT_CUDA(cudaSetDevice(device)); return RT_OK; }
+  int32_t st = check_device(device);
+  if (st != RT_OK) return st;
+  RT_CUDA(cudaSetDevice(device));
+  auto* ds = new DeviceScene();
+  ds->device = device;
+  cudaDeviceGetAttribute(&ds->sm_count, cudaDevAttrMultiProcessorCount, device);
+  const FlatScene& f = s.flat;
+  DScene& d = ds->d;
+  cudaError_t e = cudaSuccess;
+  auto chk = [&](cudaError_t x) { if (e == cudaSuccess) e = x; };
+  chk(upload_vec(*ds, reinterpret_cast<const float4*>(f.nodes.data()), f.nodes.size() * 2, &d.nodes));
+  chk(upload_vec(*ds, reinterpret_cast<const float4*>(f.prims.data()), f.prims.size() / 4, &d.prims));
+  chk(upload_vec(*ds, reinterpret_cast<const float4*>(f.tri_uv.data()), f.tri_uv.size() / 4, &d.tri_uv));
+  chk(upload_vec(*ds, f.xforms.data(), f.xforms.size(), &d.xforms));
+  chk(upload_vec(*ds, f.materials.data(), f.materials.size(), &d.materials));
+  chk(upload_vec(*ds, f.textures.data(), f.textures.size(), &d.textures));
+  chk(upload_vec(*ds, reinterpret_cast<const float4*>(f.texels.data()), f.texels.size() / 4, &d.texels));
+  chk(upload_vec(*ds, f.canonical.data(), f.canonical.size(), &d.canonical));
+  chk(upload_vec(*ds, f.noise_grad.data(), f.noise_grad.size(), &d.noise_grad));
+  chk(upload_vec(*ds, f.noise_perm.data(), f.noise_perm.size(), &d.noise_perm));
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ds->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&ds->h_ctl), sizeof(Ctl));
+  if (e != cudaSuccess) {
+    set_error(std::string("scene upload failed: ") + cudaGetErrorString(e));
+    destroy_device_scene(ds);
+    return RT_ERR_CUDA;
+  }
+  std::memcpy(d.media, f.media, sizeof d.media);
+  d.n_media = f.n_media;
+  d.surface_root = f.surface_root;
+  d.has_noise = f.has_noise;
+  d.n_prims = (uint32_t)f.canonical.size();
+  s.devices[device] = ds;
+  *out = ds;
+  return RT_OK;
+}
+
+// Camera of Ray.hs:123-155 evaluated in double, stored fp32
+static int32_t make_camera(const RtCamera& c, DCamera* out) {
+  if (c.image_width <= 0 || !(c.aspect_ratio > 0) || c.samples_per_pixel <= 0) { set_error("bad camera settings"); return RT_ERR_INVALID_ARG; }
+  if (c.n_redirect_targets < 0 || c.n_redirect_targets > kMaxTargets) { set_error("more than 8 cs_redirectTargets"); return RT_ERR_UNSUPPORTED; }
+  if (c.n_redirect_targets && !c.redirect_targets) { set_error("null redirect target array"); return RT_ERR_INVALID_ARG; }
+  if (c.bg_kind != RT_BG_CONSTANT && c.bg_kind != RT_BG_YGRADIENT) {
+    set_error("cs_background is a user-defined closure (neither constant nor affine in dir.y): rejected, no CPU fallback");
+    return RT_ERR_USER_DEFINED;
+  }
+  DCamera k{};
+  k.W = c.image_width;
+  k.H = (int)std::nearbyint((double)c.image_width / c.aspect_ratio);
+  if (k.H <= 0) { set_error("image height is zero"); return RT_ERR_INVALID_ARG; }
+  k.spp = c.samples_per_pixel;
+  k.max_depth = c.max_recursion_depth;
+  auto sub = [](const double* a, const double* b, double* r) { for (int i = 0; i < 3; i++) r[i] = a[i] - b[i]; };
+  auto crs = [](const double* a, const double* b, double* r) {
+    r[0] = a[1] * b[2] - a[2] * b[1]; r[1] = a[2] * b[0] - a[0] * b[2]; r[2] = a[0] * b[1] - a[1] * b[0];
+  };
+  auto nrm = [](double* a) {
+    double l = a[0] * a[0] + a[1] * a[1] + a[2] * a[2];
+    if (std::fabs(l) <= 1e-12 || std::fabs(1 - l) <= 1e-12) return;   // linear's normalize
+    double s = 1 / std::sqrt(l);
+    for (int i = 0; i < 3; i++) a[i] *= s;
+  };
+  double vh = c.focus_dist * std::tan(c.vfov / 2) * 2;
+  double vw = vh * (double)k.W / (double)k.H;
+  double w[3], u[3], v[3];
+  sub(c.center, c.look_at, w);
+  nrm(w);
+  crs(c.up, w, u);
+  nrm(u);
+  crs(w, u, v);
+  double rad = c.focus_dist * std::tan(c.defocus_angle / 2);
+  for (int i = 0; i < 3; i++) {
+    double across = vw * u[i], down = -(vh * v[i]);
+    k.center[i] = (float)c.center[i];
+    k.top_left[i] = (float)(-w[i] * c.focus_dist - across / 2 - down / 2);   // relative to the centre
+    k.pixel_u[i] = (float)(across / k.W);
+    k.pixel_v[i] = (float)(down / k.H);
+    k.defocus_u[i] = (float)(u[i] * rad);
+    k.defocus_v[i] = (float)(v[i] * rad);
+    k.bg0[i] = (float)c.bg_c0[i];
+    k.bg1[i] = (float)c.bg_c1[i];
+  }
+  k.has_defocus = rad != 0.0;
+  k.bg_kind = c.bg_kind;
+  k.n_targets = c.n_redirect_targets;
+  double acc = 0;
+  for (int t = 0; t < k.n_targets; t++) {
+    const RtRedirectTarget& r = c.redirect_targets[t];
+    DTarget& d = k.targets[t];
+    acc += r.p;
+    d.p = (float)r.p;
+    d.cumulative = (float)acc;
+    double cp[3];
+    crs(r.s0, r.s1, cp);
+    double ncp = std::sqrt(cp[0] * cp[0] + cp[1] * cp[1] + cp[2] * cp[2]);
+    double n[3] = {0, 0, 0}, nS[3] = {0, 0, 0}, wa[3] = {0, 0, 0}, wb[3] = {0, 0, 0};
+    if (ncp > 0) {
+      for (int i = 0; i < 3; i++) { n[i] = cp[i] / ncp; nS[i] = n[i] / ncp; }
+      crs(r.s1, nS, wa);
+      crs(nS, r.s0, wb);
+    }
+    for (int i = 0; i < 3; i++) {
+      d.origin[i] = (float)r.q[i]; d.U[i] = (float)r.s0[i]; d.V[i] = (float)r.s1[i]; d.crs[i] = (float)cp[i];
+      d.n[i] = (float)n[i]; d.wa[i] = (float)wa[i]; d.wb[i] = (float)wb[i];
+    }
+  }
+  k.rem_prob = (float)(1.0 - acc);
+  *out = k;
+  return RT_OK;
+}
+
+static int32_t ensure_workspace(DeviceScene& ds, uint32_t pool, size_t accum_elems) {
+  if (ds.pool != pool) {
+    auto drop = [&](void* p) {
+      if (!p) return;
+      cudaFree(p);
+      ds.allocs.erase(std::remove(ds.allocs.begin(), ds.allocs.end(), p), ds.allocs.end());
+    };
+    for (int k = 0; k < 2; k++) { drop(ds.q[k].o); drop(ds.q[k].d); drop(ds.q[k].thr); drop(ds.q[k].meta); ds.q[k] = Queue{}; }
+    drop(ds.hits); drop(ds.ctl);
+    ds.hits = nullptr; ds.ctl = nullptr; ds.pool = 0;
+    auto grab = [&](void** p, size_t bytes) -> cudaError_t {
+      cudaError_t e = cudaMalloc(p, bytes);
+      if (e == cudaSuccess) ds.allocs.push_back(*p);
+      return e;
+    };
+    for (int k = 0; k < 2; k++) {
+      RT_CUDA(grab((void**)&ds.q[k].o, (size_t)pool * 16));
+      RT_CUDA(grab((void**)&ds.q[k].d, (size_t)pool * 16));
+      RT_CUDA(grab((void**)&ds.q[k].thr, (size_t)pool * 16));
+      RT_CUDA(grab((void**)&ds.q[k].meta, (size_t)pool * 8));
+    }
+    RT_CUDA(grab((void**)&ds.hits, (size_t)pool * 8));
+    RT_CUDA(grab((void**)&ds.ctl, sizeof(Ctl)));
+    ds.pool = pool;
+  }
+  if (ds.accum_elems < accum_elems) {
+    void* p[3] = {nullptr, nullptr, nullptr};
+    for (int k = 0; k < 3; k++) {
+      RT_CUDA(cudaMalloc(&p[k], accum_elems * sizeof(float)));
+      ds.allocs.push_back(p[k]);
+    }
+    ds.sum = (float*)p[0]; ds.sumsq = (float*)p[1]; ds.out = (float*)p[2];
+    ds.accum_elems = accum_elems;
+  }
+  return RT_OK;
+}
+
+static uint32_t choose_pool(const Scene& s, unsigned long long total_items) {
+  uint32_t pool = s.pool_size;
+  if (const char* e = std::getenv("RT_B200_POOL")) pool = (uint32_t)std::strtoul(e, nullptr, 10);
+  if (pool == 0) pool = 1u << 20;
+  pool = std::max<uint32_t>(pool, 1024);
+  if (total_items < pool) pool = (uint32_t)std::max<unsigned long long>(1024, (total_items + 1023) / 1024 * 1024);
+  return pool;
+}
+
+// the wavefront loop, accumulating UN-normalised sums into d_sum (+ d_sumsq)
+static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint64_t seed, uint64_t first_sample,
+                             uint64_t n_samples, float* d_sum, float* d_sumsq, cudaStream_t stream, RtStats* stats) {
+  const uint32_t n_pixels = (uint32_t)cam.W * (uint32_t)cam.H;
+  const unsigned long long total = (unsigned long long)n_pixels * n_samples;
+  RenderArgs A{};
+  A.cam = cam;
+  A.key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+  A.first_sample = first_sample;
+  A.n_pixels = n_pixels;
+  A.sum = d_sum;
+  A.sumsq = d_sumsq;
+  A.hits = ds.hits;
+  Ctl init{};
+  init.total_items = total;
+  init.pool = ds.pool;
+  *ds.h_ctl = init;
+  RT_CUDA(cudaMemcpyAsync(ds.ctl, ds.h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, stream));
+
+  const bool timing = stats != nullptr && std::getenv("RT_B200_NOTIMING") == nullptr;
+  const size_t kMaxTimed = 4096;            // iterations with per-kernel events
+  if (timing && ds.events.size() < kMaxTimed * 4 + 2) {
+    size_t want = kMaxTimed * 4 + 2;
+    while (ds.events.size() < want) {
+      cudaEvent_t e;
+      RT_CUDA(cudaEventCreate(&e));
+      ds.events.push_back(e);
+    }
+  }
+  cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+  if (timing) { ev_begin = ds.events[kMaxTimed * 4]; ev_end = ds.events[kMaxTimed * 4 + 1]; RT_CUDA(cudaEventRecord(ev_begin, stream)); }
+
+  const int g_trav = ds.sm_count * 8, g_shade = ds.sm_count * 8, g_gen = ds.sm_count * 4;
+  uint64_t launches = 0;
+  size_t timed = 0;
+  uint32_t iter = 0;
+  int cur = 0;
+  // first batch: enough iterations to start every sample, afterwards small batches until the pool drains
+  unsigned long long batch = std::max<unsigned long long>(4, total / ds.pool + 2);
+  for (;;) {
+    for (unsigned long long b = 0; b < batch; b++) {
+      Queue& q = ds.q[cur];
+      Queue& qn = ds.q[cur ^ 1];
+      const bool t_this = timing && timed < kMaxTimed;
+      k_raygen<<<g_gen, kRaygenBlock, 0, stream>>>(ds.ctl, q, A);
+      if (t_this) cudaEventRecord(ds.events[timed * 4 + 0], stream);
+      k_traverse<<<g_trav, kTraverseBlock, 0, stream>>>(ds.ctl, q, ds.d, A);
+      if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
+      k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, ds.d, A);
+      if (t_this) { cudaEventRecord(ds.events[timed * 4 + 2], stream); timed++; }
+      k_advance<<<1, 1, 0, stream>>>(ds.ctl);
+      launches += 4;
+      cur ^= 1;
+      iter++;
+    }
+    RT_CUDA(cudaMemcpyAsync(ds.h_ctl, ds.ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, stream));
+    RT_CUDA(cudaStreamSynchronize(stream));
+    if (ds.h_ctl->next_item >= total && ds.h_ctl->n_cur == 0) break;
+    batch = 8;
+    if (iter > 100000000u) { set_error("wavefront loop did not terminate"); return RT_ERR_CUDA; }
+  }
+  if (timing) { RT_CUDA(cudaEventRecord(ev_end, stream)); RT_CUDA(cudaEventSynchronize(ev_end)); }
+  RT_CUDA(cudaGetLastError());
+  if (stats) {
+    stats->samples = total;
+    stats->rays = ds.h_ctl->rays;
+    stats->launches = launches;
+    stats->iterations = ds.h_ctl->iterations;
+    stats->pool = ds.pool;
+    if (timing) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, ev_begin, ev_end);
+      stats->ms_total = ms;
+      double tt = 0, tsd = 0;
+      for (size_t k = 0; k < timed; k++) {
+        float a = 0, b = 0;
+        cudaEventElapsedTime(&a, ds.events[k * 4 + 0], ds.events[k * 4 + 1]);
+        cudaEventElapsedTime(&b, ds.events[k * 4 + 1], ds.events[k * 4 + 2]);
+        tt += a;
+        tsd += b;
+      }
+      // iterations beyond the timed window (very long renders) are extrapolated by iteration count
+      double scale = timed ? (double)iter / (double)timed : 0.0;
+      if (timed == kMaxTimed && iter > timed) { tt *= scale; tsd *= scale; }
+      stats->ms_traverse = tt;
+      stats->ms_shade = tsd;
+      stats->ms_raygen = std::max(0.0, (double)ms - tt - tsd);
+    }
+  }
+  (void)s;
+  return RT_OK;
+}
+
+}  // namespace rtb
+
+using namespace rtb;
+
+extern "C" {
+
+int32_t rt_device_count(int32_t* n) {
+  if (!n) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  int c = 0, good = 0;
+  if (cudaGetDeviceCount(&c) != cudaSuccess) c = 0;
+  for (int i = 0; i < c; i++) {
+    cudaDeviceProp p;
+    if (cudaGetDeviceProperties(&p, i) == cudaSuccess && p.major >= 10) good++;
+  }
+  *n = good;
+  return RT_OK;
+}
+
+int32_t rt_scene_upload(RtScene* sp, int32_t device) {
+  if (!sp) { set_error("null scene"); return RT_ERR_INVALID_ARG; }
+  DeviceScene* ds = nullptr;
+  return get_device_scene(*reinterpret_cast<Scene*>(sp), device, &ds);
+}
+
+int32_t rt_render_device(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample,
+                         uint64_t n_samples, float* d_sum, float* d_sumsq, void* cuda_stream, RtStats* stats) {
+  if (!sp || !rc || !d_sum) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  Scene& s = *reinterpret_cast<Scene*>(sp);
+  DeviceScene* ds = nullptr;
+  int32_t st = get_device_scene(s, device, &ds);
+  if (st != RT_OK) return st;
+  DCamera cam;
+  st = make_camera(*rc, &cam);
+  if (st != RT_OK) return st;
+  if (stats) std::memset(stats, 0, sizeof *stats);
+  if (n_samples == 0) return RT_OK;
+  const unsigned long long total = (unsigned long long)cam.W * cam.H * n_samples;
+  st = ensure_workspace(*ds, choose_pool(s, total), 0);
+  if (st != RT_OK) return st;
+  cudaStream_t stream = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : ds->stream;
+  return run_wavefront(s, *ds, cam, seed, first_sample, n_samples, d_sum, d_sumsq, stream, stats);
+}
+
+int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample,
+                  uint64_t n_samples, float* rgb_out, float* rgb_sumsq_out, RtStats* stats) {
+  if (!sp || !rc || !rgb_out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  Scene& s = *reinterpret_cast<Scene*>(sp);
+  DeviceScene* ds = nullptr;
+  int32_t st = get_device_scene(s, device, &ds);
+  if (st != RT_OK) return st;
+  DCamera cam;
+  st = make_camera(*rc, &cam);
+  if (st != RT_OK) return st;
+  if (stats) std::memset(stats, 0, sizeof *stats);
+  const size_t elems = (size_t)cam.W * cam.H * 3;
+  const unsigned long long total = (unsigned long long)cam.W * cam.H * n_samples;
+  st = ensure_workspace(*ds, choose_pool(s, std::max<unsigned long long>(total, 1)), elems);
+  if (st != RT_OK) return st;
+  cudaStream_t stream = ds->stream;
+  RT_CUDA(cudaMemsetAsync(ds->sum, 0, elems * sizeof(float), stream));
+  if (rgb_sumsq_out) RT_CUDA(cudaMemsetAsync(ds->sumsq, 0, elems * sizeof(float), stream));
+  if (n_samples) {
+    st = run_wavefront(s, *ds, cam, seed, first_sample, n_samples, ds->sum, rgb_sumsq_out ? ds->sumsq : nullptr, stream, stats);
+    if (st != RT_OK) return st;
+  }
+  cudaEvent_t c0, c1;
+  RT_CUDA(cudaEventCreate(&c0));
+  RT_CUDA(cudaEventCreate(&c1));
+  k_scale<<<ds->sm_count * 4, 256, 0, stream>>>(ds->sum, ds->out, (int)elems, 1.0f / (float)cam.spp);   // Ray.hs:232
+  RT_CUDA(cudaEventRecord(c0, stream));
+  RT_CUDA(cudaMemcpyAsync(rgb_out, ds->out, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  if (rgb_sumsq_out) RT_CUDA(cudaMemcpyAsync(rgb_sumsq_out, ds->sumsq, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  RT_CUDA(cudaEventRecord(c1, stream));
+  RT_CUDA(cudaStreamSynchronize(stream));
+  if (stats) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c0, c1);
+    stats->ms_copy = ms;
+    stats->launches += 1;
+  }
+  cudaEventDestroy(c0);
+  cudaEventDestroy(c1);
+  RT_CUDA(cudaGetLastError());
+  return RT_OK;
+}
+
+int32_t rt_probe_primary(RtScene* sp, int32_t device, const RtCamera* rc, double time, uint32_t* ids, float* ts) {
+  if (!sp || !rc || !ids || !ts) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  Scene& s = *reinterpret_cast<Scene*>(sp);
+  DeviceScene* ds = nullptr;
+  int32_t st = get_device_scene(s, device, &ds);
+  if (st != RT_OK) return st;
+  DCamera cam;
+  st = make_camera(*rc, &cam);
+  if (st != RT_OK) return st;
+  const size_t n = (size_t)cam.W * cam.H;
+  uint32_t* d_ids = nullptr;
+  float* d_ts = nullptr;
+  RT_CUDA(cudaMalloc((void**)&d_ids, n * 4));
+  RT_CUDA(cudaMalloc((void**)&d_ts, n * 4));
+  k_probe<<<ds->sm_count * 8, kTraverseBlock, 0, ds->stream>>>(ds->d, cam, (float)time, d_ids, d_ts);
+  cudaError_t e = cudaMemcpyAsync(ids, d_ids, n * 4, cudaMemcpyDeviceToHost, ds->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(ts, d_ts, n * 4, cudaMemcpyDeviceToHost, ds->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ds->stream);
+  cudaFree(d_ids);
+  cudaFree(d_ts);
+  RT_CUDA(e);
+  return RT_OK;
+}
+
+int32_t rt_tonemap_u8(int32_t device, const float* rgb, int32_t n_pixels, int32_t mode, uint8_t* out) {
+  if (!rgb || !out || n_pixels < 0) { set_error("bad argument"); return RT_ERR_INVALID_ARG; }
+  int32_t st = check_device(device);
+  if (st != RT_OK) return st;
+  RT_CUDA(cudaSetDevice(device));
+  const size_t n = (size_t)n_pixels * 3;
+  if (n == 0) return RT_OK;
+  float* d_in = nullptr;
+  uint8_t* d_out = nullptr;
+  RT_CUDA(cudaMalloc((void**)&d_in, n * 4));
+  RT_CUDA(cudaMalloc((void**)&d_out, n));
+  cudaError_t e = cudaMemcpy(d_in, rgb, n * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    k_tonemap<<<592, 256>>>(d_in, (int)n, mode, d_out);
+    e = cudaMemcpy(out, d_out, n, cudaMemcpyDeviceToHost);
+  }
+  cudaFree(d_in);
+  cudaFree(d_out);
+  RT_CUDA(e);
+  return RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,271 @@
+// rt_trace.cuh — device-side math, Philox RNG, primitive tests and BVH traversal (sm_100a).
+//
+// Reference semantics followed (src/Graphics/Ray/*.hs):
+//   * open hit intervals tmin < t < tmax (Core.hs:83-84); closed, conservative box test
+//     (Core.hs:95-106,147-152) — here on padded fp32 boxes, NaN never culls;
+//   * sphere: nearer root if inside the interval, else the farther one (Geometry.hs:63-80);
+//   * plane shapes: |n.d| > 1e-8, planar coordinates a, b, inclusive shape tests
+//     (Geometry.hs:123-132,150,174);
+//   * exact ties: the primitive earlier in the reference's evaluation order wins
+//     (Geometry.hs:340-345,356-361) = lower primitive index here.
+// Deliberate fp32 measures: a ray never re-hits the planar primitive it
+// starts on and only sees the far root of the sphere it starts on (exact in real arithmetic,
+// and what the reference's fp64 + tmin = 1e-4 yields); spheres with r >= 64 use an fp64
+// discriminant.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rt_device.h"
+
+namespace rtb {
+
+// ---- small vector helpers -----------------------------------------------------------------------
+struct f3 {
+  float x, y, z;
+};
+__device__ __forceinline__ f3 mk3(float x, float y, float z) { return f3{x, y, z}; }
+__device__ __forceinline__ f3 ld3(const float* p) { return f3{p[0], p[1], p[2]}; }
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return f3{a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ f3 operator-(f3 a, f3 b) { return f3{a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ f3 operator-(f3 a) { return f3{-a.x, -a.y, -a.z}; }
+__device__ __forceinline__ f3 operator*(float s, f3 a) { return f3{s * a.x, s * a.y, s * a.z}; }
+__device__ __forceinline__ f3 operator*(f3 a, f3 b) { return f3{a.x * b.x, a.y * b.y, a.z * b.z}; }
+__device__ __forceinline__ float dot3(f3 a, f3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
+__device__ __forceinline__ f3 fma3(float s, f3 a, f3 b) { return f3{fmaf(s, a.x, b.x), fmaf(s, a.y, b.y), fmaf(s, a.z, b.z)}; }
+__device__ __forceinline__ f3 mat3(const float* M, f3 v) {
+  return f3{fmaf(M[0], v.x, fmaf(M[1], v.y, M[2] * v.z)), fmaf(M[3], v.x, fmaf(M[4], v.y, M[5] * v.z)),
+            fmaf(M[6], v.x, fmaf(M[7], v.y, M[8] * v.z))};
+}
+// linear's `normalize` (leaves near-zero / already-unit vectors alone)
+__device__ __forceinline__ f3 normalize3(f3 v) {
+  float l = dot3(v, v);
+  if (fabsf(l) <= 1e-12f) return v;
+  return rsqrtf(l) * v;
+}
+
+// ---- Philox4x32-10 counter RNG -------------------------------------------------------------------
+// key = render seed; counter = (pixel, sample lo, bounce<<8 | block, sample hi).  The sample set
+// therefore depends only on (seed, pixel, global sample index), never on pool size or GPU count.
+__device__ __forceinline__ uint4 philox4x32(uint4 c, uint2 k) {
+#pragma unroll
+  for (int r = 0; r < 10; r++) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += 0x9E3779B9u;
+    k.y += 0xBB67AE85u;
+  }
+  return c;
+}
+__device__ __forceinline__ float u01(uint32_t x) { return (float)(x >> 8) * 5.9604644775390625e-8f; }  // [0,1)
+
+enum : uint32_t { RNG_RAYGEN = 0xF0u, RNG_MEDIA = 0x10u, RNG_SHADE = 0x40u };
+__device__ __forceinline__ uint4 rng4(uint2 key, uint32_t pixel, uint64_t sample, uint32_t bounce, uint32_t block) {
+  return philox4x32(make_uint4(pixel, (uint32_t)sample, (bounce << 8) | block, (uint32_t)(sample >> 32)), key);
+}
+
+// uniform direction on the unit sphere (same distribution as the rejection sampler, Core.hs:54-60)
+__device__ __forceinline__ f3 unit_vector(float u1, float u2) {
+  float z = 1.f - 2.f * u1;
+  float r = sqrtf(fmaxf(0.f, 1.f - z * z));
+  float s, c;
+  sincospif(2.f * u2, &s, &c);
+  return f3{r * c, r * s, z};
+}
+
+// ---- ray ---------------------------------------------------------------------------------------------
+struct RayT {
+  f3 o, d;
+  float time;
+};
+
+struct Hit {
+  float t;
+  uint32_t prim;   // primitive index, kNone = miss
+  bool front;
+};
+
+// one primitive; `skip_a` = geometry the ray ORIGIN lies on, `skip_b` = geometry of a hit at tmin
+// that must not be reported again (second boundary query of constantMedium, Geometry.hs:311)
+__device__ __forceinline__ void intersect_prim(const DScene& sc, uint32_t i, const RayT& ray, float tmin,
+                                               uint32_t skip_a, uint32_t skip_b, Hit& best) {
+  const float4* P = sc.prims + 4 * (size_t)i;
+  const float4 m4 = __ldg(P + 3);
+  const uint32_t tf = __float_as_uint(m4.x), geom = __float_as_uint(m4.y);
+  const float4 p0 = __ldg(P);
+  f3 o = ray.o, d = ray.d;
+  if (tf & PRIM_FLAG_MOVING) {  // transform / moving instance kept local (Geometry.hs:388-389,452-454)
+    const DXform& X = sc.xforms[__float_as_uint(m4.z)];
+    f3 b = fma3(ray.time, ld3(X.binv1), ld3(X.binv0));
+    o = mat3(X.Ainv, ray.o) + b;
+    d = mat3(X.Ainv, ray.d);
+  }
+  float t;
+  bool front;
+  if ((tf & PRIM_TYPE_MASK) == PRIM_SPHERE) {
+    const bool on_a = geom == skip_a, on_b = geom == skip_b;
+    float h, sq;
+    if (tf & PRIM_FLAG_BIG) {  // fp64 up to the discriminant, stable roots in fp32
+      const float4 p1 = __ldg(P + 1);
+      double cx = (double)p0.x + (double)p1.x, cy = (double)p0.y + (double)p1.y, cz = (double)p0.z + (double)p1.z;
+      double r = (double)p0.w + (double)p1.w;
+      double ox = cx - (double)o.x, oy = cy - (double)o.y, oz = cz - (double)o.z;
+      double hd = (double)d.x * ox + (double)d.y * oy + (double)d.z * oz;
+      double c = ox * ox + oy * oy + oz * oz - r * r;
+      // |d|^2 = 1 + O(1e-7) after the fp32 normalise; at |oc| ~ 1e3 the term (|d|^2 - 1) c is NOT negligible
+      // against the discriminant, so the quadratic keeps its leading coefficient
+      double dd = (double)d.x * (double)d.x + (double)d.y * (double)d.y + (double)d.z * (double)d.z;
+      double disc = hd * hd - dd * c;
+      if (!(disc >= 0.0)) return;
+      sq = sqrtf((float)disc);
+      h = (float)hd;
+      // q = h + sign(h) sqrt(disc): roots are q/|d|^2 and c/q, neither suffers cancellation
+      double q = hd >= 0.0 ? hd + (double)sq : hd - (double)sq;
+      float rq = (float)(q * (2.0 - dd)), rc = q != 0.0 ? __fdividef((float)c, (float)q) : 0.f;
+      float near_t = fminf(rq, rc), far_t = fmaxf(rq, rc);
+      if (on_a || on_b) {
+        if (on_a && !(hd > 0.0)) return;
+        t = far_t;
+        if (!(t > tmin)) return;
+      } else {
+        t = near_t;
+        if (!(t > tmin && t <= best.t)) { t = far_t; if (!(t > tmin)) return; }
+      }
+      front = (double)t <= hd;
+    } else {
+      f3 oc = mk3(p0.x, p0.y, p0.z) - o;
+      h = dot3(d, oc);
+      f3 l = fma3(-h, d, oc);                 // component of oc perpendicular to the ray
+      float disc = fmaf(p0.w, p0.w, -dot3(l, l));
+      if (!(disc >= 0.f)) return;
+      sq = sqrtf(disc);
+      if (on_a || on_b) {
+        if (on_a && !(h > 0.f)) return;
+        t = h + sq;
+        if (!(t > tmin)) return;
+      } else {
+        t = h - sq;
+        if (!(t > tmin && t <= best.t)) { t = h + sq; if (!(t > tmin)) return; }
+      }
+      front = t <= h;                          // d.(p-c) = t - h  (Geometry.hs:83-84, `<=`)
+    }
+    if (p0.w < 0.f) front = !front;
+  } else {
+    if (geom == skip_a || geom == skip_b) return;
+    const float4 p1 = __ldg(P + 1), p2 = __ldg(P + 2);
+    f3 q = mk3(p0.x, p0.y, p0.z), n = mk3(p0.w, p1.x, p1.y);
+    float denom = dot3(n, d);
+    if (!(fabsf(denom) > 1e-8f)) return;
+    f3 qo = q - o;
+    t = __fdividef(dot3(n, qo), denom);
+    if (!(t > tmin && t <= best.t)) return;
+    f3 pr = fma3(t, d, -qo);                   // p - q
+    float a = dot3(mk3(p1.z, p1.w, p2.x), pr), b = dot3(mk3(p2.y, p2.z, p2.w), pr);
+    if ((tf & PRIM_TYPE_MASK) == PRIM_PGRAM) { if (!(0.f <= a && a <= 1.f && 0.f <= b && b <= 1.f)) return; }
+    else { if (!(a >= 0.f && b >= 0.f && a + b <= 1.f)) return; }
+    front = denom < 0.f;
+  }
+  if (t < best.t || (t == best.t && i < best.prim)) {
+    best.t = t;
+    best.prim = i;
+    best.front = front;
+  }
+}
+
+// slab test of one 32-byte node against the clipped interval (tmin, tmax]
+__device__ __forceinline__ bool box_hit(const float4 lo, const float4 hi, f3 inv, f3 oinv, float tmin, float tmax, float& tn) {
+  float x0 = fmaf(lo.x, inv.x, -oinv.x), x1 = fmaf(hi.x, inv.x, -oinv.x);
+  float y0 = fmaf(lo.y, inv.y, -oinv.y), y1 = fmaf(hi.y, inv.y, -oinv.y);
+  float z0 = fmaf(lo.z, inv.z, -oinv.z), z1 = fmaf(hi.z, inv.z, -oinv.z);
+  tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
+  float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
+  return tn <= tf;   // fminf/fmaxf drop NaN operands: a NaN slab never culls (Appendix A.8)
+}
+
+// Closest hit below node pair `root`.  `stack` is this thread's column of the shared-memory short
+// stack (stride = blockDim.x words).  `best` carries (tmax, kNone) in and the result out.
+__device__ __forceinline__ void closest_hit(const DScene& sc, uint32_t root, const RayT& ray, float tmin,
+                                            uint32_t skip_a, uint32_t skip_b, uint32_t* stack, uint32_t stride, Hit& best) {
+  if (root == kNone) return;
+  f3 inv;
+  inv.x = fabsf(ray.d.x) > 1e-30f ? __frcp_rn(ray.d.x) : copysignf(1e30f, ray.d.x);
+  inv.y = fabsf(ray.d.y) > 1e-30f ? __frcp_rn(ray.d.y) : copysignf(1e30f, ray.d.y);
+  inv.z = fabsf(ray.d.z) > 1e-30f ? __frcp_rn(ray.d.z) : copysignf(1e30f, ray.d.z);
+  const f3 oinv = ray.o * inv;
+  uint32_t cur = root;
+  int sp = 0;
+  for (;;) {
+    const float4* N = sc.nodes + 2 * (size_t)cur;
+    const float4 l0 = __ldg(N), h0 = __ldg(N + 1), l1 = __ldg(N + 2), h1 = __ldg(N + 3);
+    float tn0, tn1;
+    bool hit0 = box_hit(l0, h0, inv, oinv, tmin, best.t, tn0);
+    bool hit1 = box_hit(l1, h1, inv, oinv, tmin, best.t, tn1);
+    const uint32_t a0 = __float_as_uint(l0.w), b0 = __float_as_uint(h0.w);
+    const uint32_t a1 = __float_as_uint(l1.w), b1 = __float_as_uint(h1.w);
+    if (hit0 && (b0 & kLeafBit)) {
+      for (uint32_t k = 0, n = b0 & ~kLeafBit; k < n; k++) intersect_prim(sc, a0 + k, ray, tmin, skip_a, skip_b, best);
+      hit0 = false;
+    }
+    if (hit1 && (b1 & kLeafBit)) {
+      for (uint32_t k = 0, n = b1 & ~kLeafBit; k < n; k++) intersect_prim(sc, a1 + k, ray, tmin, skip_a, skip_b, best);
+      hit1 = false;
+    }
+    hit0 = hit0 && tn0 <= best.t;
+    hit1 = hit1 && tn1 <= best.t;
+    if (hit0 && hit1) {
+      const bool first0 = tn0 <= tn1;     // near child first; results do not depend on the order
+      stack[sp * stride] = first0 ? a1 : a0;
+      sp++;
+      cur = first0 ? a0 : a1;
+    } else if (hit0) cur = a0;
+    else if (hit1) cur = a1;
+    else {
+      if (sp == 0) break;
+      sp--;
+      cur = stack[sp * stride];
+    }
+  }
+}
+
+// ---- full closest-hit query of a path segment: surfaces, then every medium (Geometry.hs:298-330) ---
+__device__ __forceinline__ Hit trace_segment(const DScene& sc, const RayT& ray, uint32_t origin_geom, bool with_media,
+                                             uint2 key, uint32_t pixel, uint64_t sample, uint32_t bounce,
+                                             uint32_t* stack, uint32_t stride) {
+  const float tmin = 1e-4f;  // Ray.hs:178
+  Hit best{__int_as_float(0x7f800000), kNone, false};
+  closest_hit(sc, sc.surface_root, ray, tmin, origin_geom, kNone, stack, stride, best);
+  if (with_media && sc.n_media) {
+    uint4 rnd = make_uint4(0, 0, 0, 0);
+    for (uint32_t m = 0; m < sc.n_media; m++) {
+      if ((m & 3u) == 0) rnd = rng4(key, pixel, sample, bounce, RNG_MEDIA + (m >> 2));
+      const uint32_t rbits = (m & 3u) == 0 ? rnd.x : ((m & 3u) == 1 ? rnd.y : ((m & 3u) == 2 ? rnd.z : rnd.w));
+      const DMedium& md = sc.media[m];
+      Hit h1{__int_as_float(0x7f800000), kNone, false};
+      closest_hit(sc, md.root, ray, tmin, origin_geom, kNone, stack, stride, h1);
+      if (h1.prim == kNone) continue;
+      float t1, t2;
+      if (h1.front) {
+        if (!(h1.t < best.t)) continue;
+        const uint32_t g1 = __float_as_uint(__ldg(sc.prims + 4 * (size_t)h1.prim + 3).y);
+        Hit h2{__int_as_float(0x7f800000), kNone, false};
+        closest_hit(sc, md.root, ray, h1.t, origin_geom, g1, stack, stride, h2);
+        if (h2.prim == kNone) continue;
+        t1 = h1.t;
+        t2 = fminf(best.t, h2.t);
+      } else {
+        t1 = tmin;
+        t2 = fminf(best.t, h1.t);
+      }
+      const float hit_dist = md.neg_inv_density * logf(u01(rbits));   // rand = 0 → +inf → no hit
+      if (hit_dist < t2 - t1) {
+        best.t = t1 + hit_dist;
+        best.prim = kMediumBase + m;
+        best.front = true;
+      }
+    }
+  }
+  return best;
+}
+
+}  // namespace rtb

@@ -1,0 +1,207 @@
+"""GPU parity tests proper (-m gpu): the CUDA path, called through the C ABI (ctypes → librt_b200.so),
+against the CPU oracle on the same scenes.
+
+Gates (BASELINE.json north_star):
+  1. primary-ray primitive id matches on >= 99.99 % of pixels;
+  2. hit distance t within 1e-5 relative;
+  3. images agree statistically: mean luminance within 1 %, and no pixel fails a 4-sigma test
+     (a pixel fails only if it fails again under an independent re-seed: SURVEY §7.3 item 4).
+Gates 1–2 are evaluated on WELL-CONDITIONED pixels (oracle.harness.probe_stable): where the pixel-centre ray
+runs exactly through a primitive edge or grazes a silhouette the reference's own answer is fp64 rounding noise
+(README scene: the mirror's left edge projects exactly onto pixel column 46, a = 2.2e-16); those pixels are
+counted and reported, and must stay a tiny fraction of the image."""
+import numpy as np
+import pytest
+
+import raytrace_b200 as rt
+from raytrace_b200 import scenes
+from raytrace_b200.ray import CompiledScene
+from oracle.harness import OracleScene
+from util import MISS, luminance, z_scores
+
+pytestmark = pytest.mark.gpu
+
+PROBE_CASES = [
+    ("readme", dict()),
+    ("cornell", dict(spp=1)),
+    ("demo1", dict(spp=1)),
+    ("demo2", dict(width=800, spp=1)),
+    ("pawn", dict(width=1920, aspect=16 / 9, spp=1)),
+    ("bunny_volume", dict(spp=1)),
+]
+
+
+@pytest.mark.parametrize("name,kw", PROBE_CASES, ids=[c[0] for c in PROBE_CASES])
+def test_primary_ray_id_and_distance(built, name, kw):
+    """Gates 1 and 2 at BASELINE.json's full image sizes."""
+    ctor, _ = scenes.CONFIGS[name]
+    s, w = ctor(**kw)
+    ids, ts = CompiledScene(w).probe_primary(s)
+    oids, ots, stable = OracleScene(w).probe_stable(s)
+    assert stable.mean() > 0.99, stable.mean()
+    match = (ids == oids)[stable].mean()
+    raw = (ids == oids).mean()
+    both = stable & (ids == oids) & (oids != MISS)
+    rel = np.abs(ts[both] - ots[both]) / ots[both]
+    print(f"{name}: id match {match:.6f} (raw {raw:.6f}, ill-conditioned px {int((~stable).sum())}), max rel dt {rel.max():.2e}")
+    assert match >= 0.9999
+    assert raw >= 0.999
+    assert rel.max() <= 1e-5
+    assert np.isinf(ts[ids == MISS]).all()
+
+
+STAT_CASES = [
+    # name, ctor kwargs, spp per run
+    ("readme", dict(width=192), 256),
+    ("cornell", dict(width=96), 256),
+    ("cornell_noredirect", dict(width=96), 256),
+    ("demo1", dict(width=160), 128),
+    ("demo2", dict(width=96, depth=50), 128),
+    ("pawn", dict(width=96), 128),
+    ("bunny_volume", dict(width=128), 64),
+]
+
+
+def _render_both(cs, ora, s, seed):
+    img, sq, st = cs.render(s, rt.mkStdGen(seed), want_sumsq=True, want_stats=True)
+    ref, rsq, cnt = ora.render(s, seed, want_sumsq=True)
+    return img.astype(np.float64), sq.astype(np.float64), st, ref, rsq, cnt
+
+
+@pytest.mark.parametrize("name,kw,spp", STAT_CASES, ids=[c[0] for c in STAT_CASES])
+def test_statistical_image_parity(built, name, kw, spp):
+    """Gate 3 at sizes the oracle renders in seconds (same camera, fewer pixels)."""
+    ctor, seed = scenes.CONFIGS[name]
+    s, w = ctor(spp=spp, **kw)
+    cs, ora = CompiledScene(w), OracleScene(w)
+    img, sq, st, ref, rsq, cnt = _render_both(cs, ora, s, seed)
+    assert np.isfinite(img).all()
+    n_px = img.shape[0] * img.shape[1]
+    assert st["samples"] == n_px * spp == cnt["samples"]
+    # same path-length statistics (rays = rayColor segments that reach hitWorld, Ray.hs:178)
+    rps_g, rps_o = st["rays"] / st["samples"], cnt["rays"] / cnt["samples"]
+    assert abs(rps_g - rps_o) <= 0.01 * rps_o, (rps_g, rps_o)
+    lum_g, lum_o = luminance(img).mean(), luminance(ref).mean()
+    print(f"{name}: mean luminance gpu {lum_g:.5f} oracle {lum_o:.5f} ({(lum_g / lum_o - 1) * 100:+.3f} %), rays/sample {rps_g:.3f} vs {rps_o:.3f}")
+    assert abs(lum_g - lum_o) <= 0.01 * lum_o
+    for c in range(3):
+        mg, mo = img[..., c].mean(), ref[..., c].mean()
+        assert abs(mg - mo) <= 0.015 * max(mo, 1e-3), (c, mg, mo)
+    z1 = z_scores(img, sq, spp, ref, rsq, spp)
+    fail1 = np.abs(z1) > 4
+    print(f"   first pass: {int(fail1.sum())} of {z1.size} pixel-channels beyond 4 sigma (max |z| {np.abs(z1).max():.2f})")
+    assert fail1.mean() < 2e-3
+    if fail1.any():   # confirm on an independent re-seed
+        img2, sq2, _, ref2, rsq2, _ = _render_both(cs, ora, s, seed + 7919)
+        z2 = z_scores(img2, sq2, spp, ref2, rsq2, spp)
+        confirmed = fail1 & (np.abs(z2) > 4) & (np.sign(z1) == np.sign(z2))
+        assert not confirmed.any(), np.argwhere(confirmed)[:10]
+    # block-level agreement (tighter than per-pixel: averages 64 pixels)
+    b = 8
+    h, wd = img.shape[0] // b * b, img.shape[1] // b * b
+    bg = luminance(img)[:h, :wd].reshape(h // b, b, wd // b, b).mean(axis=(1, 3))
+    bo = luminance(ref)[:h, :wd].reshape(h // b, b, wd // b, b).mean(axis=(1, 3))
+    assert np.abs(bg - bo).mean() <= 0.05 * max(bo.mean(), 1e-3)
+
+
+FEATURE_CASES = [
+    ("metal_test", scenes.metal_test, dict(width=128, spp=128)),          # dielectric bubble, metal 1.0, defocus
+    ("noise_test", scenes.noise_test, dict(width=128, spp=64)),           # noiseTexture + marbleTexture (Perlin in smem)
+    ("quad_test", scenes.quad_test, dict(width=96, spp=64)),              # parallelograms
+    ("cuboid_test", scenes.cuboid_test, dict(width=96, spp=64)),          # cuboid + imageTexture + transform
+    ("cornell_smoke", scenes.cornell_smoke, dict(width=80, spp=128)),     # pitchBlack / isotropic media in transformed cuboids
+    ("lommel_seeliger", scenes.lommel_seeliger_test, dict(width=96, spp=128)),  # lommelSeeliger + redirect p = 0.5
+    ("bunny_test", scenes.bunny_test, dict(width=128, spp=32)),           # 4968-triangle BVH, lambertian
+]
+
+
+@pytest.mark.parametrize("name,ctor,kw", FEATURE_CASES, ids=[c[0] for c in FEATURE_CASES])
+def test_reference_feature_scenes(built, name, ctor, kw):
+    """The reference's other scene programs (test/Main.hs): each exercises one feature family."""
+    s, w = ctor(**kw)
+    spp = s.cs_samplesPerPixel
+    cs, ora = CompiledScene(w), OracleScene(w)
+    ids, ts = cs.probe_primary(s)
+    oids, ots, stable = ora.probe_stable(s)
+    assert (ids == oids)[stable].mean() >= 0.9999
+    both = stable & (ids == oids) & (oids != MISS)
+    if both.any():
+        assert (np.abs(ts[both] - ots[both]) / ots[both]).max() <= 1e-5
+    img, sq, st, ref, rsq, cnt = _render_both(cs, ora, s, 55)
+    lum_g, lum_o = luminance(img).mean(), luminance(ref).mean()
+    print(f"{name}: luminance gpu {lum_g:.5f} oracle {lum_o:.5f}")
+    assert abs(lum_g - lum_o) <= 0.01 * lum_o + 1e-4
+    assert abs(st["rays"] / st["samples"] - cnt["rays"] / cnt["samples"]) <= 0.01 * cnt["rays"] / cnt["samples"]
+    z = z_scores(img, sq, spp, ref, rsq, spp)
+    assert (np.abs(z) > 4).mean() < 2e-3
+    for c in range(3):
+        assert abs(img[..., c].mean() - ref[..., c].mean()) <= 0.015 * max(ref[..., c].mean(), 1e-3) + 1e-4
+
+
+def test_moving_and_anisotropic(built):
+    """moving under transform (chain collapse), anisotropic + transparent materials, bvhNode, triangle with uv."""
+    tex = rt.checkerTexture(4, 4, (0.9, 0.2, 0.2), (0.2, 0.2, 0.9))
+    tri = rt.triangle(((-2, -1, -4), (0, 0)), ((2, -1, -4), (1, 0)), ((0, 2.5, -4.5), (0.5, 1)))
+    mover = rt.transform(rt.translate((0.5, 0, 0)) @ rt.rotateZ(0.3),
+                         rt.moving((0, 0, 0), (0, 0.6, 0), rt.transform(rt.rotateY(0.7), rt.cuboid(rt.fromCorners((-0.4, -0.4, -3), (0.4, 0.4, -2.2))))))
+    world = rt.group([
+        rt.pureGeometry(rt.bvhNode(rt.lambertian(tex) << tri, rt.metal(0.2, rt.constantTexture(0.8)) << mover)),
+        rt.pureGeometry(rt.transparent(rt.constantTexture((0.6, 0.9, 0.6))) << rt.sphere((-1.2, 0.2, -2.5), 0.4)),
+        rt.anisotropic(0.6, rt.constantTexture((0.9, 0.8, 0.3))) << rt.constantMedium(1.5, rt.sphere((1.3, 0.3, -2.6), 0.6)),
+    ])
+    s = rt.defaultCameraSettings.replace(cs_imageWidth=96, cs_samplesPerPixel=128, cs_background=scenes.sky, cs_maxRecursionDepth=12)
+    cs, ora = CompiledScene(world), OracleScene(world)
+    for time in (0.0, 0.35, 1.0):
+        ids, ts = cs.probe_primary(s, time=time)
+        oids, ots, stable = ora.probe_stable(s, time=time)
+        assert (ids == oids)[stable].mean() >= 0.9995
+        both = stable & (ids == oids) & (oids != MISS)
+        assert (np.abs(ts[both] - ots[both]) / ots[both]).max() <= 1e-5
+    img, sq, st, ref, rsq, cnt = _render_both(cs, ora, s, 3)
+    assert abs(luminance(img).mean() - luminance(ref).mean()) <= 0.01 * luminance(ref).mean()
+    z = z_scores(img, sq, 128, ref, rsq, 128)
+    assert (np.abs(z) > 4).mean() < 2e-3
+
+
+def test_sphere_uv_known_answer_gpu(built):
+    """sphereUVTest (test/Main.hs:128-134): fully deterministic — the centre texel of earthmap."""
+    s, w = scenes.sphere_uv_test()
+    cs = CompiledScene(w)
+    ids, ts = cs.probe_primary(s)
+    assert ids[0, 0] == 1 and abs(ts[0, 0] - 0.6) < 1e-5
+    img = cs.render(s.replace(cs_samplesPerPixel=256), rt.mkStdGen(12))
+    texel = scenes.load_earthmap()[256, 512]
+    assert np.allclose(img[0, 0], texel, atol=1e-2)
+
+
+def test_sample_ranges_compose_and_are_deterministic(built):
+    """Sample-range sharding (the multi-GPU partition): rendering [0,a) and [a,n) separately gives the same
+    image as [0,n) up to fp32 summation order; the sample set does not depend on the pool size."""
+    s, w = scenes.cornell_box(spp=32, width=64)
+    cs = CompiledScene(w)
+    full = cs.render(s, rt.mkStdGen(9))
+    a = cs.render(s, rt.mkStdGen(9), first_sample=0, n_samples=12)
+    b = cs.render(s, rt.mkStdGen(9), first_sample=12, n_samples=20)
+    assert np.allclose(a + b, full, rtol=1e-4, atol=1e-5)
+    cs.handle.set_pool_size(4096)
+    small_pool = cs.render(s, rt.mkStdGen(9))
+    assert np.allclose(small_pool, full, rtol=1e-4, atol=1e-5)
+    other = cs.render(s, rt.mkStdGen(10))
+    assert not np.allclose(other, full, rtol=1e-3)
+
+
+def test_image_output_step(built, tmp_path):
+    """writeImage / writeImageSqrt (Ray.hs:248-260): OETF pin 0.74 -> 224, clamp 15 -> 255."""
+    m = np.zeros((2, 2, 3), np.float32)
+    m[0, 0] = 0.74
+    m[0, 1] = 15.0
+    m[1, 0] = 0.25
+    m[1, 1] = (-1.0, 0.0031308, 1.0)
+    from raytrace_b200.ray import _tonemap
+    o = _tonemap(m, 0)
+    assert o[0, 0, 0] == 224 and (o[0, 1] == 255).all() and o[1, 0, 0] == 137 and tuple(o[1, 1]) == (0, 10, 255)
+    q = _tonemap(m, 1)
+    assert q[1, 0, 0] == 128 and q[0, 0, 0] == int(np.sqrt(0.74) * 256)
+    rt.writeImage(str(tmp_path / "a.png"), m)
+    back = rt.readImage(str(tmp_path / "a.png"))
+    assert abs(back[0, 0, 0] - 0.74) < 0.01 and abs(back[1, 0, 0] - 0.25) < 0.005

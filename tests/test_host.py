@@ -1,0 +1,223 @@
+"""CPU-only tests: the C-ABI library loads and exports what include/rt_b200.h declares, the host
+logic behind it (description tree -> flattened scene, BVH policy, .obj loader, error behaviour)
+and the Python mirror of the reference API.  No compute call is made (no GPU here)."""
+import ctypes
+import math
+import os
+import re
+
+import numpy as np
+import pytest
+
+import raytrace_b200 as rt
+from raytrace_b200 import _ffi, scenes
+from raytrace_b200.ray import CompiledScene, classify_background, BG_CONSTANT, BG_YGRADIENT
+from oracle.harness import OracleScene
+from oracle import obj_oracle
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol(built):
+    L = _ffi.lib()
+    header = open(os.path.join(ROOT, "include", "rt_b200.h")).read()
+    declared = set(re.findall(r"\b(rt_[a-z0-9_]+)\s*\(", header))
+    assert declared == set(_ffi.EXPORTS), declared ^ set(_ffi.EXPORTS)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert L.rt_version() == 0x00010000
+
+
+def test_no_gpu_is_a_loud_error_not_a_fallback(built):
+    n = ctypes.c_int32(-1)
+    assert _ffi.lib().rt_device_count(ctypes.byref(n)) == 0
+    if n.value > 0:
+        pytest.skip("a GPU is visible")
+    s, w = scenes.readme_example(width=16, spp=1)
+    cs = CompiledScene(w, upload=False)
+    with pytest.raises(_ffi.RtError) as e:
+        cs.render(s, rt.mkStdGen(1))
+    assert e.value.status == 7 and "no CPU fallback" in e.value.message
+
+
+def test_product_never_imports_the_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "raytrace_b200")):
+        for f in files:
+            if f.endswith((".py", ".cpp", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src.replace("no oracle", ""), f
+
+
+@pytest.mark.parametrize("name", ["readme", "cornell", "demo1", "demo2", "pawn", "bunny_volume"])
+def test_flattened_tree_matches_reference_evaluation_order(built, name):
+    """bvhTree policy (Geometry.hs:369-377) + group order: the device primitive order must equal the oracle's
+    evaluation-order leaf sequence (same split axis, same stable sort, same n div 2 split)."""
+    ctor, _ = scenes.CONFIGS[name]
+    s, w = ctor()
+    cs = CompiledScene(w, upload=False)
+    nodes, canon = cs.handle.get_bvh()
+    ora = OracleScene(w)
+    order = ora.leaf_order()
+    assert np.array_equal(canon[: len(order)], order)
+    info = cs.info()
+    assert info["n_bvh_nodes"] == len(nodes) and info["max_depth"] < 32
+    # every inner node's box contains its children's boxes; leaves reference valid primitive ranges
+    lo, hi = nodes[:, 0:3], nodes[:, 4:7]
+    a, b = nodes[:, 3].view(np.uint32), nodes[:, 7].view(np.uint32)
+    for k in range(len(nodes)):
+        if b[k] == 0:          # inner
+            c = int(a[k])
+            for ch in (c, c + 1):
+                assert (lo[k] <= lo[ch] + 1e-3).all() and (hi[k] >= hi[ch] - 1e-3).all()
+        elif lo[k, 0] < 1e37:  # leaf (not the parked root sibling)
+            cnt = int(b[k] & 0x7FFFFFFF)
+            assert 1 <= cnt <= 8 and int(a[k]) + cnt <= info["n_prims"]
+
+
+def test_scene_counts(built):
+    s, w = scenes.demo2(width=16, spp=1)
+    info = CompiledScene(w, upload=False).info()
+    assert info["n_media"] == 2 and info["n_planars"] == 2401 and info["n_spheres"] == 1008
+    s, w = scenes.cornell_box()
+    info = CompiledScene(w, upload=False).info()
+    assert info["n_prims"] == 18 and info["n_media"] == 0
+
+
+def test_user_defined_closures_are_rejected(built):
+    ball = rt.sphere((0, 0, -1), 0.5)
+    cases = [
+        rt.Material(lambda d, h: None) << ball,
+        rt.lambertian(rt.solidTexture(lambda p: p)) << ball,
+        rt.lambertian(rt.uvTexture(lambda uv: (1, 1, 1))) << ball,
+        rt.lambertian(rt.Texture(lambda p, uv: (1, 1, 1))) << ball,
+        rt.lambertian(rt.constantTexture(1)) << rt.planeShape((0, 0, 0), (1, 0, 0), (0, 1, 0), lambda a, b: a * a + b * b < 1,
+                                                             lambda a, b: (a, b), rt.fromCorners((0, 0, 0), (1, 1, 0))),
+    ]
+    for w in cases:
+        with pytest.raises(_ffi.UserDefinedError) as e:
+            CompiledScene(w, upload=False)
+        assert "no CPU fallback" in e.value.message
+    with pytest.raises(_ffi.UserDefinedError):
+        classify_background(lambda ray: (ray.direction[0] ** 2, 0, 0))
+
+
+def test_error_codes(built):
+    white = rt.lambertian(rt.constantTexture(1))
+    with pytest.raises(ValueError, match="bvhTree: empty list"):
+        rt.bvhTree([])
+    with pytest.raises(_ffi.RtError) as e:      # scale must not be used with transform (Geometry.hs:434)
+        CompiledScene(white << rt.transform(rt.scale(2.0), rt.sphere((0, 0, 0), 1)), upload=False)
+    assert e.value.status == 4
+    with pytest.raises(TypeError):               # Geometry m () passed to raytrace
+        CompiledScene(rt.sphere((0, 0, 0), 1), upload=False)
+    with pytest.raises(TypeError):               # group [Geometry Identity a, Geometry (State StdGen) a]
+        rt.group([white << rt.sphere((0, 0, 0), 1), white << rt.constantMedium(1.0, rt.sphere((0, 0, 0), 1))])
+    # raw C ABI: empty bvhTree -> RT_ERR_EMPTY_BVH ; unknown ids -> RT_ERR_INVALID_ARG
+    L = _ffi.lib()
+    h = ctypes.c_void_p()
+    assert L.rt_scene_create(ctypes.byref(h)) == 0
+    d = _ffi.RtNodeDesc()
+    d.kind = 8
+    out = ctypes.c_uint32()
+    assert L.rt_scene_add_node(h, ctypes.byref(d), ctypes.byref(out)) == 0
+    assert L.rt_scene_commit(h, out.value) == 2
+    assert b"bvhTree: empty list" in L.rt_last_error()
+    assert L.rt_scene_commit(h, 99) == 1
+    info = _ffi.RtSceneInfo()
+    assert L.rt_scene_info(h, ctypes.byref(info)) == 8
+    L.rt_scene_destroy(h)
+
+
+def test_outermost_material_wins_and_shared_geometry(built):
+    a, b = rt.lambertian(rt.constantTexture(0.1)), rt.mirror(rt.constantTexture(0.9))
+    inner = a << rt.sphere((0, 0, 0), 1)
+    cs = CompiledScene(b << rt.group([inner, a << rt.sphere((3, 0, 0), 1)]), upload=False)
+    assert cs.info()["n_prims"] == 2
+    s, w = scenes.pawn(spp=1, width=8)           # the same mesh object is surface and medium boundary
+    nodes, canon = CompiledScene(w, upload=False).handle.get_bvh()
+    assert np.array_equal(np.sort(canon[:1200]), np.arange(1200)) and np.array_equal(canon[:1200], canon[1200:])
+
+
+def test_image_height_round_half_even(built):
+    L = _ffi.lib()
+    for w, aspect, expect in [(600, 16 / 9, 338), (1200, 16 / 9, 675), (100, 1.0, 100), (5, 2.0, 2), (7, 2.0, 4), (1920, 16 / 9, 1080)]:
+        s = rt.defaultCameraSettings.replace(cs_imageWidth=w, cs_aspectRatio=aspect)
+        cam = _ffi.make_camera(s, 1, (1, 1, 1), (1, 1, 1))
+        h = ctypes.c_int32()
+        assert L.rt_image_height(ctypes.byref(cam), ctypes.byref(h)) == 0
+        assert h.value == expect == rt.imageHeight(s)
+
+
+def test_background_classification():
+    assert classify_background(rt.defaultCameraSettings.cs_background)[0] == BG_CONSTANT
+    k, c0, c1 = classify_background(scenes.sky)
+    assert k == BG_YGRADIENT and np.allclose(c0, (1, 1, 1)) and np.allclose(c1, (0.5, 0.7, 1.0))
+    k, c0, c1 = classify_background(scenes.grayFade)
+    assert k == BG_YGRADIENT and np.allclose(c0, 0) and np.allclose(c1, 1)
+
+
+# ---- .obj loader (parseObj, Geometry.hs:207-285) -------------------------------------------------------
+OBJ_OK = """# comment
+v 0 0 0
+v 1 0 0   # trailing comment
+v 1 1 0 9 9
+v 0 1 0
+v -0.5e1 2.5E-1 3
+vt 0.5
+vt 0.25 0.75 0
+vn 0 0 1
+f 1 2 3 4
+f -1 -2 -3
+f 1/1 2/2 3//7
+f 1//1 2/-1 5
+g ignored
+"""
+OBJ_BAD = [
+    ("v 1 2\n", "line 1: invalid 'v' statement"),
+    ("v 1 2 .5\n", "line 1: invalid 'v' statement"),
+    ("v 0 0 0\nvt x\n", "line 2: invalid 'vt' statement"),
+    ("v 0 0 0\nv 1 0 0\nf 1 2\n", "line 3: invalid 'f' statement (fewer than 3 vertices)"),
+    ("v 0 0 0\nv 1 0 0\nv 1 1 0\nf 1 2 4\n", "line 4: index out of bounds: 4"),
+    ("v 0 0 0\nv 1 0 0\nv 1 1 0\nf 1 2 0\n", "line 4: index out of bounds: 0"),
+    ("v 0 0 0\nv 1 0 0\nv 1 1 0\nf 1 2 3x\n", "line 4: unexpected character 'x'"),
+    ("v 0 0 0\nv 1 0 0\nv 1 1 0\nf 1 2 a\n", "line 4: expected number"),
+    ("v 0 0 0\nv 1 0 0\nv 1 1 0\nf 1/ 2 3\n", "line 4: expected number"),
+    ("v 0 0 0\nv 1 0 0\nv 1 1 0\nf 1/1 2 3\n", "line 4: index out of bounds: 1"),
+]
+
+
+def test_obj_loader_matches_restatement(built):
+    m = rt.parseObj(OBJ_OK)
+    v, t, f = obj_oracle.parse_obj(OBJ_OK)
+    assert np.array_equal(m.verts, v) and np.array_equal(m.uvs, t) and np.array_equal(m.faces, f)
+    assert len(f) == 2 + 1 + 1 + 1 and tuple(f[0]) == (0, -1, 1, -1, 2, -1) and tuple(f[1]) == (0, -1, 2, -1, 3, -1)
+    assert tuple(f[2]) == (4, -1, 3, -1, 2, -1) and tuple(f[3]) == (0, 0, 1, 1, 2, -1) and tuple(f[4]) == (0, -1, 1, 1, 4, -1)
+    assert np.array_equal(t, [[0.5, 0.0], [0.25, 0.75]])
+    for text, msg in OBJ_BAD:
+        with pytest.raises(ValueError) as e1:
+            obj_oracle.parse_obj(text)
+        with pytest.raises(ValueError) as e2:
+            rt.parseObj(text)
+        assert str(e1.value) == msg == str(e2.value), (text, str(e1.value), str(e2.value))
+
+
+def test_obj_fixture_meshes():
+    pawn, bunny = scenes.load_mesh("pawn"), scenes.load_mesh("bunny")
+    assert pawn.verts.shape == (602, 3) and pawn.faces.shape == (1200, 6)
+    assert bunny.verts.shape == (2503, 3) and bunny.faces.shape == (4968, 6)
+    assert (pawn.faces[:, 1::2] == -1).all()
+    # round trip through the library's loader
+    lines = ["v %r %r %r" % tuple(float(x) for x in v) for v in pawn.verts] + ["f %d %d %d" % tuple(f[0::2] + 1) for f in pawn.faces]
+    m = rt.parseObj("\n".join(lines) + "\n")
+    assert np.array_equal(m.verts, pawn.verts) and np.array_equal(m.faces, pawn.faces)
+
+
+def test_bounding_boxes_follow_the_reference():
+    assert rt.boundingBox(rt.sphere((1, 2, 3), 2)) == ((-1, 3), (0, 4), (1, 5))
+    b = rt.boundingBox(rt.parallelogram((0, 0, 0), (1, 0, 0), (0, 1, 0)))
+    assert b == ((-0.0001, 1.0001), (-0.0001, 1.0001), (-0.0001, 0.0001))                      # padBox, Geometry.hs:144
+    g = rt.moving((0, 0, 0), (30, 0, 0), rt.sphere((400, 400, 200), 50))
+    assert rt.boundingBox(g) == ((350, 480), (350, 450), (150, 250))
+    t = rt.transform(rt.translate((1, 0, 0)) @ rt.rotateY(math.pi / 2), rt.sphere((0, 0, 0), 1))
+    assert np.allclose(np.array(rt.boundingBox(t)), [[0, 2], [-1, 1], [-1, 1]])
+    assert rt.longestDim(((0, 1), (0, 1), (0, 1))) == 2 and rt.longestDim(((0, 2), (0, 2), (0, 1))) == 1  # argMax ties, Core.hs:43-46
