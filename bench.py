@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the path-tracing hot path (BASELINE.json metric: Msamples/s).
+
+A "step" = one complete render of the workload (default: BASELINE configs[1], the Cornell box 600x600 at
+200 spp, depth 50, with cs_redirectTargets) through librt_b200.so.  With N GPUs the samples per pixel are
+split across ranks (strong scaling; scene replicated) and one NCCL reduce assembles the image.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--scene NAME] [--impl reference]
+  torchrun ... bench.py --gpus N ...            (one rank per GPU)
+
+Prints ONE JSON line on rank 0.  `value` = whole-job Msamples/s with the scene resident in HBM;
+`e2e` = the same metric through the public API with host buffers (scene commit + upload, render, image
+read-back inside the timed region); `roofline` = the traversal kernel against the measured HBM peak using
+SURVEY §8(d)'s algorithmic bytes per ray; `cpu_baseline` = the CPU oracle (a C++ port of the reference's
+algorithm; the Haskell reference cannot be built here) on all host cores, on a bounded sample.
+`--impl reference` times that CPU oracle as the reference arm.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (scene key in raytrace_b200.scenes.CONFIGS, ctor kwargs, description)
+    "cornell": ("cornell", dict(), "cornell_box_600x600_200spp_depth50_redirect"),
+    "cornell_noredirect": ("cornell_noredirect", dict(), "cornell_box_600x600_200spp_depth50_noredirect"),
+    "readme": ("readme", dict(), "readme_example_600x338_50spp_depth10"),
+    "demo1": ("demo1", dict(), "demo1_1200x675_500spp_depth50"),
+    "demo2": ("demo2", dict(), "demo2_800x800_250spp_depth50"),
+    "pawn": ("pawn", dict(width=1920, aspect=16 / 9, spp=1024), "pawn_1920x1080_1024spp_depth20"),
+    "bunny_volume": ("bunny_volume", dict(), "bunny_volume_1920x1080_1024spp_depth20"),
+}
+CPU_SAMPLE_SPP = {"cornell": 32, "cornell_noredirect": 16, "readme": 200, "demo1": 16, "demo2": 8, "pawn": 4, "bunny_volume": 4}
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f).get("hbm_gbs", 6650.0), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[k] for r in self.rows if len(r) >= 6 for k in range(4) if r[2 + k].lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def split_samples(spp: int, world: int, rank: int):
+    """Sample-range sharding: rank r renders global sample indices [first, first+count) of every
+    pixel; a remainder is spread over the first ranks.  The union over ranks is [0, spp) for any world size."""
+    base, rem = divmod(spp, world)
+    count = base + (1 if rank < rem else 0)
+    first = rank * base + min(rank, rem)
+    return first, count
+
+
+def cpu_oracle_rate(world_desc, settings, seed, spp, threads=0):
+    from oracle.harness import OracleScene
+    ora = OracleScene(world_desc)
+    _, cnt = ora.render(settings, seed, spp=spp, threads=threads)
+    return cnt
+
+
+def run_reference(args, rank, world_size):
+    """Reference arm: the reference's algorithm on the host cores (CPU oracle port; no GHC here)."""
+    if rank != 0:
+        return
+    from raytrace_b200 import scenes
+    key, kw, desc = WORKLOADS[args.scene]
+    ctor, seed = scenes.CONFIGS[key]
+    settings, world = ctor(**kw)
+    spp = CPU_SAMPLE_SPP[args.scene]
+    from oracle.harness import OracleScene
+    ora = OracleScene(world)
+    for _ in range(args.warmup):
+        ora.render(settings, seed, spp=max(1, spp // 8))
+    secs, samples, cnt = 0.0, 0, None
+    for k in range(args.steps):
+        _, cnt = ora.render(settings, seed + k, spp=spp)
+        secs += cnt["seconds"]
+        samples += cnt["samples"]
+    value = samples / secs / 1e6
+    line = {
+        "impl": "reference", "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "note": "CPU oracle (C++ port of the Haskell reference; GHC absent), all host threads"},
+        "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": cnt["threads"], "kind": "port",
+                         "sample": f"{spp} of {settings.cs_samplesPerPixel} spp per step, full resolution"},
+        "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "mrays_per_s": cnt["rays"] / cnt["seconds"] / 1e6,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--scene", default="cornell", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world_size)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from raytrace_b200 import scenes, mkStdGen
+    from raytrace_b200.ray import CompiledScene, imageHeight
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    distributed = world_size > 1
+    if distributed:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    key, kw, desc = WORKLOADS[args.scene]
+    ctor, seed = scenes.CONFIGS[key]
+    settings, world = ctor(**kw)
+    W, H, spp = settings.cs_imageWidth, imageHeight(settings), settings.cs_samplesPerPixel
+    first, count = split_samples(spp, world_size, rank)
+    total_samples = W * H * spp
+
+    cs = CompiledScene(world, device=local_rank)           # commit + upload once: scene resident in HBM
+    stream = torch.cuda.current_stream(dev)
+    acc = torch.zeros(H * W * 3, dtype=torch.float32, device=dev)
+    out_host = torch.empty(H * W * 3, dtype=torch.float32).pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def one_step(step_seed):
+        """device-resident step: render this rank's sample range, reduce to rank 0, normalise."""
+        acc.zero_()
+        st = cs.render_device(settings, mkStdGen(step_seed), first, count, acc.data_ptr(), 0, stream.cuda_stream)
+        if distributed:
+            dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
+        if rank == 0:
+            acc.mul_(1.0 / spp)
+        return st
+
+    for k in range(args.warmup):
+        one_step(seed + 1000 + k)
+    barrier()
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    step_ms, stats = [], []
+    barrier()
+    t_wall0 = time.perf_counter()
+    for k in range(args.steps):
+        flush.fill_(k & 0xFF)                                # flush L2 between timed iterations (outside the events)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if distributed:
+            dist.barrier()
+        e0.record(stream)
+        st = one_step(seed + k)
+        e1.record(stream)
+        e1.synchronize()
+        step_ms.append(e0.elapsed_time(e1))
+        stats.append(st)
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop() if rank == 0 else None
+
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+    if distributed:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)      # max over ranks
+    total_ms = float(total_ms.item())
+    lum = float(acc.mean().item()) if rank == 0 else 0.0
+
+    # ---- e2e: public API with HOST buffers; scene commit + upload + render + image read-back per step ----
+    e2e_ms = []
+    h2d = 0
+    for k in range(max(1, min(args.steps, 3))):
+        barrier()
+        t0 = time.perf_counter()
+        cs2 = CompiledScene(world, device=local_rank)       # host description -> flatten -> H2D
+        h2d = cs2.info()["device_bytes"]
+        if not distributed:
+            img = cs2.render(settings, mkStdGen(seed + 77 + k))   # rt_render: D2H of the normalised image inside
+        else:
+            acc.zero_()
+            cs2.render_device(settings, mkStdGen(seed + 77 + k), first, count, acc.data_ptr(), 0, stream.cuda_stream)
+            dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                acc.mul_(1.0 / spp)
+                out_host.copy_(acc, non_blocking=True)
+            torch.cuda.synchronize(dev)
+        dt = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
+        if distributed:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e_ms.append(float(dt.item()))
+        del cs2
+
+    if rank != 0:
+        if distributed:
+            dist.destroy_process_group()
+        return
+
+    ms_per_step = total_ms / args.steps
+    value = total_samples / (ms_per_step * 1e-3) / 1e6
+    rays = sum(s["rays"] for s in stats)
+    trav_ms = sum(s["ms_traverse"] for s in stats)
+    shade_ms = sum(s["ms_shade"] for s in stats)
+    iters = sum(s["iterations"] for s in stats)
+    launches = sum(s["launches"] for s in stats)
+
+    # ---- CPU baseline + the oracle's traversal counters (they define the algorithmic bytes per ray) ----
+    cpu = None
+    bytes_per_ray = None
+    if not args.no_cpu_baseline:
+        cspp = CPU_SAMPLE_SPP[args.scene]
+        cnt = cpu_oracle_rate(world, settings, seed, cspp)
+        n_node, n_sph, n_pl = (cnt[k] / cnt["rays"] for k in ("box_tests", "sphere_tests", "planar_tests"))
+        bytes_per_ray = 32 * n_node + 16 * n_sph + 48 * n_pl + 128
+        cpu = {"value": cnt["samples"] / cnt["seconds"] / 1e6, "unit": "Msamples/s", "cores": cnt["threads"], "kind": "port",
+               "sample": f"{cspp} of {spp} spp, full resolution ({cnt['samples']} samples, {cnt['seconds']:.2f} s)",
+               "mrays_per_s": cnt["rays"] / cnt["seconds"] / 1e6, "rays_per_sample": cnt["rays"] / cnt["samples"],
+               "tests_per_ray": {"box": n_node, "sphere": n_sph, "planar": n_pl}}
+    peak, peak_kind = load_peaks()
+    roof = None
+    if bytes_per_ray is not None and trav_ms > 0:
+        achieved = rays * bytes_per_ray / (trav_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "k_traverse", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
+                "bytes_per_ray_algorithmic": bytes_per_ray, "avg_launch_ms": trav_ms / max(iters, 1),
+                "rays_per_launch": rays / max(iters, 1),
+                "note": "algorithmic bytes = SURVEY 8(d): 32*N_node + 16*N_sphere + 48*N_planar + 128 with the "
+                        "reference's per-ray test counts (oracle counters); scene data is L1/L2 resident, so this is "
+                        "a rate of algorithmic work, not DRAM traffic"}
+    e2e_val = total_samples / (statistics.median(e2e_ms) * 1e-3) / 1e6
+    line = {
+        "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world_size, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "image": [W, H], "spp": spp, "max_depth": settings.cs_maxRecursionDepth,
+                   "parallelism": f"sample-sharded x{world_size}" if distributed else "single GPU",
+                   "l2": "256 MiB flush between timed steps", "pool": stats[-1]["pool"]},
+        "mrays_per_s": rays / (total_ms * 1e-3) / 1e6 * (world_size if distributed else 1),
+        "rays_per_sample": rays / (count * W * H * args.steps),
+        "kernel_ms_per_step": {"traverse": trav_ms / args.steps, "shade": shade_ms / args.steps,
+                               "iterations": iters / args.steps},
+        "gpu_launches": int(launches),
+        "e2e": {"value": e2e_val, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": W * H * 3 * 4,
+                "ms_per_step": statistics.median(e2e_ms)},
+        "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
+        "mean_radiance": lum, "wall_s": t_wall,
+    }
+    print(json.dumps(line), flush=True)
+    if distributed:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -3,8 +3,9 @@
 //
 // Layout summary (DESIGN.md §"Data layout in HBM"):
 //   nodes   : 32-byte BVH nodes, 2 x float4 {lo.xyz, a} {hi.xyz, b}; siblings adjacent (one 64 B
-//             fetch tests both children).  inner: a = index of first child, b = 0;
-//             leaf : a = first primitive, b = kLeafBit | primitive count.
+//             fetch tests both children).  a = node reference: inner → index of the pair holding its children;
+//             leaf → kLeafBit | first primitive << 3 | (count - 1).  b = primitive count (leaf) or 0.
+//             Roots are bare references (no node, no box test of their own, as in the reference).
 //   prims   : 64-byte records, 4 x float4; index order = the reference's evaluation order
 //             (group: list order, Geometry.hs:340-345; bvhNode: left first, :356-361), so
 //             "lower index wins an exact tie" reproduces the reference's tie rules.
@@ -34,6 +35,9 @@ constexpr uint32_t PRIM_TYPE_MASK = 3u;
 constexpr uint32_t PRIM_FLAG_BIG = 4u;      // large-radius sphere: fp64 discriminant
 constexpr uint32_t PRIM_FLAG_MOVING = 8u;   // stays in local space; ray is mapped by xform(time)
 constexpr uint32_t PRIM_FLAG_UVXFORM = 16u; // sphere under a rotation: uv needs the local normal
+
+// scene feature bits: which code the traversal kernel must contain (template specialisation)
+constexpr uint32_t TF_SPHERE = 1u, TF_PLANAR = 2u, TF_MOVING = 4u, TF_MEDIA = 8u;
 
 struct DNode {  // 32 bytes
   float lo[3];
@@ -66,7 +70,7 @@ struct DTexture {   // Texture.hs
 
 struct DMedium {    // constantMedium, Geometry.hs:298-330
   float neg_inv_density;
-  uint32_t root;        // node pair index of the boundary tree
+  uint32_t root;        // node reference of the boundary tree
   uint32_t material;
   uint32_t geom_lo, geom_hi;  // geom-id range of the boundary primitives (dense ids)
 };
@@ -103,7 +107,7 @@ struct DScene {     // device pointers of one uploaded scene
   const uint8_t* noise_perm;   // 3*256
   DMedium media[kMaxMedia];
   uint32_t n_media;
-  uint32_t surface_root;       // node pair index or kNone
+  uint32_t surface_root;       // node reference or kNone
   uint32_t has_noise;
   uint32_t n_prims;
 };

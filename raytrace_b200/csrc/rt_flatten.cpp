@@ -18,6 +18,7 @@
 //     exact tie" equals the reference's tie rules (earlier child / left child wins).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <limits>
@@ -503,7 +504,7 @@ struct Builder {
   }
 
   // ---- device-shaped tree --------------------------------------------------------------------------------
-  static constexpr uint32_t kLeafMax = 8;
+  uint32_t kLeafMax = 8;     // RT_B200_LEAF overrides (tuning knob; <= 8 by the 3-bit count field)
   bool all_single_leaves(const RNode& n) const {
     for (int c : n.children) if (rnodes[c].kind != RNode::LEAF) return false;
     return true;
@@ -564,24 +565,22 @@ struct Builder {
     double pad = 1e-5 * m + 1e-6;  // slab test runs in fp32: keep boxes conservative
     for (int k = 0; k < 3; k++) { d.lo[k] = round_down(h.box.lo[k] - pad); d.hi[k] = round_up(h.box.hi[k] + pad); }
   }
-  // emit the pair (l, r) at nodes[at], nodes[at+1]; r < 0 → never-hit dummy
-  uint32_t emit_pair(FlatScene& fs, int l, int r, uint32_t depth, uint32_t& max_depth) {
+  // Node reference: leaf → kLeafBit | first << 3 | (count - 1); inner → index of the node PAIR holding its two
+  // children (siblings adjacent: one 64-byte fetch tests both).  A root has no node of its own: like the
+  // reference, the top-level geometry's own box is never tested.
+  uint32_t emit_ref(FlatScene& fs, int hn, uint32_t depth, uint32_t& max_depth) {
+    const HNode h = hnodes[hn];
+    max_depth = std::max(max_depth, depth);
+    if (h.left < 0) return kLeafBit | (h.first << 3) | (h.count - 1);
     uint32_t at = (uint32_t)fs.nodes.size();
     fs.nodes.emplace_back();
     fs.nodes.emplace_back();
-    max_depth = std::max(max_depth, depth);
-    int ids[2] = {l, r};
+    int ids[2] = {h.left, h.right};
     for (int k = 0; k < 2; k++) {
       DNode d;
-      if (ids[k] < 0) {  // sibling slot of a root: a leaf with zero primitives, parked far away
-        for (int j = 0; j < 3; j++) { d.lo[j] = 3.0e38f; d.hi[j] = 3.0e38f; }
-        d.a = 0; d.b = kLeafBit;
-      } else {
-        const HNode h = hnodes[ids[k]];
-        write_node(d, h);
-        if (h.left >= 0) { d.b = 0; d.a = emit_pair(fs, h.left, h.right, depth + 1, max_depth); }
-        else { d.a = h.first; d.b = kLeafBit | h.count; }
-      }
+      write_node(d, hnodes[ids[k]]);
+      d.a = emit_ref(fs, ids[k], depth + 1, max_depth);
+      d.b = hnodes[ids[k]].left < 0 ? hnodes[ids[k]].count : 0;
       fs.nodes[at + k] = d;
     }
     return at;
@@ -704,6 +703,7 @@ void default_noise_tables(int32_t perm[3][256], double grad[256][3]) {
 int32_t flatten_scene(Scene& sc, uint32_t root) {
   try {
     Builder b(sc);
+    if (const char* e = std::getenv("RT_B200_LEAF")) b.kLeafMax = std::min<uint32_t>(8, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
     b.mat_used.assign(sc.materials.size(), 0);
     b.tex_used.assign(sc.textures.size(), 0);
     XfState id;
@@ -717,13 +717,13 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
     uint32_t max_depth = 0;
     if (surf >= 0) {
       int h = b.to_device(surf);
-      fs.surface_root = b.emit_pair(fs, h, -1, 1, max_depth);
+      fs.surface_root = b.emit_ref(fs, h, 0, max_depth);
     }
     for (size_t i = 0; i < b.media.size(); i++) {
       int h = b.to_device(b.media[i].rtree);
       DMedium& dm = fs.media[i];
       dm.neg_inv_density = (float)(-(1.0 / b.media[i].density));
-      dm.root = b.emit_pair(fs, h, -1, 1, max_depth);
+      dm.root = b.emit_ref(fs, h, 0, max_depth);
       dm.material = b.media[i].material;
       dm.geom_lo = dm.geom_hi = 0;
     }
@@ -732,6 +732,13 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
     if (max_depth + 1 > (uint32_t)kStackDepth)
       b.fail(RT_ERR_UNSUPPORTED, "flattened BVH is deeper than the shared-memory traversal stack (32 levels)");
     b.pack_prims(fs);
+    if (fs.canonical.size() >= (1u << 28)) b.fail(RT_ERR_UNSUPPORTED, "more than 2^28 primitives");
+    for (const HPrim& p : b.prims) {
+      if (p.index == kNone) continue;
+      fs.features |= (p.type == PRIM_SPHERE) ? TF_SPHERE : TF_PLANAR;
+      if (p.flags & PRIM_FLAG_MOVING) fs.features |= TF_MOVING;
+    }
+    if (!b.media.empty()) fs.features |= TF_MEDIA;
 
     fs.xforms.resize(b.xforms.size());
     for (size_t i = 0; i < b.xforms.size(); i++) {

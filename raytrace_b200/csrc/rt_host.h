@@ -50,6 +50,7 @@ struct FlatScene {
   uint32_t has_noise = 0;
   uint32_t n_spheres = 0, n_planars = 0;
   uint32_t max_depth = 0;
+  uint32_t features = 0;       // TF_* bits: selects the kernel specialisation
   uint64_t bytes() const;
 };
 

@@ -112,6 +112,9 @@ __global__ void __launch_bounds__(kRaygenBlock) k_raygen(const Ctl* __restrict__
 }
 
 // ---- traversal / closest hit ---------------------------------------------------------------------------
+// F = scene feature bits (TF_*): one specialisation per combination that occurs (sphere-only, planar-only,
+// mixed; with / without media; a catch-all with moving instances), chosen at launch from FlatScene::features.
+template <uint32_t F>
 __global__ void __launch_bounds__(kTraverseBlock) k_traverse(const Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
                                                              const __grid_constant__ RenderArgs A) {
   __shared__ uint32_t s_stack[kStackDepth * kTraverseBlock];
@@ -122,14 +125,28 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse(const Ctl* __restri
     RayT ray{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
     uint32_t pixel = 0;
     uint2 meta = make_uint2(0, 0);
-    if (sc.n_media) {
+    if constexpr ((F & TF_MEDIA) != 0) {
       pixel = __float_as_uint(q.thr[i].w);
       meta = q.meta[i];
     }
     unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
-    Hit h = trace_segment(sc, ray, __float_as_uint(d4.w), true, A.key, pixel, sample, meta.y, stack, kTraverseBlock);
+    Hit h = trace_segment<F>(sc, ray, __float_as_uint(d4.w), true, A.key, pixel, sample, meta.y, stack, kTraverseBlock);
     // front flag travels in the sign of t (t > 0 always): negative = back side
     A.hits[i] = make_float2(h.front ? h.t : -h.t, __uint_as_float(h.prim));
+  }
+}
+
+using TraverseFn = void (*)(const Ctl*, Queue, const DScene, const RenderArgs);
+static TraverseFn pick_traverse(uint32_t features) {
+  if (features & TF_MOVING) return k_traverse<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_MEDIA>;
+  switch (features & (TF_SPHERE | TF_PLANAR | TF_MEDIA)) {
+    case TF_SPHERE: return k_traverse<TF_SPHERE>;
+    case TF_PLANAR: return k_traverse<TF_PLANAR>;
+    case TF_SPHERE | TF_PLANAR: return k_traverse<TF_SPHERE | TF_PLANAR>;
+    case TF_SPHERE | TF_MEDIA: return k_traverse<TF_SPHERE | TF_MEDIA>;
+    case TF_PLANAR | TF_MEDIA: return k_traverse<TF_PLANAR | TF_MEDIA>;
+    case TF_SPHERE | TF_PLANAR | TF_MEDIA: return k_traverse<TF_SPHERE | TF_PLANAR | TF_MEDIA>;
+    default: return k_traverse<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_MEDIA>;
   }
 }
 
@@ -223,7 +240,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_probe(const __grid_constant_
     ray.time = time;
     ray.o = ld3(c.center);
     ray.d = normalize3(fma3((float)i + 0.5f, ld3(c.pixel_u), fma3((float)j + 0.5f, ld3(c.pixel_v), ld3(c.top_left))));
-    Hit h = trace_segment(sc, ray, kNone, false, make_uint2(0, 0), 0, 0, 0, s_stack + threadIdx.x, kTraverseBlock);
+    Hit h = trace_segment<TF_SPHERE | TF_PLANAR | TF_MOVING>(sc, ray, kNone, false, make_uint2(0, 0), 0, 0, 0, s_stack + threadIdx.x, kTraverseBlock);
     ids[p] = h.prim == kNone ? kNone : sc.canonical[h.prim];
     ts[p] = h.t;
   }
@@ -498,6 +515,7 @@ static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint
   cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
   if (timing) { ev_begin = ds.events[kMaxTimed * 4]; ev_end = ds.events[kMaxTimed * 4 + 1]; RT_CUDA(cudaEventRecord(ev_begin, stream)); }
 
+  const TraverseFn traverse = pick_traverse(s.flat.features);
   const int g_trav = ds.sm_count * 8, g_shade = ds.sm_count * 8, g_gen = ds.sm_count * 4;
   uint64_t launches = 0;
   size_t timed = 0;
@@ -512,7 +530,7 @@ static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint
       const bool t_this = timing && timed < kMaxTimed;
       k_raygen<<<g_gen, kRaygenBlock, 0, stream>>>(ds.ctl, q, A);
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 0], stream);
-      k_traverse<<<g_trav, kTraverseBlock, 0, stream>>>(ds.ctl, q, ds.d, A);
+      traverse<<<g_trav, kTraverseBlock, 0, stream>>>(ds.ctl, q, ds.d, A);
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
       k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, ds.d, A);
       if (t_this) { cudaEventRecord(ds.events[timed * 4 + 2], stream); timed++; }
@@ -555,7 +573,6 @@ static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint
       stats->ms_raygen = std::max(0.0, (double)ms - tt - tsd);
     }
   }
-  (void)s;
   return RT_OK;
 }
 

@@ -87,7 +87,9 @@ struct Hit {
 };
 
 // one primitive; `skip_a` = geometry the ray ORIGIN lies on, `skip_b` = geometry of a hit at tmin
-// that must not be reported again (second boundary query of constantMedium, Geometry.hs:311)
+// that must not be reported again (second boundary query of constantMedium, Geometry.hs:311).
+// F = scene feature bits (TF_*): code for absent primitive kinds / instances is compiled out.
+template <uint32_t F>
 __device__ __forceinline__ void intersect_prim(const DScene& sc, uint32_t i, const RayT& ray, float tmin,
                                                uint32_t skip_a, uint32_t skip_b, Hit& best) {
   const float4* P = sc.prims + 4 * (size_t)i;
@@ -95,76 +97,81 @@ __device__ __forceinline__ void intersect_prim(const DScene& sc, uint32_t i, con
   const uint32_t tf = __float_as_uint(m4.x), geom = __float_as_uint(m4.y);
   const float4 p0 = __ldg(P);
   f3 o = ray.o, d = ray.d;
-  if (tf & PRIM_FLAG_MOVING) {  // transform / moving instance kept local (Geometry.hs:388-389,452-454)
-    const DXform& X = sc.xforms[__float_as_uint(m4.z)];
-    f3 b = fma3(ray.time, ld3(X.binv1), ld3(X.binv0));
-    o = mat3(X.Ainv, ray.o) + b;
-    d = mat3(X.Ainv, ray.d);
+  if constexpr ((F & TF_MOVING) != 0) {
+    if (tf & PRIM_FLAG_MOVING) {  // transform / moving instance kept local (Geometry.hs:388-389,452-454)
+      const DXform& X = sc.xforms[__float_as_uint(m4.z)];
+      f3 b = fma3(ray.time, ld3(X.binv1), ld3(X.binv0));
+      o = mat3(X.Ainv, ray.o) + b;
+      d = mat3(X.Ainv, ray.d);
+    }
   }
   float t;
   bool front;
-  if ((tf & PRIM_TYPE_MASK) == PRIM_SPHERE) {
-    const bool on_a = geom == skip_a, on_b = geom == skip_b;
-    float h, sq;
-    if (tf & PRIM_FLAG_BIG) {  // fp64 up to the discriminant, stable roots in fp32
-      const float4 p1 = __ldg(P + 1);
-      double cx = (double)p0.x + (double)p1.x, cy = (double)p0.y + (double)p1.y, cz = (double)p0.z + (double)p1.z;
-      double r = (double)p0.w + (double)p1.w;
-      double ox = cx - (double)o.x, oy = cy - (double)o.y, oz = cz - (double)o.z;
-      double hd = (double)d.x * ox + (double)d.y * oy + (double)d.z * oz;
-      double c = ox * ox + oy * oy + oz * oz - r * r;
-      // |d|^2 = 1 + O(1e-7) after the fp32 normalise; at |oc| ~ 1e3 the term (|d|^2 - 1) c is NOT negligible
-      // against the discriminant, so the quadratic keeps its leading coefficient
-      double dd = (double)d.x * (double)d.x + (double)d.y * (double)d.y + (double)d.z * (double)d.z;
-      double disc = hd * hd - dd * c;
-      if (!(disc >= 0.0)) return;
-      sq = sqrtf((float)disc);
-      h = (float)hd;
-      // q = h + sign(h) sqrt(disc): roots are q/|d|^2 and c/q, neither suffers cancellation
-      double q = hd >= 0.0 ? hd + (double)sq : hd - (double)sq;
-      float rq = (float)(q * (2.0 - dd)), rc = q != 0.0 ? __fdividef((float)c, (float)q) : 0.f;
-      float near_t = fminf(rq, rc), far_t = fmaxf(rq, rc);
-      if (on_a || on_b) {
-        if (on_a && !(hd > 0.0)) return;
-        t = far_t;
-        if (!(t > tmin)) return;
+  const bool is_sphere = (F & TF_PLANAR) == 0 || ((F & TF_SPHERE) != 0 && (tf & PRIM_TYPE_MASK) == PRIM_SPHERE);
+  if (is_sphere) {
+    if constexpr ((F & TF_SPHERE) != 0) {
+      const bool on_a = geom == skip_a, on_b = geom == skip_b;
+      if (tf & PRIM_FLAG_BIG) {  // fp64 up to the discriminant, stable roots in fp32
+        const float4 p1 = __ldg(P + 1);
+        double cx = (double)p0.x + (double)p1.x, cy = (double)p0.y + (double)p1.y, cz = (double)p0.z + (double)p1.z;
+        double r = (double)p0.w + (double)p1.w;
+        double ox = cx - (double)o.x, oy = cy - (double)o.y, oz = cz - (double)o.z;
+        double hd = (double)d.x * ox + (double)d.y * oy + (double)d.z * oz;
+        double c = ox * ox + oy * oy + oz * oz - r * r;
+        // |d|^2 = 1 + O(1e-7) after the fp32 normalise; at |oc| ~ 1e3 the term (|d|^2 - 1) c is NOT negligible
+        // against the discriminant, so the quadratic keeps its leading coefficient
+        double dd = (double)d.x * (double)d.x + (double)d.y * (double)d.y + (double)d.z * (double)d.z;
+        double disc = hd * hd - dd * c;
+        if (!(disc >= 0.0)) return;
+        float sq = sqrtf((float)disc);
+        // q = h + sign(h) sqrt(disc): roots are q/|d|^2 and c/q, neither suffers cancellation
+        double q = hd >= 0.0 ? hd + (double)sq : hd - (double)sq;
+        float rq = (float)(q * (2.0 - dd)), rc = q != 0.0 ? __fdividef((float)c, (float)q) : 0.f;
+        float near_t = fminf(rq, rc), far_t = fmaxf(rq, rc);
+        if (on_a || on_b) {
+          if (on_a && !(hd > 0.0)) return;
+          t = far_t;
+          if (!(t > tmin)) return;
+        } else {
+          t = near_t;
+          if (!(t > tmin && t <= best.t)) { t = far_t; if (!(t > tmin)) return; }
+        }
+        front = (double)t <= hd;
       } else {
-        t = near_t;
-        if (!(t > tmin && t <= best.t)) { t = far_t; if (!(t > tmin)) return; }
+        f3 oc = mk3(p0.x, p0.y, p0.z) - o;
+        float h = dot3(d, oc);
+        f3 l = fma3(-h, d, oc);                 // component of oc perpendicular to the ray
+        float disc = fmaf(p0.w, p0.w, -dot3(l, l));
+        if (!(disc >= 0.f)) return;
+        float sq = sqrtf(disc);
+        if (on_a || on_b) {
+          if (on_a && !(h > 0.f)) return;
+          t = h + sq;
+          if (!(t > tmin)) return;
+        } else {
+          t = h - sq;
+          if (!(t > tmin && t <= best.t)) { t = h + sq; if (!(t > tmin)) return; }
+        }
+        front = t <= h;                          // d.(p-c) = t - h  (Geometry.hs:83-84, `<=`)
       }
-      front = (double)t <= hd;
-    } else {
-      f3 oc = mk3(p0.x, p0.y, p0.z) - o;
-      h = dot3(d, oc);
-      f3 l = fma3(-h, d, oc);                 // component of oc perpendicular to the ray
-      float disc = fmaf(p0.w, p0.w, -dot3(l, l));
-      if (!(disc >= 0.f)) return;
-      sq = sqrtf(disc);
-      if (on_a || on_b) {
-        if (on_a && !(h > 0.f)) return;
-        t = h + sq;
-        if (!(t > tmin)) return;
-      } else {
-        t = h - sq;
-        if (!(t > tmin && t <= best.t)) { t = h + sq; if (!(t > tmin)) return; }
-      }
-      front = t <= h;                          // d.(p-c) = t - h  (Geometry.hs:83-84, `<=`)
-    }
-    if (p0.w < 0.f) front = !front;
+      if (p0.w < 0.f) front = !front;
+    } else return;
   } else {
-    if (geom == skip_a || geom == skip_b) return;
-    const float4 p1 = __ldg(P + 1), p2 = __ldg(P + 2);
-    f3 q = mk3(p0.x, p0.y, p0.z), n = mk3(p0.w, p1.x, p1.y);
-    float denom = dot3(n, d);
-    if (!(fabsf(denom) > 1e-8f)) return;
-    f3 qo = q - o;
-    t = __fdividef(dot3(n, qo), denom);
-    if (!(t > tmin && t <= best.t)) return;
-    f3 pr = fma3(t, d, -qo);                   // p - q
-    float a = dot3(mk3(p1.z, p1.w, p2.x), pr), b = dot3(mk3(p2.y, p2.z, p2.w), pr);
-    if ((tf & PRIM_TYPE_MASK) == PRIM_PGRAM) { if (!(0.f <= a && a <= 1.f && 0.f <= b && b <= 1.f)) return; }
-    else { if (!(a >= 0.f && b >= 0.f && a + b <= 1.f)) return; }
-    front = denom < 0.f;
+    if constexpr ((F & TF_PLANAR) != 0) {
+      if (geom == skip_a || geom == skip_b) return;
+      const float4 p1 = __ldg(P + 1), p2 = __ldg(P + 2);
+      f3 q = mk3(p0.x, p0.y, p0.z), n = mk3(p0.w, p1.x, p1.y);
+      float denom = dot3(n, d);
+      if (!(fabsf(denom) > 1e-8f)) return;
+      f3 qo = q - o;
+      t = __fdividef(dot3(n, qo), denom);
+      if (!(t > tmin && t <= best.t)) return;
+      f3 pr = fma3(t, d, -qo);                   // p - q
+      float a = dot3(mk3(p1.z, p1.w, p2.x), pr), b = dot3(mk3(p2.y, p2.z, p2.w), pr);
+      if ((tf & PRIM_TYPE_MASK) == PRIM_PGRAM) { if (!(0.f <= a && a <= 1.f && 0.f <= b && b <= 1.f)) return; }
+      else { if (!(a >= 0.f && b >= 0.f && a + b <= 1.f)) return; }
+      front = denom < 0.f;
+    } else return;
   }
   if (t < best.t || (t == best.t && i < best.prim)) {
     best.t = t;
@@ -183,85 +190,88 @@ __device__ __forceinline__ bool box_hit(const float4 lo, const float4 hi, f3 inv
   return tn <= tf;   // fminf/fmaxf drop NaN operands: a NaN slab never culls (Appendix A.8)
 }
 
-// Closest hit below node pair `root`.  `stack` is this thread's column of the shared-memory short
-// stack (stride = blockDim.x words).  `best` carries (tmax, kNone) in and the result out.
+// Closest hit below node reference `root` ("while-while" traversal: every lane first descends through inner
+// nodes until it holds a leaf, then the warp tests primitives together — keeps the expensive primitive code
+// SIMD-dense).  `stack` is this thread's column of the shared-memory short stack (stride words apart).
+// `best` carries (tmax, kNone) in and the result out.
+template <uint32_t F>
 __device__ __forceinline__ void closest_hit(const DScene& sc, uint32_t root, const RayT& ray, float tmin,
                                             uint32_t skip_a, uint32_t skip_b, uint32_t* stack, uint32_t stride, Hit& best) {
-  if (root == kNone) return;
   f3 inv;
   inv.x = fabsf(ray.d.x) > 1e-30f ? __frcp_rn(ray.d.x) : copysignf(1e30f, ray.d.x);
   inv.y = fabsf(ray.d.y) > 1e-30f ? __frcp_rn(ray.d.y) : copysignf(1e30f, ray.d.y);
   inv.z = fabsf(ray.d.z) > 1e-30f ? __frcp_rn(ray.d.z) : copysignf(1e30f, ray.d.z);
   const f3 oinv = ray.o * inv;
-  uint32_t cur = root;
+  uint32_t cur = root;          // kNone (leaf bit set, all ones) = nothing left
   int sp = 0;
-  for (;;) {
-    const float4* N = sc.nodes + 2 * (size_t)cur;
-    const float4 l0 = __ldg(N), h0 = __ldg(N + 1), l1 = __ldg(N + 2), h1 = __ldg(N + 3);
-    float tn0, tn1;
-    bool hit0 = box_hit(l0, h0, inv, oinv, tmin, best.t, tn0);
-    bool hit1 = box_hit(l1, h1, inv, oinv, tmin, best.t, tn1);
-    const uint32_t a0 = __float_as_uint(l0.w), b0 = __float_as_uint(h0.w);
-    const uint32_t a1 = __float_as_uint(l1.w), b1 = __float_as_uint(h1.w);
-    if (hit0 && (b0 & kLeafBit)) {
-      for (uint32_t k = 0, n = b0 & ~kLeafBit; k < n; k++) intersect_prim(sc, a0 + k, ray, tmin, skip_a, skip_b, best);
-      hit0 = false;
+  while (cur != kNone) {
+    while (!(cur & kLeafBit)) {
+      const float4* N = sc.nodes + 2 * (size_t)cur;
+      const float4 l0 = __ldg(N), h0 = __ldg(N + 1), l1 = __ldg(N + 2), h1 = __ldg(N + 3);
+      float tn0, tn1;
+      const bool hit0 = box_hit(l0, h0, inv, oinv, tmin, best.t, tn0);
+      const bool hit1 = box_hit(l1, h1, inv, oinv, tmin, best.t, tn1);
+      const uint32_t r0 = __float_as_uint(l0.w), r1 = __float_as_uint(l1.w);
+      if (hit0 && hit1) {
+        const bool first0 = tn0 <= tn1;     // near child first; results do not depend on the order
+        stack[sp * stride] = first0 ? r1 : r0;
+        sp++;
+        cur = first0 ? r0 : r1;
+      } else if (hit0) cur = r0;
+      else if (hit1) cur = r1;
+      else if (sp > 0) { sp--; cur = stack[sp * stride]; }
+      else cur = kNone;
     }
-    if (hit1 && (b1 & kLeafBit)) {
-      for (uint32_t k = 0, n = b1 & ~kLeafBit; k < n; k++) intersect_prim(sc, a1 + k, ray, tmin, skip_a, skip_b, best);
-      hit1 = false;
-    }
-    hit0 = hit0 && tn0 <= best.t;
-    hit1 = hit1 && tn1 <= best.t;
-    if (hit0 && hit1) {
-      const bool first0 = tn0 <= tn1;     // near child first; results do not depend on the order
-      stack[sp * stride] = first0 ? a1 : a0;
-      sp++;
-      cur = first0 ? a0 : a1;
-    } else if (hit0) cur = a0;
-    else if (hit1) cur = a1;
-    else {
-      if (sp == 0) break;
-      sp--;
-      cur = stack[sp * stride];
-    }
+    if (cur == kNone) break;
+    const uint32_t first = (cur & ~kLeafBit) >> 3, count = (cur & 7u) + 1u;
+    for (uint32_t k = 0; k < count; k++) intersect_prim<F>(sc, first + k, ray, tmin, skip_a, skip_b, best);
+    if (sp > 0) { sp--; cur = stack[sp * stride]; }
+    else cur = kNone;
   }
 }
 
 // ---- full closest-hit query of a path segment: surfaces, then every medium (Geometry.hs:298-330) ---
+template <uint32_t F>
 __device__ __forceinline__ Hit trace_segment(const DScene& sc, const RayT& ray, uint32_t origin_geom, bool with_media,
                                              uint2 key, uint32_t pixel, uint64_t sample, uint32_t bounce,
                                              uint32_t* stack, uint32_t stride) {
   const float tmin = 1e-4f;  // Ray.hs:178
-  Hit best{__int_as_float(0x7f800000), kNone, false};
-  closest_hit(sc, sc.surface_root, ray, tmin, origin_geom, kNone, stack, stride, best);
-  if (with_media && sc.n_media) {
-    uint4 rnd = make_uint4(0, 0, 0, 0);
-    for (uint32_t m = 0; m < sc.n_media; m++) {
-      if ((m & 3u) == 0) rnd = rng4(key, pixel, sample, bounce, RNG_MEDIA + (m >> 2));
-      const uint32_t rbits = (m & 3u) == 0 ? rnd.x : ((m & 3u) == 1 ? rnd.y : ((m & 3u) == 2 ? rnd.z : rnd.w));
-      const DMedium& md = sc.media[m];
-      Hit h1{__int_as_float(0x7f800000), kNone, false};
-      closest_hit(sc, md.root, ray, tmin, origin_geom, kNone, stack, stride, h1);
-      if (h1.prim == kNone) continue;
-      float t1, t2;
-      if (h1.front) {
-        if (!(h1.t < best.t)) continue;
-        const uint32_t g1 = __float_as_uint(__ldg(sc.prims + 4 * (size_t)h1.prim + 3).y);
-        Hit h2{__int_as_float(0x7f800000), kNone, false};
-        closest_hit(sc, md.root, ray, h1.t, origin_geom, g1, stack, stride, h2);
-        if (h2.prim == kNone) continue;
-        t1 = h1.t;
-        t2 = fminf(best.t, h2.t);
-      } else {
-        t1 = tmin;
-        t2 = fminf(best.t, h1.t);
-      }
-      const float hit_dist = md.neg_inv_density * logf(u01(rbits));   // rand = 0 → +inf → no hit
-      if (hit_dist < t2 - t1) {
-        best.t = t1 + hit_dist;
-        best.prim = kMediumBase + m;
-        best.front = true;
+  const float inf = __int_as_float(0x7f800000);
+  Hit best{inf, kNone, false};
+  closest_hit<F>(sc, sc.surface_root, ray, tmin, origin_geom, kNone, stack, stride, best);
+  if constexpr ((F & TF_MEDIA) != 0) {
+    if (with_media) {
+      uint4 rnd = make_uint4(0, 0, 0, 0);
+      for (uint32_t m = 0; m < sc.n_media; m++) {
+        if ((m & 3u) == 0) rnd = rng4(key, pixel, sample, bounce, RNG_MEDIA + (m >> 2));
+        const uint32_t rbits = (m & 3u) == 0 ? rnd.x : ((m & 3u) == 1 ? rnd.y : ((m & 3u) == 2 ? rnd.z : rnd.w));
+        const DMedium& md = sc.media[m];
+        // boundary query 1 on (tmin, inf); if it is a front-side hit before the current closest hit, query 2 on
+        // (t1, inf) finds where the ray leaves again (Geometry.hs:307-313).  One code copy serves both.
+        float t1 = tmin, t2 = 0.f, qmin = tmin;
+        uint32_t skip_b = kNone;
+        bool have_segment = false;
+        for (int pass = 0; pass < 2; pass++) {
+          Hit h{inf, kNone, false};
+          closest_hit<F>(sc, md.root, ray, qmin, origin_geom, skip_b, stack, stride, h);
+          if (h.prim == kNone) break;
+          if (pass == 0) {
+            if (!h.front) { t1 = tmin; t2 = fminf(best.t, h.t); have_segment = true; break; }
+            if (!(h.t < best.t)) break;
+            t1 = qmin = h.t;
+            skip_b = __float_as_uint(__ldg(sc.prims + 4 * (size_t)h.prim + 3).y);
+          } else {
+            t2 = fminf(best.t, h.t);
+            have_segment = true;
+          }
+        }
+        if (!have_segment) continue;
+        const float hit_dist = md.neg_inv_density * logf(u01(rbits));   // rand = 0 → +inf → no hit
+        if (hit_dist < t2 - t1) {
+          best.t = t1 + hit_dist;
+          best.prim = kMediumBase + m;
+          best.front = true;
+        }
       }
     }
   }

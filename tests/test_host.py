@@ -61,17 +61,23 @@ def test_flattened_tree_matches_reference_evaluation_order(built, name):
     assert np.array_equal(canon[: len(order)], order)
     info = cs.info()
     assert info["n_bvh_nodes"] == len(nodes) and info["max_depth"] < 32
-    # every inner node's box contains its children's boxes; leaves reference valid primitive ranges
+    # every inner node's box contains its children's boxes; leaf references address valid primitive ranges
     lo, hi = nodes[:, 0:3], nodes[:, 4:7]
-    a, b = nodes[:, 3].view(np.uint32), nodes[:, 7].view(np.uint32)
+    ref, cnt = nodes[:, 3].view(np.uint32), nodes[:, 7].view(np.uint32)
+    LEAF = 0x80000000
+    seen = np.zeros(info["n_prims"], bool)
     for k in range(len(nodes)):
-        if b[k] == 0:          # inner
-            c = int(a[k])
+        if ref[k] & LEAF:
+            first, c = int(ref[k] & 0x7FFFFFFF) >> 3, int(ref[k] & 7) + 1
+            assert c == cnt[k] and 1 <= c <= 8 and first + c <= info["n_prims"]
+            seen[first:first + c] = True
+        else:
+            c = int(ref[k])
+            assert c % 2 == 0 and cnt[k] == 0
             for ch in (c, c + 1):
                 assert (lo[k] <= lo[ch] + 1e-3).all() and (hi[k] >= hi[ch] - 1e-3).all()
-        elif lo[k, 0] < 1e37:  # leaf (not the parked root sibling)
-            cnt = int(b[k] & 0x7FFFFFFF)
-            assert 1 <= cnt <= 8 and int(a[k]) + cnt <= info["n_prims"]
+    if len(nodes):                 # every primitive is reachable through some leaf (a medium whose boundary is one
+        assert (~seen).sum() <= 8 * info["n_media"]      # leaf is referenced from its DMedium record, not a node)
 
 
 def test_scene_counts(built):
