@@ -4,7 +4,7 @@
 // Layout summary (DESIGN.md §"Data layout in HBM"):
 //   nodes   : 32-byte BVH nodes, 2 x float4 {lo.xyz, a} {hi.xyz, b}; siblings adjacent (one 64 B
 //             fetch tests both children).  a = node reference: inner → index of the pair holding its children;
-//             leaf → kLeafBit | first primitive << 3 | (count - 1).  b = primitive count (leaf) or 0.
+//             leaf → kLeafBit | first primitive << 5 | (count - 1), count <= 32.  b = primitive count (leaf) or 0.
 //             Roots are bare references (no node, no box test of their own, as in the reference).
 //   prims   : 64-byte records, 4 x float4; index order = the reference's evaluation order
 //             (group: list order, Geometry.hs:340-345; bvhNode: left first, :356-361), so
@@ -22,6 +22,7 @@ namespace rtb {
 
 constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr uint32_t kLeafBit = 0x80000000u;
+constexpr uint32_t kLeafShift = 5u, kLeafCountMask = 31u, kLeafCap = 32u;   // leaf ref = kLeafBit | first << 5 | (count - 1)
 constexpr uint32_t kMediumBase = 0xFFFF0000u;  // hit.prim >= kMediumBase: medium (prim - base)
 constexpr int kStackDepth = 32;                // shared-memory short stack entries per thread
 constexpr int kMaxTargets = 8;                 // cs_redirectTargets entries supported on device
@@ -72,7 +73,10 @@ struct DMedium {    // constantMedium, Geometry.hs:298-330
   float neg_inv_density;
   uint32_t root;        // node reference of the boundary tree
   uint32_t material;
-  uint32_t geom_lo, geom_hi;  // geom-id range of the boundary primitives (dense ids)
+  // Boundary primitives whose geometry ids form the dense range [geom_lo, geom_hi] AND which are all also part of the
+  // surface tree (e.g. `dielectric <$ mesh` + `constantMedium rho mesh`): the surface closest hit then answers the first
+  // boundary query (closest over a subset = closest over the set when it lies in the subset).  shared = 0 otherwise.
+  uint32_t geom_lo, geom_hi, shared;
 };
 
 struct DTarget {    // RedirectTarget, Ray.hs:112-118 (+ its parallelogram record for the pdf probe)

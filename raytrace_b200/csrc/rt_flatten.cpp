@@ -504,10 +504,34 @@ struct Builder {
   }
 
   // ---- device-shaped tree --------------------------------------------------------------------------------
-  uint32_t kLeafMax = 8;     // RT_B200_LEAF overrides (tuning knob; <= 8 by the 3-bit count field)
-  bool all_single_leaves(const RNode& n) const {
-    for (int c : n.children) if (rnodes[c].kind != RNode::LEAF) return false;
-    return true;
+  // A `group` subtree made only of groups and primitives with at most kLeafMax primitives becomes ONE leaf (a linear
+  // scan, exactly what the reference does for `group`): every lane of a warp then runs the same instruction stream,
+  // which beats a divergent BVH walk for small lists.  RT_B200_LEAF overrides (<= 32 by the 5-bit count field).
+  uint32_t kLeafMax = 24;
+  // A bvhTree subtree with at most kCollapse primitives becomes one leaf (the reference's tree, truncated: same split
+  // policy above, a short scan below).  RT_B200_COLLAPSE overrides.
+  uint32_t kCollapse = 1;
+  // number of primitives below a subtree made only of GROUPs and LEAFs; 0 if it contains a BVH node
+  uint32_t flat_count(const RNode& n) const {
+    if (n.kind == RNode::LEAF) return 1;
+    if (n.kind != RNode::GROUP) return 0;
+    uint32_t tot = 0;
+    for (int c : n.children) {
+      uint32_t k = flat_count(rnodes[c]);
+      if (k == 0) return 0;
+      tot += k;
+      if (tot > kLeafCap) return kLeafCap + 1;
+    }
+    return tot;
+  }
+  void count_collect(const RNode& n, uint32_t& k, uint32_t& first, BoxD& box) const {
+    if (k > kLeafCap) return;
+    if (n.kind == RNode::LEAF) { k++; first = std::min(first, prims[n.prim].index); box.join(prims[n.prim].box); return; }
+    for (int c : n.children) count_collect(rnodes[c], k, first, box);
+  }
+  void flat_collect(const RNode& n, uint32_t& first, BoxD& box) const {
+    if (n.kind == RNode::LEAF) { first = std::min(first, prims[n.prim].index); box.join(prims[n.prim].box); return; }
+    for (int c : n.children) flat_collect(rnodes[c], first, box);
   }
   int median_build(std::vector<int> hs) {  // the reference's split policy on device boxes
     if (hs.size() == 1) return hs[0];
@@ -536,13 +560,30 @@ struct Builder {
       hnodes[me].box = prims[n.prim].box;
       return me;
     }
-    if (n.kind == RNode::GROUP && n.children.size() <= kLeafMax && all_single_leaves(n)) {
-      hnodes.emplace_back();       // e.g. a cuboid: one leaf of 6 parallelograms (contiguous indices)
-      int me = (int)hnodes.size() - 1;
-      hnodes[me].first = prims[rnodes[n.children[0]].prim].index;
-      hnodes[me].count = (uint32_t)n.children.size();
-      for (int c : n.children) hnodes[me].box.join(prims[rnodes[c].prim].box);
-      return me;
+    if (n.kind == RNode::GROUP) {
+      const uint32_t k = flat_count(n);
+      if (k >= 1 && k <= kLeafMax) {   // e.g. a cuboid (6 parallelograms) or the whole Cornell box (18): one leaf;
+        hnodes.emplace_back();         // indices are contiguous because numbering is a DFS in evaluation order
+        int me = (int)hnodes.size() - 1;
+        uint32_t first = kNone;
+        BoxD box;
+        flat_collect(n, first, box);
+        hnodes[me].first = first;
+        hnodes[me].count = k;
+        hnodes[me].box = box;
+        return me;
+      }
+    }
+    if (n.kind == RNode::BVH && kCollapse > 1) {
+      uint32_t k = 0, first = kNone;
+      BoxD box;
+      count_collect(n, k, first, box);
+      if (k <= kCollapse) {
+        hnodes.emplace_back();
+        int me = (int)hnodes.size() - 1;
+        hnodes[me].first = first; hnodes[me].count = k; hnodes[me].box = box;
+        return me;
+      }
     }
     std::vector<int> hs;
     for (int c : n.children) hs.push_back(to_device(c));
@@ -557,6 +598,12 @@ struct Builder {
     return median_build(std::move(hs));  // GROUP → BVH (results identical to the linear scan)
   }
 
+  void collect_geoms(int r, std::vector<uint32_t>& out) const {
+    const RNode& n = rnodes[r];
+    if (n.kind == RNode::LEAF) { out.push_back(prims[n.prim].geom); return; }
+    for (int c : n.children) collect_geoms(c, out);
+  }
+
   static float round_down(double x) { float f = (float)x; return (double)f > x ? std::nextafterf(f, -INFINITY) : f; }
   static float round_up(double x) { float f = (float)x; return (double)f < x ? std::nextafterf(f, INFINITY) : f; }
   void write_node(DNode& d, const HNode& h) {
@@ -565,13 +612,13 @@ struct Builder {
     double pad = 1e-5 * m + 1e-6;  // slab test runs in fp32: keep boxes conservative
     for (int k = 0; k < 3; k++) { d.lo[k] = round_down(h.box.lo[k] - pad); d.hi[k] = round_up(h.box.hi[k] + pad); }
   }
-  // Node reference: leaf → kLeafBit | first << 3 | (count - 1); inner → index of the node PAIR holding its two
+  // Node reference: leaf → kLeafBit | first << 5 | (count - 1); inner → index of the node PAIR holding its two
   // children (siblings adjacent: one 64-byte fetch tests both).  A root has no node of its own: like the
   // reference, the top-level geometry's own box is never tested.
   uint32_t emit_ref(FlatScene& fs, int hn, uint32_t depth, uint32_t& max_depth) {
     const HNode h = hnodes[hn];
     max_depth = std::max(max_depth, depth);
-    if (h.left < 0) return kLeafBit | (h.first << 3) | (h.count - 1);
+    if (h.left < 0) return kLeafBit | (h.first << kLeafShift) | (h.count - 1);
     uint32_t at = (uint32_t)fs.nodes.size();
     fs.nodes.emplace_back();
     fs.nodes.emplace_back();
@@ -703,7 +750,8 @@ void default_noise_tables(int32_t perm[3][256], double grad[256][3]) {
 int32_t flatten_scene(Scene& sc, uint32_t root) {
   try {
     Builder b(sc);
-    if (const char* e = std::getenv("RT_B200_LEAF")) b.kLeafMax = std::min<uint32_t>(8, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
+    if (const char* e = std::getenv("RT_B200_LEAF")) b.kLeafMax = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
+    if (const char* e = std::getenv("RT_B200_COLLAPSE")) b.kCollapse = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
     b.mat_used.assign(sc.materials.size(), 0);
     b.tex_used.assign(sc.textures.size(), 0);
     XfState id;
@@ -719,20 +767,33 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
       int h = b.to_device(surf);
       fs.surface_root = b.emit_ref(fs, h, 0, max_depth);
     }
+    std::vector<uint32_t> surf_geoms;
+    if (surf >= 0) b.collect_geoms(surf, surf_geoms);
+    std::sort(surf_geoms.begin(), surf_geoms.end());
+    surf_geoms.erase(std::unique(surf_geoms.begin(), surf_geoms.end()), surf_geoms.end());
     for (size_t i = 0; i < b.media.size(); i++) {
       int h = b.to_device(b.media[i].rtree);
       DMedium& dm = fs.media[i];
       dm.neg_inv_density = (float)(-(1.0 / b.media[i].density));
       dm.root = b.emit_ref(fs, h, 0, max_depth);
       dm.material = b.media[i].material;
-      dm.geom_lo = dm.geom_hi = 0;
+      dm.geom_lo = dm.geom_hi = dm.shared = 0;
+      // shared-boundary shortcut: dense geometry-id range, every id also present in the surface tree
+      std::vector<uint32_t> g;
+      b.collect_geoms(b.media[i].rtree, g);
+      std::sort(g.begin(), g.end());
+      g.erase(std::unique(g.begin(), g.end()), g.end());
+      if (!g.empty() && g.back() - g.front() + 1 == g.size() && std::getenv("RT_B200_NO_SHARED") == nullptr &&
+          std::includes(surf_geoms.begin(), surf_geoms.end(), g.begin(), g.end())) {
+        dm.geom_lo = g.front(); dm.geom_hi = g.back(); dm.shared = 1;
+      }
     }
     fs.n_media = (uint32_t)b.media.size();
     fs.max_depth = max_depth;
     if (max_depth + 1 > (uint32_t)kStackDepth)
       b.fail(RT_ERR_UNSUPPORTED, "flattened BVH is deeper than the shared-memory traversal stack (32 levels)");
     b.pack_prims(fs);
-    if (fs.canonical.size() >= (1u << 28)) b.fail(RT_ERR_UNSUPPORTED, "more than 2^28 primitives");
+    if (fs.canonical.size() >= (1u << 26)) b.fail(RT_ERR_UNSUPPORTED, "more than 2^26 primitives");
     for (const HPrim& p : b.prims) {
       if (p.index == kNone) continue;
       fs.features |= (p.type == PRIM_SPHERE) ? TF_SPHERE : TF_PLANAR;

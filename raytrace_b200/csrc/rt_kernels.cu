@@ -43,6 +43,7 @@ struct Ctl {                      // device-resident control block of one render
   unsigned long long rays;        // path segments traversed so far
   unsigned int n_cur, n_next;
   unsigned int iterations, pool;
+  unsigned int trav_next, _pad;   // next queue slot the persistent traversal warps fetch (reset by k_advance)
 };
 
 struct Queue {                    // SoA live-ray queue (56 B per path)
@@ -60,6 +61,7 @@ struct RenderArgs {
   float* sum;
   float* sumsq;
   float2* hits;                   // per queue slot: t, prim (bits)
+  int refill;                     // persistent traversal: idle lanes per warp that trigger a fetch
 };
 
 __device__ __forceinline__ uint32_t live_count(const Ctl* ctl) {
@@ -115,9 +117,9 @@ __global__ void __launch_bounds__(kRaygenBlock) k_raygen(const Ctl* __restrict__
 // F = scene feature bits (TF_*): one specialisation per combination that occurs (sphere-only, planar-only,
 // mixed; with / without media; a catch-all with moving instances), chosen at launch from FlatScene::features.
 template <uint32_t F>
-__global__ void __launch_bounds__(kTraverseBlock) k_traverse(const Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
+__global__ void __launch_bounds__(kTraverseBlock) k_traverse(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
                                                              const __grid_constant__ RenderArgs A) {
-  __shared__ uint32_t s_stack[kStackDepth * kTraverseBlock];
+  extern __shared__ uint32_t s_stack[];   // (scene BVH depth + 1) x kTraverseBlock words: a deeper static stack would only eat L1
   const uint32_t n = live_count(ctl);
   uint32_t* stack = s_stack + threadIdx.x;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -136,18 +138,209 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse(const Ctl* __restri
   }
 }
 
-using TraverseFn = void (*)(const Ctl*, Queue, const DScene, const RenderArgs);
-static TraverseFn pick_traverse(uint32_t features) {
-  if (features & TF_MOVING) return k_traverse<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_MEDIA>;
-  switch (features & (TF_SPHERE | TF_PLANAR | TF_MEDIA)) {
-    case TF_SPHERE: return k_traverse<TF_SPHERE>;
-    case TF_PLANAR: return k_traverse<TF_PLANAR>;
-    case TF_SPHERE | TF_PLANAR: return k_traverse<TF_SPHERE | TF_PLANAR>;
-    case TF_SPHERE | TF_MEDIA: return k_traverse<TF_SPHERE | TF_MEDIA>;
-    case TF_PLANAR | TF_MEDIA: return k_traverse<TF_PLANAR | TF_MEDIA>;
-    case TF_SPHERE | TF_PLANAR | TF_MEDIA: return k_traverse<TF_SPHERE | TF_PLANAR | TF_MEDIA>;
-    default: return k_traverse<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_MEDIA>;
+
+// ---- persistent traversal with dynamic ray fetch ----------------------------------------------------------------
+// Per-ray work varies by two orders of magnitude (a background ray leaves after the root pair; a ray through a mesh
+// walks ~40 nodes, and a medium adds boundary queries), so a static ray→lane map leaves most lanes idle (ncu, round 1:
+// 8–13 of 32 threads active per instruction).  Here every lane is a small state machine {query → next query →
+// result}; a warp whose idle-lane count reaches kRefill grabs that many new queue slots with ONE atomic
+// (ballot/popc ranks), so lanes are replaced as they finish instead of waiting for the slowest ray of the warp.
+// Query sequence of one path segment (Geometry.hs:298-330 hoisted, see rt_trace.cuh::trace_segment — same results):
+//   surfaces on (tmin, inf) → for each medium: boundary on (tmin, inf) [+ boundary on (t1, inf)] + free-flight sample.
+
+constexpr int kPrimBurst = 8;   // primitives tested per PRIMITIVE step
+
+template <uint32_t F>
+__global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
+                                                               const __grid_constant__ RenderArgs A) {
+  extern __shared__ uint32_t s_stack[];   // (scene BVH depth + 1) x kTraverseBlock words: a deeper static stack would only eat L1
+  uint32_t* const stack = s_stack + threadIdx.x;
+  constexpr uint32_t stride = kTraverseBlock;
+  constexpr bool kMedia = (F & TF_MEDIA) != 0;
+  constexpr uint32_t kFull = 0xFFFFFFFFu;
+  const uint32_t n = live_count(ctl);
+  const uint32_t lane = threadIdx.x & 31u;
+  const float tmin0 = 1e-4f;   // Ray.hs:178
+  const float inf = __int_as_float(0x7f800000);
+
+  bool active = false, exhausted = false;
+  uint32_t slot = 0, cur = kNone, origin_geom = kNone, skip_b = kNone;
+  uint32_t pc = 0, pe = 0;        // pending primitive range of the current leaf
+  int sp = 0;
+  RayT ray{};
+  f3 inv{}, oinv{};
+  float tmin = tmin0;
+  Hit h{inf, kNone, false};      // running result of the current query
+  Hit best{inf, kNone, false};   // media scenes: closest event of the segment so far
+  uint32_t m = 0;                // media scenes: 0 = surface query, k+1 = medium k
+  int pass = 0;
+  float t1 = 0.f;
+
+  for (;;) {
+    // Every lane is in one of three states, each served by different code:
+    //   N  cur is an inner node        → NODE step (fetch the 64-byte child pair, two slab tests, push/pop)
+    //   P  pc < pe (rest of a leaf)    → PRIMITIVE step (up to kPrimBurst primitive tests)
+    //   F  query finished              → FINISH step (media bookkeeping, result write) followed by the ray fetch
+    // Running them "as the lanes come" serialises the three codes at 7–12 of 32 active threads (ncu, round 1), so the
+    // warp votes each iteration and runs only ONE kind: F when enough lanes wait for it (or nothing else is left),
+    // otherwise the majority of N and P; the other lanes keep their state and join later.  Closest hit is order
+    // independent, so results do not change.
+    if (active && pc == pe && (cur & kLeafBit) && cur != kNone) {   // leaf reference → primitive range; next node from the stack
+      pc = (cur & ~kLeafBit) >> kLeafShift;
+      pe = pc + (cur & kLeafCountMask) + 1u;
+      if (sp > 0) { sp--; cur = stack[sp * stride]; }
+      else cur = kNone;
+    }
+    const bool want_p = active && pc < pe;
+    const bool want_n = active && !want_p && cur != kNone;
+    const bool want_f = active && !want_p && !want_n;
+    const int n_p = __popc(__ballot_sync(kFull, want_p)), n_n = __popc(__ballot_sync(kFull, want_n));
+    const int n_f = __popc(__ballot_sync(kFull, want_f));
+
+    if (n_n + n_p != 0 && n_f < A.refill) {
+      if (n_n >= n_p) {
+        if (want_n) {
+          const float4* N = sc.nodes + 2 * (size_t)cur;
+          const float4 l0 = __ldg(N), h0 = __ldg(N + 1), l1 = __ldg(N + 2), h1 = __ldg(N + 3);
+          float tn0, tn1;
+          const bool hit0 = box_hit(l0, h0, inv, oinv, tmin, h.t, tn0);
+          const bool hit1 = box_hit(l1, h1, inv, oinv, tmin, h.t, tn1);
+          const uint32_t r0 = __float_as_uint(l0.w), r1 = __float_as_uint(l1.w);
+          if (hit0 && hit1) {
+            const bool first0 = tn0 <= tn1;
+            stack[sp * stride] = first0 ? r1 : r0;
+            sp++;
+            cur = first0 ? r0 : r1;
+          } else if (hit0) cur = r0;
+          else if (hit1) cur = r1;
+          else if (sp > 0) { sp--; cur = stack[sp * stride]; }
+          else cur = kNone;
+        }
+      } else if (want_p) {
+        const uint32_t stop = min(pe, pc + (uint32_t)kPrimBurst);
+        for (; pc < stop; pc++) intersect_prim<F>(sc, pc, ray, tmin, origin_geom, skip_b, h);
+      }
+      continue;
+    }
+
+    // ---- FINISH step: next query of the segment, or its result --------------------------------------------------
+    if (want_f) {
+      if constexpr (!kMedia) {
+        A.hits[slot] = make_float2(h.front ? h.t : -h.t, __uint_as_float(h.prim));
+        active = false;
+      } else {
+        bool have_h = true;          // h holds a boundary / surface answer to evaluate
+        for (;;) {
+          if (have_h) {
+            float s1 = 0.f, s2 = -1.f;   // free-flight segment (s1, s2); empty when s2 < s1
+            if (m == 0) { best = h; }
+            else if (pass == 0) {
+              if (h.prim != kNone) {
+                if (!h.front) { s1 = tmin0; s2 = fminf(best.t, h.t); }           // we are inside (Geometry.hs:313)
+                else if (h.t < best.t) {                                        // entry before the closest event
+                  t1 = h.t;
+                  tmin = h.t;
+                  skip_b = __float_as_uint(__ldg(sc.prims + 4 * (size_t)h.prim + 3).y);
+                  pass = 1;
+                  cur = sc.media[m - 1].root;
+                  h = Hit{inf, kNone, false};
+                  break;                                                        // → second boundary query on (t1, inf)
+                }
+              }
+            } else if (h.prim != kNone) { s1 = t1; s2 = fminf(best.t, h.t); }
+            if (s2 >= s1) {
+              const DMedium& md = sc.media[m - 1];
+              const uint32_t pixel = __float_as_uint(q.thr[slot].w);
+              const uint2 meta = q.meta[slot];
+              const unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
+              const uint32_t k = m - 1;
+              const uint4 rnd = rng4(A.key, pixel, sample, meta.y, RNG_MEDIA + (k >> 2));
+              const uint32_t rbits = (k & 3u) == 0 ? rnd.x : ((k & 3u) == 1 ? rnd.y : ((k & 3u) == 2 ? rnd.z : rnd.w));
+              const float hit_dist = md.neg_inv_density * logf(u01(rbits));      // rand = 0 → +inf → no hit
+              if (hit_dist < s2 - s1) { best.t = s1 + hit_dist; best.prim = kMediumBase + k; best.front = true; }
+            }
+            m++;
+          }
+          if (m > sc.n_media) {           // all media done: the segment's closest event
+            A.hits[slot] = make_float2(best.front ? best.t : -best.t, __uint_as_float(best.prim));
+            active = false;
+            break;
+          }
+          const DMedium& md = sc.media[m - 1];   // set up this medium's first boundary query
+          pass = 0;
+          have_h = true;
+          if (md.shared && (best.prim == kNone || best.prim < kMediumBase)) {
+            // boundary ⊆ surfaces: the surface answer is the boundary answer when it lies on the boundary, and a
+            // surface miss is a boundary miss
+            if (best.prim == kNone) { h = best; continue; }
+            const uint32_t g = __float_as_uint(__ldg(sc.prims + 4 * (size_t)best.prim + 3).y);
+            if (g >= md.geom_lo && g <= md.geom_hi) { h = best; continue; }
+          }
+          cur = md.root;
+          tmin = tmin0;
+          skip_b = kNone;
+          h = Hit{inf, kNone, false};
+          break;
+        }
+        sp = 0;
+      }
+    }
+    // ---- ray fetch: one atomic per warp hands a queue slot to every lane without a ray ----------------------------
+    if (!exhausted) {
+      const uint32_t idle = __ballot_sync(kFull, !active);
+      if (idle) {
+        const int want = __popc(idle), leader = __ffs(idle) - 1;
+        uint32_t base = 0;
+        if ((int)lane == leader) base = atomicAdd(&ctl->trav_next, (unsigned int)want);
+        base = __shfl_sync(kFull, base, leader);
+        exhausted = base + (uint32_t)want >= n;
+        if (!active) {
+          const uint32_t i = base + __popc(idle & ((1u << lane) - 1u));
+          if (i < n) {
+            const float4 o4 = q.o[i], d4 = q.d[i];
+            ray = RayT{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
+            origin_geom = __float_as_uint(d4.w);
+            inv.x = fabsf(ray.d.x) > 1e-30f ? __frcp_rn(ray.d.x) : copysignf(1e30f, ray.d.x);
+            inv.y = fabsf(ray.d.y) > 1e-30f ? __frcp_rn(ray.d.y) : copysignf(1e30f, ray.d.y);
+            inv.z = fabsf(ray.d.z) > 1e-30f ? __frcp_rn(ray.d.z) : copysignf(1e30f, ray.d.z);
+            oinv = ray.o * inv;
+            slot = i;
+            active = true;
+            cur = sc.surface_root;
+            sp = 0;
+            tmin = tmin0;
+            skip_b = kNone;
+            h = Hit{inf, kNone, false};
+            m = 0;
+          }
+        }
+      }
+    }
+    if (__ballot_sync(kFull, active) == 0u) break;
   }
+}
+
+using TraverseFn = void (*)(Ctl*, Queue, const DScene, const RenderArgs);
+template <template <uint32_t> class K>
+static TraverseFn pick_by_features(uint32_t features) {
+  if (features & TF_MOVING) return K<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_MEDIA>::fn();
+  switch (features & (TF_SPHERE | TF_PLANAR | TF_MEDIA)) {
+    case TF_SPHERE: return K<TF_SPHERE>::fn();
+    case TF_PLANAR: return K<TF_PLANAR>::fn();
+    case TF_SPHERE | TF_PLANAR: return K<TF_SPHERE | TF_PLANAR>::fn();
+    case TF_SPHERE | TF_MEDIA: return K<TF_SPHERE | TF_MEDIA>::fn();
+    case TF_PLANAR | TF_MEDIA: return K<TF_PLANAR | TF_MEDIA>::fn();
+    case TF_SPHERE | TF_PLANAR | TF_MEDIA: return K<TF_SPHERE | TF_PLANAR | TF_MEDIA>::fn();
+    default: return K<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_MEDIA>::fn();
+  }
+}
+template <uint32_t F> struct StaticK { static TraverseFn fn() { return k_traverse<F>; } };
+template <uint32_t F> struct PersistentK { static TraverseFn fn() { return k_traverse_p<F>; } };
+// default: persistent warps with dynamic fetch; RT_B200_TRAVERSE=static selects the one-ray-per-thread kernel (A/B runs)
+static TraverseFn pick_traverse(uint32_t features) {
+  const char* e = std::getenv("RT_B200_TRAVERSE");
+  if (e && std::strcmp(e, "static") == 0) return pick_by_features<StaticK>(features);
+  return pick_by_features<PersistentK>(features);
 }
 
 // ---- shading, accumulation, compaction -------------------------------------------------------------------
@@ -225,13 +418,14 @@ __global__ void k_advance(Ctl* ctl) {
   ctl->rays += n_tot;
   ctl->n_cur = ctl->n_next;
   ctl->n_next = 0;
+  ctl->trav_next = 0;
   ctl->iterations += 1;
 }
 
 // ---- deterministic primary-ray probe (parity gate: primitive id + t) --------------------------------------
 __global__ void __launch_bounds__(kTraverseBlock) k_probe(const __grid_constant__ DScene sc, const __grid_constant__ DCamera cam, float time,
                                                           uint32_t* __restrict__ ids, float* __restrict__ ts) {
-  __shared__ uint32_t s_stack[kStackDepth * kTraverseBlock];
+  extern __shared__ uint32_t s_stack[];   // (scene BVH depth + 1) x kTraverseBlock words: a deeper static stack would only eat L1
   const uint32_t n = (uint32_t)cam.W * (uint32_t)cam.H;
   for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
     DCamera const& c = cam;
@@ -496,6 +690,8 @@ static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint
   A.sum = d_sum;
   A.sumsq = d_sumsq;
   A.hits = ds.hits;
+  A.refill = 12;
+  if (const char* e = std::getenv("RT_B200_REFILL")) A.refill = std::min(32, std::max(1, std::atoi(e)));
   Ctl init{};
   init.total_items = total;
   init.pool = ds.pool;
@@ -516,7 +712,9 @@ static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint
   if (timing) { ev_begin = ds.events[kMaxTimed * 4]; ev_end = ds.events[kMaxTimed * 4 + 1]; RT_CUDA(cudaEventRecord(ev_begin, stream)); }
 
   const TraverseFn traverse = pick_traverse(s.flat.features);
-  const int g_trav = ds.sm_count * 8, g_shade = ds.sm_count * 8, g_gen = ds.sm_count * 4;
+  int g_trav = ds.sm_count * 8, g_shade = ds.sm_count * 8, g_gen = ds.sm_count * 4;
+  if (const char* e = std::getenv("RT_B200_TRAV_BLOCKS")) g_trav = ds.sm_count * std::max(1, std::atoi(e));
+  const size_t stack_bytes = (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t);
   uint64_t launches = 0;
   size_t timed = 0;
   uint32_t iter = 0;
@@ -530,7 +728,7 @@ static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint
       const bool t_this = timing && timed < kMaxTimed;
       k_raygen<<<g_gen, kRaygenBlock, 0, stream>>>(ds.ctl, q, A);
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 0], stream);
-      traverse<<<g_trav, kTraverseBlock, 0, stream>>>(ds.ctl, q, ds.d, A);
+      traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, ds.d, A);
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
       k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, ds.d, A);
       if (t_this) { cudaEventRecord(ds.events[timed * 4 + 2], stream); timed++; }
@@ -676,7 +874,7 @@ int32_t rt_probe_primary(RtScene* sp, int32_t device, const RtCamera* rc, double
   float* d_ts = nullptr;
   RT_CUDA(cudaMalloc((void**)&d_ids, n * 4));
   RT_CUDA(cudaMalloc((void**)&d_ts, n * 4));
-  k_probe<<<ds->sm_count * 8, kTraverseBlock, 0, ds->stream>>>(ds->d, cam, (float)time, d_ids, d_ts);
+  k_probe<<<ds->sm_count * 8, kTraverseBlock, (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t), ds->stream>>>(ds->d, cam, (float)time, d_ids, d_ts);
   cudaError_t e = cudaMemcpyAsync(ids, d_ids, n * 4, cudaMemcpyDeviceToHost, ds->stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(ts, d_ts, n * 4, cudaMemcpyDeviceToHost, ds->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ds->stream);

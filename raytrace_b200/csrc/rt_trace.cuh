@@ -223,7 +223,7 @@ __device__ __forceinline__ void closest_hit(const DScene& sc, uint32_t root, con
       else cur = kNone;
     }
     if (cur == kNone) break;
-    const uint32_t first = (cur & ~kLeafBit) >> 3, count = (cur & 7u) + 1u;
+    const uint32_t first = (cur & ~kLeafBit) >> kLeafShift, count = (cur & kLeafCountMask) + 1u;
     for (uint32_t k = 0; k < count; k++) intersect_prim<F>(sc, first + k, ray, tmin, skip_a, skip_b, best);
     if (sp > 0) { sp--; cur = stack[sp * stride]; }
     else cur = kNone;
@@ -253,7 +253,15 @@ __device__ __forceinline__ Hit trace_segment(const DScene& sc, const RayT& ray, 
         bool have_segment = false;
         for (int pass = 0; pass < 2; pass++) {
           Hit h{inf, kNone, false};
-          closest_hit<F>(sc, md.root, ray, qmin, origin_geom, skip_b, stack, stride, h);
+          bool answered = false;
+          if (pass == 0 && md.shared && (best.prim == kNone || best.prim < kMediumBase)) {
+            // boundary ⊆ surfaces (DMedium::shared): a surface miss is a boundary miss, and a surface hit ON the
+            // boundary is the closest boundary hit
+            if (best.prim == kNone) break;
+            const uint32_t g = __float_as_uint(__ldg(sc.prims + 4 * (size_t)best.prim + 3).y);
+            if (g >= md.geom_lo && g <= md.geom_hi) { h = best; answered = true; }
+          }
+          if (!answered) closest_hit<F>(sc, md.root, ray, qmin, origin_geom, skip_b, stack, stride, h);
           if (h.prim == kNone) break;
           if (pass == 0) {
             if (!h.front) { t1 = tmin; t2 = fminf(best.t, h.t); have_segment = true; break; }
