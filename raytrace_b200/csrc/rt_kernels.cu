@@ -1,13 +1,14 @@
 // rt_kernels.cu — the wavefront path tracer (sm_100a) and the CUDA half of the C ABI.
 //
-// One render = a loop of four kernels over a pool of P live paths:
+// One render = a loop of three kernels over a pool of P live paths:
 //   k_raygen   : refill the free tail of the current queue with camera rays (Ray.hs:157-172,229),
 //                Philox counter RNG keyed by (seed; pixel, global sample, bounce, block)
 //   k_traverse : closest hit per live ray — BVH traversal with __ldg float4 node-pair fetches and a
 //                shared-memory short stack; media boundary queries + free-flight sampling
 //   k_shade    : material / texture / redirect-mixture evaluation, radiance accumulation, and
 //                warp-ballot/popc stream compaction of the surviving rays into the next queue
-//   k_advance  : one thread; swaps queue counters (keeps the loop free of host round trips)
+//                (steady state: finished paths are REPLACED in their own slot by new camera paths, nothing moves);
+//                the last block to finish prepares the next iteration (keeps the loop free of host round trips)
 // The host reads the control block back only once per batch of iterations.
 #include <cuda_runtime.h>
 
@@ -34,16 +35,22 @@ namespace rtb {
   } while (0)
 
 constexpr int kTraverseBlock = 128;
-constexpr int kShadeBlock = 128;
+constexpr int kShadeBlock = 256;
 constexpr int kRaygenBlock = 256;
 
 struct Ctl {                      // device-resident control block of one render
   unsigned long long next_item;   // next (sample, pixel) work item to start
   unsigned long long total_items;
   unsigned long long rays;        // path segments traversed so far
-  unsigned int n_cur, n_next;
+  unsigned long long fill_item0;  // this iteration: first work item k_raygen turns into a camera ray
+  unsigned int n_cur, n_next;     // live paths entering the iteration / compacted survivors leaving it
+  unsigned int n_live, fill_lo;   // this iteration: queue slots [0, n_live) are live, [fill_lo, n_live) freshly generated
+  unsigned int inplace;           // this iteration: every finished path can be replaced by a new camera path in its own
+                                  //   slot (enough work items left) → no compaction, the queue stays full
   unsigned int iterations, pool;
-  unsigned int trav_next, _pad;   // next queue slot the persistent traversal warps fetch (reset by k_advance)
+  unsigned int trav_next;         // next queue slot the persistent traversal warps fetch
+  unsigned int blocks_done;       // k_shade blocks finished (the last one prepares the next iteration)
+  unsigned int allow_inplace;
 };
 
 struct Queue {                    // SoA live-ray queue (56 B per path)
@@ -64,10 +71,25 @@ struct RenderArgs {
   int refill;                     // persistent traversal: idle lanes per warp that trigger a fetch
 };
 
-__device__ __forceinline__ uint32_t live_count(const Ctl* ctl) {
-  unsigned long long rem = ctl->total_items - ctl->next_item;
-  unsigned int room = ctl->pool - ctl->n_cur;
-  return ctl->n_cur + (rem < room ? (unsigned int)rem : room);
+// Closes iteration k and prepares iteration k+1 (single thread: the last k_shade block, or k_begin for k = 0).
+__device__ void prepare_iteration(volatile Ctl* ctl, bool first) {
+  unsigned int n_cur = 0;
+  if (!first) {
+    n_cur = ctl->inplace ? ctl->n_live : ctl->n_next;
+    ctl->rays += ctl->n_live;
+    ctl->iterations += 1;
+  }
+  const unsigned long long rem = ctl->total_items - ctl->next_item;
+  const unsigned int room = ctl->pool - n_cur;
+  const unsigned int fill = rem < room ? (unsigned int)rem : room;
+  ctl->n_cur = n_cur;
+  ctl->n_next = 0;
+  ctl->trav_next = 0;
+  ctl->fill_lo = n_cur;
+  ctl->n_live = n_cur + fill;
+  ctl->fill_item0 = ctl->next_item;
+  ctl->next_item += fill;
+  ctl->inplace = (ctl->allow_inplace && n_cur + fill > 0 && ctl->total_items - ctl->next_item >= (unsigned long long)(n_cur + fill)) ? 1u : 0u;
 }
 
 // ---- camera rays -----------------------------------------------------------------------------------
@@ -89,27 +111,32 @@ __device__ __forceinline__ RayT camera_ray(const DCamera& cam, uint32_t pixel, f
   return r;
 }
 
+struct NewPath { RayT ray; uint32_t pixel; uint32_t sample_lo; };
+// work item → camera path (Ray.hs:157-172,229): item = local sample index * n_pixels + pixel
+__device__ __forceinline__ NewPath new_camera_path(const RenderArgs& A, unsigned long long item) {
+  const unsigned long long s_local = item / A.n_pixels;
+  const uint32_t pixel = (uint32_t)(item - s_local * A.n_pixels);
+  const unsigned long long sample = A.first_sample + s_local;
+  const uint4 r0 = rng4(A.key, pixel, sample, 0, RNG_RAYGEN);
+  float lu = 0.f, lv = 0.f;
+  if (A.cam.has_defocus) {
+    const uint4 r1 = rng4(A.key, pixel, sample, 0, RNG_RAYGEN + 1);
+    lu = u01(r1.x);
+    lv = u01(r1.y);
+  }
+  return NewPath{camera_ray(A.cam, pixel, u01(r0.x), lu, lv, u01(r0.y), u01(r0.z)), pixel, (uint32_t)sample};
+}
+
 __global__ void __launch_bounds__(kRaygenBlock) k_raygen(const Ctl* __restrict__ ctl, Queue q, const __grid_constant__ RenderArgs A) {
-  const uint32_t n_cur = ctl->n_cur, n_tot = live_count(ctl);
-  const unsigned long long next = ctl->next_item;
-  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; n_cur + t < n_tot; t += gridDim.x * blockDim.x) {
-    unsigned long long item = next + t;
-    unsigned long long s_local = item / A.n_pixels;
-    uint32_t pixel = (uint32_t)(item - s_local * A.n_pixels);
-    unsigned long long sample = A.first_sample + s_local;
-    uint4 r0 = rng4(A.key, pixel, sample, 0, RNG_RAYGEN);
-    float lu = 0.f, lv = 0.f;
-    if (A.cam.has_defocus) {
-      uint4 r1 = rng4(A.key, pixel, sample, 0, RNG_RAYGEN + 1);
-      lu = u01(r1.x);
-      lv = u01(r1.y);
-    }
-    RayT ray = camera_ray(A.cam, pixel, u01(r0.x), lu, lv, u01(r0.y), u01(r0.z));
-    uint32_t slot = n_cur + t;
-    q.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
-    q.d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(kNone));
-    q.thr[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(pixel));
-    q.meta[slot] = make_uint2((uint32_t)sample, 0u);
+  const uint32_t lo = ctl->fill_lo, n = ctl->n_live;
+  const unsigned long long item0 = ctl->fill_item0;
+  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; lo + t < n; t += gridDim.x * blockDim.x) {
+    const NewPath np = new_camera_path(A, item0 + t);
+    const uint32_t slot = lo + t;
+    q.o[slot] = make_float4(np.ray.o.x, np.ray.o.y, np.ray.o.z, np.ray.time);
+    q.d[slot] = make_float4(np.ray.d.x, np.ray.d.y, np.ray.d.z, __uint_as_float(kNone));
+    q.thr[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(np.pixel));
+    q.meta[slot] = make_uint2(np.sample_lo, 0u);
   }
 }
 
@@ -120,7 +147,7 @@ template <uint32_t F>
 __global__ void __launch_bounds__(kTraverseBlock) k_traverse(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
                                                              const __grid_constant__ RenderArgs A) {
   extern __shared__ uint32_t s_stack[];   // (scene BVH depth + 1) x kTraverseBlock words: a deeper static stack would only eat L1
-  const uint32_t n = live_count(ctl);
+  const uint32_t n = ctl->n_live;
   uint32_t* stack = s_stack + threadIdx.x;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const float4 o4 = q.o[i], d4 = q.d[i];
@@ -158,7 +185,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
   constexpr uint32_t stride = kTraverseBlock;
   constexpr bool kMedia = (F & TF_MEDIA) != 0;
   constexpr uint32_t kFull = 0xFFFFFFFFu;
-  const uint32_t n = live_count(ctl);
+  const uint32_t n = ctl->n_live;
   const uint32_t lane = threadIdx.x & 31u;
   const float tmin0 = 1e-4f;   // Ray.hs:178
   const float inf = __int_as_float(0x7f800000);
@@ -242,8 +269,14 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
                   tmin = h.t;
                   skip_b = __float_as_uint(__ldg(sc.prims + 4 * (size_t)h.prim + 3).y);
                   pass = 1;
-                  cur = sc.media[m - 1].root;
                   h = Hit{inf, kNone, false};
+                  const uint32_t root = sc.media[m - 1].root;
+                  if (root & kLeafBit) {    // boundary is a short primitive list: answer the query right here
+                    const uint32_t first = (root & ~kLeafBit) >> kLeafShift, count = (root & kLeafCountMask) + 1u;
+                    for (uint32_t k = 0; k < count; k++) intersect_prim<F>(sc, first + k, ray, tmin, origin_geom, skip_b, h);
+                    continue;
+                  }
+                  cur = root;
                   break;                                                        // → second boundary query on (t1, inf)
                 }
               }
@@ -276,10 +309,15 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
             const uint32_t g = __float_as_uint(__ldg(sc.prims + 4 * (size_t)best.prim + 3).y);
             if (g >= md.geom_lo && g <= md.geom_hi) { h = best; continue; }
           }
-          cur = md.root;
           tmin = tmin0;
           skip_b = kNone;
           h = Hit{inf, kNone, false};
+          if (md.root & kLeafBit) {
+            const uint32_t first = (md.root & ~kLeafBit) >> kLeafShift, count = (md.root & kLeafCountMask) + 1u;
+            for (uint32_t k = 0; k < count; k++) intersect_prim<F>(sc, first + k, ray, tmin, origin_geom, skip_b, h);
+            continue;
+          }
+          cur = md.root;
           break;
         }
         sp = 0;
@@ -344,10 +382,18 @@ static TraverseFn pick_traverse(uint32_t features) {
 }
 
 // ---- shading, accumulation, compaction -------------------------------------------------------------------
+// One block-iteration = kShadeBlock consecutive queue slots.  Slot reservation is aggregated per BLOCK (warp
+// ballot/popc ranks → shared-memory warp counts → ONE global atomic): the per-warp atomic of round 1 spent half of the
+// kernel waiting on a single contended address (ncu: 49 % of stall samples on the SHFL after it).
+//   inplace = 1 (work items left for every live path): a finished path is replaced by a new camera path in its OWN slot;
+//               the atomic hands out work items; nothing moves, the queue stays full.
+//   inplace = 0 (draining): survivors are compacted into the next queue; the atomic hands out dense slots.
 __global__ void __launch_bounds__(kShadeBlock) k_shade(Ctl* __restrict__ ctl, Queue q, Queue qn, const __grid_constant__ DScene sc,
                                                        const __grid_constant__ RenderArgs A) {
   __shared__ float s_grad[256 * 3];
   __shared__ uint8_t s_perm[3 * 256];
+  __shared__ uint32_t s_cnt[2][kShadeBlock / 32];
+  __shared__ unsigned long long s_base[2];
   if (sc.has_noise) {      // Perlin tables staged in shared memory (Noise.hs:52-92)
     for (int k = threadIdx.x; k < 768; k += blockDim.x) {
       s_grad[k] = sc.noise_grad[k];
@@ -356,14 +402,15 @@ __global__ void __launch_bounds__(kShadeBlock) k_shade(Ctl* __restrict__ ctl, Qu
     __syncthreads();
   }
   const NoiseTab T{s_grad, s_perm};
-  const uint32_t n = live_count(ctl);
-  const uint32_t lane = threadIdx.x & 31u;
-  const uint32_t stride = gridDim.x * blockDim.x;
-  for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < n; base += stride) {
-    const uint32_t i = base + lane;
+  const uint32_t n = ctl->n_live;
+  const bool inplace = ctl->inplace != 0;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  int par = 0;
+  for (uint32_t base = blockIdx.x * kShadeBlock; base < n; base += gridDim.x * kShadeBlock, par ^= 1) {
+    const uint32_t i = base + threadIdx.x;
     bool alive = false;
-    RayT ray;
-    f3 thr;
+    RayT ray{};
+    f3 thr = mk3(0.f, 0.f, 0.f);
     uint32_t origin_geom = kNone, pixel = 0;
     uint2 meta = make_uint2(0, 0);
     if (i < n) {
@@ -394,33 +441,55 @@ __global__ void __launch_bounds__(kShadeBlock) k_shade(Ctl* __restrict__ ctl, Qu
       if (meta.y >= (uint32_t)A.cam.max_depth) alive = false;   // rayColor 0 = zero (Ray.hs:176)
       if (thr.x == 0.f && thr.y == 0.f && thr.z == 0.f) alive = false;   // nothing downstream can contribute
     }
-    // stream compaction: one atomic per warp, ranks from ballot/popc
-    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, alive);
-    if (mask) {
-      uint32_t start = 0;
-      const int leader = __ffs(mask) - 1;
-      if ((int)lane == leader) start = atomicAdd(&ctl->n_next, (unsigned int)__popc(mask));
-      start = __shfl_sync(0xFFFFFFFFu, start, leader);
-      if (alive) {
-        const uint32_t slot = start + __popc(mask & ((1u << lane) - 1u));
-        qn.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
-        qn.d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(origin_geom));
-        qn.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(pixel));
-        qn.meta[slot] = meta;
+    // lanes that need an index from the block's reservation: finished paths (a work item) or survivors (a dense slot)
+    const bool need = inplace ? (i < n && !alive) : alive;
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, need);
+    if (lane == 0) s_cnt[par][warp] = __popc(mask);
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kShadeBlock / 32; w++) {
+      const uint32_t c = s_cnt[par][w];
+      before += (w < (int)warp) ? c : 0u;
+      total += c;
+    }
+    if (threadIdx.x == 0 && total)
+      s_base[par] = inplace ? atomicAdd(&ctl->next_item, (unsigned long long)total)
+                            : (unsigned long long)atomicAdd(&ctl->n_next, total);
+    __syncthreads();
+    const unsigned long long mine = s_base[par] + before + __popc(mask & ((1u << lane) - 1u));
+    uint32_t slot = i;
+    if (inplace) {
+      if (need) {   // path regeneration: Ray.hs:229-231 for the next (pixel, sample) work item
+        const NewPath np = new_camera_path(A, mine);
+        ray = np.ray;
+        thr = mk3(1.f, 1.f, 1.f);
+        pixel = np.pixel;
+        meta = make_uint2(np.sample_lo, 0u);
+        origin_geom = kNone;
+        alive = true;
       }
+    } else slot = (uint32_t)mine;
+    if (alive) {
+      qn.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
+      qn.d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(origin_geom));
+      qn.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(pixel));
+      qn.meta[slot] = meta;
+    }
+  }
+  // the last block to finish closes the iteration and prepares the next (no separate launch, no host round trip)
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&ctl->blocks_done, 1u) == gridDim.x - 1) {
+      __threadfence();
+      ctl->blocks_done = 0;
+      prepare_iteration(ctl, false);
     }
   }
 }
 
-__global__ void k_advance(Ctl* ctl) {
-  const uint32_t n_tot = live_count(ctl);
-  ctl->next_item += n_tot - ctl->n_cur;
-  ctl->rays += n_tot;
-  ctl->n_cur = ctl->n_next;
-  ctl->n_next = 0;
-  ctl->trav_next = 0;
-  ctl->iterations += 1;
-}
+__global__ void k_begin(Ctl* ctl) { prepare_iteration(ctl, true); }
 
 // ---- deterministic primary-ray probe (parity gate: primitive id + t) --------------------------------------
 __global__ void __launch_bounds__(kTraverseBlock) k_probe(const __grid_constant__ DScene sc, const __grid_constant__ DCamera cam, float time,
@@ -671,7 +740,7 @@ static int32_t ensure_workspace(DeviceScene& ds, uint32_t pool, size_t accum_ele
 static uint32_t choose_pool(const Scene& s, unsigned long long total_items) {
   uint32_t pool = s.pool_size;
   if (const char* e = std::getenv("RT_B200_POOL")) pool = (uint32_t)std::strtoul(e, nullptr, 10);
-  if (pool == 0) pool = 1u << 20;
+  if (pool == 0) pool = 1u << 22;   // fewer, larger iterations: launch gaps and kernel tails amortise (sweep in profiles/r01b)
   pool = std::max<uint32_t>(pool, 1024);
   if (total_items < pool) pool = (uint32_t)std::max<unsigned long long>(1024, (total_items + 1023) / 1024 * 1024);
   return pool;
@@ -690,11 +759,14 @@ static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint
   A.sum = d_sum;
   A.sumsq = d_sumsq;
   A.hits = ds.hits;
-  A.refill = 12;
+  A.refill = 20;
   if (const char* e = std::getenv("RT_B200_REFILL")) A.refill = std::min(32, std::max(1, std::atoi(e)));
   Ctl init{};
   init.total_items = total;
   init.pool = ds.pool;
+  init.allow_inplace = 0;   // measured (profiles/r01b): replacing paths in place mixes fresh camera rays with bounced rays inside
+                            // every warp; traversal and shading both lose more to divergence than compaction costs
+  if (const char* e = std::getenv("RT_B200_INPLACE")) init.allow_inplace = std::atoi(e) != 0;
   *ds.h_ctl = init;
   RT_CUDA(cudaMemcpyAsync(ds.ctl, ds.h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, stream));
 
@@ -719,8 +791,12 @@ static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint
   size_t timed = 0;
   uint32_t iter = 0;
   int cur = 0;
-  // first batch: enough iterations to start every sample, afterwards small batches until the pool drains
-  unsigned long long batch = std::max<unsigned long long>(4, total / ds.pool + 2);
+  // The loop is device driven: the last k_shade block prepares the next iteration, the host only launches batches
+  // and reads the 80-byte control block back between them.  Batch length follows the measured consumption of work
+  // items (iterations past the end are empty launches, so the estimate stays a little short).
+  k_begin<<<1, 1, 0, stream>>>(ds.ctl);
+  launches++;
+  unsigned long long batch = 4, prev_started = 0;
   for (;;) {
     for (unsigned long long b = 0; b < batch; b++) {
       Queue& q = ds.q[cur];
@@ -732,15 +808,18 @@ static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
       k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, ds.d, A);
       if (t_this) { cudaEventRecord(ds.events[timed * 4 + 2], stream); timed++; }
-      k_advance<<<1, 1, 0, stream>>>(ds.ctl);
-      launches += 4;
+      launches += 3;
       cur ^= 1;
       iter++;
     }
     RT_CUDA(cudaMemcpyAsync(ds.h_ctl, ds.ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, stream));
     RT_CUDA(cudaStreamSynchronize(stream));
-    if (ds.h_ctl->next_item >= total && ds.h_ctl->n_cur == 0) break;
-    batch = 8;
+    if (ds.h_ctl->n_live == 0) break;
+    const unsigned long long started = ds.h_ctl->next_item, left = total - started;
+    const double per_iter = (double)(started - prev_started) / (double)batch;
+    prev_started = started;
+    if (left > 0 && per_iter >= 1.0) batch = (unsigned long long)std::min(4096.0, std::max(4.0, 0.9 * (double)left / per_iter));
+    else batch = 8;
     if (iter > 100000000u) { set_error("wavefront loop did not terminate"); return RT_ERR_CUDA; }
   }
   if (timing) { RT_CUDA(cudaEventRecord(ev_end, stream)); RT_CUDA(cudaEventSynchronize(ev_end)); }
