@@ -17,6 +17,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -528,12 +530,18 @@ __global__ void k_scale(const float* __restrict__ in, float* __restrict__ out, i
 // =================================================================================================================
 // host side
 // =================================================================================================================
-struct DeviceScene {
+struct DeviceScene {              // one committed scene resident on one device: a single arena allocation
   int device = 0;
   int sm_count = 148;
   DScene d{};
-  std::vector<void*> allocs;
-  // render workspace
+  void* arena = nullptr;
+};
+
+// Render workspace (queues, hit buffer, control block, accumulators, events, stream).  Workspaces belong to the
+// DEVICE, not to a scene: a render borrows one from the per-device free list and returns it, so building a new scene
+// does not re-allocate half a gigabyte, and concurrent renders (GHC safe calls from several OS threads) never share one.
+struct Workspace {
+  int device = 0;
   uint32_t pool = 0;
   Queue q[2]{};
   float2* hits = nullptr;
@@ -543,30 +551,59 @@ struct DeviceScene {
   float* sumsq = nullptr;
   float* out = nullptr;
   size_t accum_elems = 0;
+  std::vector<void*> allocs;
   std::vector<cudaEvent_t> events;
   cudaStream_t stream = nullptr;
+};
+
+static std::mutex g_ws_mutex;
+static std::map<int, std::vector<Workspace*>> g_ws_free;
+
+static void destroy_workspace(Workspace* w) {
+  if (!w) return;
+  for (void* p : w->allocs) cudaFree(p);
+  for (auto e : w->events) cudaEventDestroy(e);
+  if (w->h_ctl) cudaFreeHost(w->h_ctl);
+  if (w->stream) cudaStreamDestroy(w->stream);
+  delete w;
+}
+
+static int32_t acquire_workspace(int device, Workspace** out) {
+  {
+    std::lock_guard<std::mutex> lock(g_ws_mutex);
+    auto& v = g_ws_free[device];
+    if (!v.empty()) { *out = v.back(); v.pop_back(); return RT_OK; }
+  }
+  auto* w = new Workspace();
+  w->device = device;
+  cudaError_t e = cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&w->h_ctl), sizeof(Ctl));
+  if (e != cudaSuccess) {
+    set_error(std::string("workspace creation failed: ") + cudaGetErrorString(e));
+    destroy_workspace(w);
+    return RT_ERR_CUDA;
+  }
+  *out = w;
+  return RT_OK;
+}
+
+static void release_workspace(Workspace* w) {
+  std::lock_guard<std::mutex> lock(g_ws_mutex);
+  auto& v = g_ws_free[w->device];
+  if (v.size() < 4) v.push_back(w);
+  else destroy_workspace(w);
+}
+
+struct WorkspaceLease {           // RAII: returns the workspace on every exit path
+  Workspace* w = nullptr;
+  ~WorkspaceLease() { if (w) release_workspace(w); }
 };
 
 void destroy_device_scene(DeviceScene* d) {
   if (!d) return;
   cudaSetDevice(d->device);
-  for (void* p : d->allocs) cudaFree(p);
-  for (auto e : d->events) cudaEventDestroy(e);
-  if (d->h_ctl) cudaFreeHost(d->h_ctl);
-  if (d->stream) cudaStreamDestroy(d->stream);
+  if (d->arena) cudaFree(d->arena);
   delete d;
-}
-
-template <class T>
-static cudaError_t upload_vec(DeviceScene& ds, const T* src, size_t count, const T** dst) {
-  void* p = nullptr;
-  size_t bytes = std::max<size_t>(count * sizeof(T), 16);
-  cudaError_t e = cudaMalloc(&p, bytes);
-  if (e != cudaSuccess) return e;
-  ds.allocs.push_back(p);
-  if (count) e = cudaMemcpy(p, src, count * sizeof(T), cudaMemcpyHostToDevice);
-  *dst = reinterpret_cast<const T*>(p);
-  return e;
 }
 
 static int32_t check_device(int device) {
@@ -597,25 +634,36 @@ static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
   cudaDeviceGetAttribute(&ds->sm_count, cudaDevAttrMultiProcessorCount, device);
   const FlatScene& f = s.flat;
   DScene& d = ds->d;
-  cudaError_t e = cudaSuccess;
-  auto chk = [&](cudaError_t x) { if (e == cudaSuccess) e = x; };
-  chk(upload_vec(*ds, reinterpret_cast<const float4*>(f.nodes.data()), f.nodes.size() * 2, &d.nodes));
-  chk(upload_vec(*ds, reinterpret_cast<const float4*>(f.prims.data()), f.prims.size() / 4, &d.prims));
-  chk(upload_vec(*ds, reinterpret_cast<const float4*>(f.tri_uv.data()), f.tri_uv.size() / 4, &d.tri_uv));
-  chk(upload_vec(*ds, f.xforms.data(), f.xforms.size(), &d.xforms));
-  chk(upload_vec(*ds, f.materials.data(), f.materials.size(), &d.materials));
-  chk(upload_vec(*ds, f.textures.data(), f.textures.size(), &d.textures));
-  chk(upload_vec(*ds, reinterpret_cast<const float4*>(f.texels.data()), f.texels.size() / 4, &d.texels));
-  chk(upload_vec(*ds, f.canonical.data(), f.canonical.size(), &d.canonical));
-  chk(upload_vec(*ds, f.noise_grad.data(), f.noise_grad.size(), &d.noise_grad));
-  chk(upload_vec(*ds, f.noise_perm.data(), f.noise_perm.size(), &d.noise_perm));
-  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ds->stream, cudaStreamNonBlocking);
-  if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&ds->h_ctl), sizeof(Ctl));
+  // one arena, one staging buffer, one H2D copy (256-byte aligned sections)
+  struct Sec { const void* src; size_t bytes; size_t off; };
+  Sec secs[10] = {
+      {f.nodes.data(), f.nodes.size() * sizeof(DNode), 0},   {f.prims.data(), f.prims.size() * sizeof(float), 0},
+      {f.tri_uv.data(), f.tri_uv.size() * sizeof(float), 0}, {f.xforms.data(), f.xforms.size() * sizeof(DXform), 0},
+      {f.materials.data(), f.materials.size() * sizeof(DMaterial), 0}, {f.textures.data(), f.textures.size() * sizeof(DTexture), 0},
+      {f.texels.data(), f.texels.size() * sizeof(float), 0}, {f.canonical.data(), f.canonical.size() * sizeof(uint32_t), 0},
+      {f.noise_grad.data(), f.noise_grad.size() * sizeof(float), 0}, {f.noise_perm.data(), f.noise_perm.size(), 0}};
+  size_t total_bytes = 0;
+  for (Sec& x : secs) { x.off = total_bytes; total_bytes += (x.bytes + 255) / 256 * 256 + 256; }
+  std::vector<unsigned char> staging(total_bytes, 0);
+  for (const Sec& x : secs) if (x.bytes) std::memcpy(staging.data() + x.off, x.src, x.bytes);
+  cudaError_t e = cudaMalloc(&ds->arena, total_bytes);
+  if (e == cudaSuccess) e = cudaMemcpy(ds->arena, staging.data(), total_bytes, cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
     set_error(std::string("scene upload failed: ") + cudaGetErrorString(e));
     destroy_device_scene(ds);
     return RT_ERR_CUDA;
   }
+  const unsigned char* base = static_cast<const unsigned char*>(ds->arena);
+  d.nodes = reinterpret_cast<const float4*>(base + secs[0].off);
+  d.prims = reinterpret_cast<const float4*>(base + secs[1].off);
+  d.tri_uv = reinterpret_cast<const float4*>(base + secs[2].off);
+  d.xforms = reinterpret_cast<const DXform*>(base + secs[3].off);
+  d.materials = reinterpret_cast<const DMaterial*>(base + secs[4].off);
+  d.textures = reinterpret_cast<const DTexture*>(base + secs[5].off);
+  d.texels = reinterpret_cast<const float4*>(base + secs[6].off);
+  d.canonical = reinterpret_cast<const uint32_t*>(base + secs[7].off);
+  d.noise_grad = reinterpret_cast<const float*>(base + secs[8].off);
+  d.noise_perm = reinterpret_cast<const uint8_t*>(base + secs[9].off);
   std::memcpy(d.media, f.media, sizeof d.media);
   d.n_media = f.n_media;
   d.surface_root = f.surface_root;
@@ -700,7 +748,7 @@ static int32_t make_camera(const RtCamera& c, DCamera* out) {
   return RT_OK;
 }
 
-static int32_t ensure_workspace(DeviceScene& ds, uint32_t pool, size_t accum_elems) {
+static int32_t ensure_workspace(Workspace& ds, uint32_t pool, size_t accum_elems) {
   if (ds.pool != pool) {
     auto drop = [&](void* p) {
       if (!p) return;
@@ -747,7 +795,7 @@ static uint32_t choose_pool(const Scene& s, unsigned long long total_items) {
 }
 
 // the wavefront loop, accumulating UN-normalised sums into d_sum (+ d_sumsq)
-static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint64_t seed, uint64_t first_sample,
+static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DCamera& cam, uint64_t seed, uint64_t first_sample,
                              uint64_t n_samples, float* d_sum, float* d_sumsq, cudaStream_t stream, RtStats* stats) {
   const uint32_t n_pixels = (uint32_t)cam.W * (uint32_t)cam.H;
   const unsigned long long total = (unsigned long long)n_pixels * n_samples;
@@ -784,8 +832,8 @@ static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint
   if (timing) { ev_begin = ds.events[kMaxTimed * 4]; ev_end = ds.events[kMaxTimed * 4 + 1]; RT_CUDA(cudaEventRecord(ev_begin, stream)); }
 
   const TraverseFn traverse = pick_traverse(s.flat.features);
-  int g_trav = ds.sm_count * 8, g_shade = ds.sm_count * 8, g_gen = ds.sm_count * 4;
-  if (const char* e = std::getenv("RT_B200_TRAV_BLOCKS")) g_trav = ds.sm_count * std::max(1, std::atoi(e));
+  int g_trav = dev.sm_count * 8, g_shade = dev.sm_count * 8, g_gen = dev.sm_count * 4;
+  if (const char* e = std::getenv("RT_B200_TRAV_BLOCKS")) g_trav = dev.sm_count * std::max(1, std::atoi(e));
   const size_t stack_bytes = (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t);
   uint64_t launches = 0;
   size_t timed = 0;
@@ -804,9 +852,9 @@ static int32_t run_wavefront(Scene& s, DeviceScene& ds, const DCamera& cam, uint
       const bool t_this = timing && timed < kMaxTimed;
       k_raygen<<<g_gen, kRaygenBlock, 0, stream>>>(ds.ctl, q, A);
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 0], stream);
-      traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, ds.d, A);
+      traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, dev.d, A);
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
-      k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, ds.d, A);
+      k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
       if (t_this) { cudaEventRecord(ds.events[timed * 4 + 2], stream); timed++; }
       launches += 3;
       cur ^= 1;
@@ -890,10 +938,13 @@ int32_t rt_render_device(RtScene* sp, int32_t device, const RtCamera* rc, uint64
   if (stats) std::memset(stats, 0, sizeof *stats);
   if (n_samples == 0) return RT_OK;
   const unsigned long long total = (unsigned long long)cam.W * cam.H * n_samples;
-  st = ensure_workspace(*ds, choose_pool(s, total), 0);
+  WorkspaceLease lease;
+  st = acquire_workspace(device, &lease.w);
   if (st != RT_OK) return st;
-  cudaStream_t stream = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : ds->stream;
-  return run_wavefront(s, *ds, cam, seed, first_sample, n_samples, d_sum, d_sumsq, stream, stats);
+  st = ensure_workspace(*lease.w, choose_pool(s, total), 0);
+  if (st != RT_OK) return st;
+  cudaStream_t stream = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : lease.w->stream;
+  return run_wavefront(s, *ds, *lease.w, cam, seed, first_sample, n_samples, d_sum, d_sumsq, stream, stats);
 }
 
 int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample,
@@ -909,22 +960,26 @@ int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed
   if (stats) std::memset(stats, 0, sizeof *stats);
   const size_t elems = (size_t)cam.W * cam.H * 3;
   const unsigned long long total = (unsigned long long)cam.W * cam.H * n_samples;
-  st = ensure_workspace(*ds, choose_pool(s, std::max<unsigned long long>(total, 1)), elems);
+  WorkspaceLease lease;
+  st = acquire_workspace(device, &lease.w);
   if (st != RT_OK) return st;
-  cudaStream_t stream = ds->stream;
-  RT_CUDA(cudaMemsetAsync(ds->sum, 0, elems * sizeof(float), stream));
-  if (rgb_sumsq_out) RT_CUDA(cudaMemsetAsync(ds->sumsq, 0, elems * sizeof(float), stream));
+  Workspace& ws = *lease.w;
+  st = ensure_workspace(ws, choose_pool(s, std::max<unsigned long long>(total, 1)), elems);
+  if (st != RT_OK) return st;
+  cudaStream_t stream = ws.stream;
+  RT_CUDA(cudaMemsetAsync(ws.sum, 0, elems * sizeof(float), stream));
+  if (rgb_sumsq_out) RT_CUDA(cudaMemsetAsync(ws.sumsq, 0, elems * sizeof(float), stream));
   if (n_samples) {
-    st = run_wavefront(s, *ds, cam, seed, first_sample, n_samples, ds->sum, rgb_sumsq_out ? ds->sumsq : nullptr, stream, stats);
+    st = run_wavefront(s, *ds, ws, cam, seed, first_sample, n_samples, ws.sum, rgb_sumsq_out ? ws.sumsq : nullptr, stream, stats);
     if (st != RT_OK) return st;
   }
   cudaEvent_t c0, c1;
   RT_CUDA(cudaEventCreate(&c0));
   RT_CUDA(cudaEventCreate(&c1));
-  k_scale<<<ds->sm_count * 4, 256, 0, stream>>>(ds->sum, ds->out, (int)elems, 1.0f / (float)cam.spp);   // Ray.hs:232
+  k_scale<<<ds->sm_count * 4, 256, 0, stream>>>(ws.sum, ws.out, (int)elems, 1.0f / (float)cam.spp);   // Ray.hs:232
   RT_CUDA(cudaEventRecord(c0, stream));
-  RT_CUDA(cudaMemcpyAsync(rgb_out, ds->out, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
-  if (rgb_sumsq_out) RT_CUDA(cudaMemcpyAsync(rgb_sumsq_out, ds->sumsq, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  RT_CUDA(cudaMemcpyAsync(rgb_out, ws.out, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  if (rgb_sumsq_out) RT_CUDA(cudaMemcpyAsync(rgb_sumsq_out, ws.sumsq, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
   RT_CUDA(cudaEventRecord(c1, stream));
   RT_CUDA(cudaStreamSynchronize(stream));
   if (stats) {
@@ -948,15 +1003,19 @@ int32_t rt_probe_primary(RtScene* sp, int32_t device, const RtCamera* rc, double
   DCamera cam;
   st = make_camera(*rc, &cam);
   if (st != RT_OK) return st;
+  WorkspaceLease lease;
+  st = acquire_workspace(device, &lease.w);
+  if (st != RT_OK) return st;
+  cudaStream_t stream = lease.w->stream;
   const size_t n = (size_t)cam.W * cam.H;
   uint32_t* d_ids = nullptr;
   float* d_ts = nullptr;
   RT_CUDA(cudaMalloc((void**)&d_ids, n * 4));
   RT_CUDA(cudaMalloc((void**)&d_ts, n * 4));
-  k_probe<<<ds->sm_count * 8, kTraverseBlock, (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t), ds->stream>>>(ds->d, cam, (float)time, d_ids, d_ts);
-  cudaError_t e = cudaMemcpyAsync(ids, d_ids, n * 4, cudaMemcpyDeviceToHost, ds->stream);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(ts, d_ts, n * 4, cudaMemcpyDeviceToHost, ds->stream);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(ds->stream);
+  k_probe<<<ds->sm_count * 8, kTraverseBlock, (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t), stream>>>(ds->d, cam, (float)time, d_ids, d_ts);
+  cudaError_t e = cudaMemcpyAsync(ids, d_ids, n * 4, cudaMemcpyDeviceToHost, stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(ts, d_ts, n * 4, cudaMemcpyDeviceToHost, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
   cudaFree(d_ids);
   cudaFree(d_ts);
   RT_CUDA(e);
