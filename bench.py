@@ -85,13 +85,7 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def split_samples(spp: int, world: int, rank: int):
-    """Sample-range sharding: rank r renders global sample indices [first, first+count) of every
-    pixel; a remainder is spread over the first ranks.  The union over ranks is [0, spp) for any world size."""
-    base, rem = divmod(spp, world)
-    count = base + (1 if rank < rem else 0)
-    first = rank * base + min(rank, rem)
-    return first, count
+from raytrace_b200.multigpu import split_samples  # noqa: E402  (sample-range sharding)
 
 
 def cpu_oracle_rate(world_desc, settings, seed, spp, threads=0):
