@@ -360,6 +360,49 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
   }
 }
 
+
+// ---- flat-list traversal ------------------------------------------------------------------------------------------
+// Scenes whose whole surface geometry is one short list (the reference's `group` of a few primitives: README scene,
+// Cornell box) need no tree and no stack: every lane tests the same primitive at the same time, so the list travels in
+// the KERNEL PARAMETER block and, with the loop unrolled, each record field is an immediate constant-bank operand of
+// the FFMA that uses it — zero loads, zero divergence between lanes.
+struct FlatList {
+  uint32_t n, first, _pad[2];
+  float4 rec[kLeafCap][4];
+};
+constexpr int kFlatBlock = 256;
+
+template <uint32_t F>
+__global__ void __launch_bounds__(kFlatBlock) k_traverse_flat(const Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
+                                                              const __grid_constant__ FlatList L, float2* __restrict__ hits) {
+  const uint32_t n = ctl->n_live;
+  const float inf = __int_as_float(0x7f800000);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4 o4 = q.o[i], d4 = q.d[i];
+    const RayT ray{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
+    const uint32_t origin_geom = __float_as_uint(d4.w);
+    Hit h{inf, kNone, false};
+#pragma unroll
+    for (int k = 0; k < (int)kLeafCap; k++) {
+      if (k >= (int)L.n) break;
+      intersect_rec<F>(sc, ParamRec{L.rec[k]}, L.first + k, ray, 1e-4f, origin_geom, kNone, h);
+    }
+    hits[i] = make_float2(h.front ? h.t : -h.t, __uint_as_float(h.prim));
+  }
+}
+
+using FlatFn = void (*)(const Ctl*, Queue, const DScene, const FlatList, float2*);
+static FlatFn pick_flat(uint32_t features) {
+  if (features & (TF_MOVING | TF_MEDIA)) return nullptr;
+  if (const char* e = std::getenv("RT_B200_TRAVERSE")) if (std::strcmp(e, "flat") != 0) return nullptr;
+  switch (features & (TF_SPHERE | TF_PLANAR)) {
+    case TF_SPHERE: return k_traverse_flat<TF_SPHERE>;
+    case TF_PLANAR: return k_traverse_flat<TF_PLANAR>;
+    case TF_SPHERE | TF_PLANAR: return k_traverse_flat<TF_SPHERE | TF_PLANAR>;
+    default: return nullptr;
+  }
+}
+
 using TraverseFn = void (*)(Ctl*, Queue, const DScene, const RenderArgs);
 template <template <uint32_t> class K>
 static TraverseFn pick_by_features(uint32_t features) {
@@ -535,6 +578,8 @@ struct DeviceScene {              // one committed scene resident on one device:
   int sm_count = 148;
   DScene d{};
   void* arena = nullptr;
+  bool has_flat = false;      // surface geometry is a single leaf: k_traverse_flat applies
+  FlatList flat{};
 };
 
 // Render workspace (queues, hit buffer, control block, accumulators, events, stream).  Workspaces belong to the
@@ -664,6 +709,12 @@ static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
   d.canonical = reinterpret_cast<const uint32_t*>(base + secs[7].off);
   d.noise_grad = reinterpret_cast<const float*>(base + secs[8].off);
   d.noise_perm = reinterpret_cast<const uint8_t*>(base + secs[9].off);
+  if (f.surface_root != kNone && (f.surface_root & kLeafBit)) {
+    ds->flat.first = (f.surface_root & ~kLeafBit) >> kLeafShift;
+    ds->flat.n = (f.surface_root & kLeafCountMask) + 1u;
+    std::memcpy(ds->flat.rec, f.prims.data() + (size_t)ds->flat.first * 16, (size_t)ds->flat.n * 64);
+    ds->has_flat = true;
+  }
   std::memcpy(d.media, f.media, sizeof d.media);
   d.n_media = f.n_media;
   d.surface_root = f.surface_root;
@@ -832,6 +883,7 @@ static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DC
   if (timing) { ev_begin = ds.events[kMaxTimed * 4]; ev_end = ds.events[kMaxTimed * 4 + 1]; RT_CUDA(cudaEventRecord(ev_begin, stream)); }
 
   const TraverseFn traverse = pick_traverse(s.flat.features);
+  const FlatFn flat = dev.has_flat ? pick_flat(s.flat.features) : nullptr;
   int g_trav = dev.sm_count * 8, g_shade = dev.sm_count * 8, g_gen = dev.sm_count * 4;
   if (const char* e = std::getenv("RT_B200_TRAV_BLOCKS")) g_trav = dev.sm_count * std::max(1, std::atoi(e));
   const size_t stack_bytes = (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t);
@@ -852,7 +904,8 @@ static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DC
       const bool t_this = timing && timed < kMaxTimed;
       k_raygen<<<g_gen, kRaygenBlock, 0, stream>>>(ds.ctl, q, A);
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 0], stream);
-      traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, dev.d, A);
+      if (flat) flat<<<dev.sm_count * 8, kFlatBlock, 0, stream>>>(ds.ctl, q, dev.d, dev.flat, ds.hits);
+      else traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, dev.d, A);
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
       k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
       if (t_this) { cudaEventRecord(ds.events[timed * 4 + 2], stream); timed++; }

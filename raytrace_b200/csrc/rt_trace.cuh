@@ -86,16 +86,40 @@ struct Hit {
   bool front;
 };
 
+// fast reciprocal (MUFU.RCP, <= 1 ulp): operands here are never denormal (|n.d| > 1e-8, q != 0)
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// Where a primitive record comes from: global memory (__ldg float4, fetched on demand) ...
+struct GlobalRec {
+  const float4* P;
+  __device__ __forceinline__ float4 meta() const { return __ldg(P + 3); }
+  __device__ __forceinline__ float4 r0() const { return __ldg(P); }
+  __device__ __forceinline__ float4 r1() const { return __ldg(P + 1); }
+  __device__ __forceinline__ float4 r2() const { return __ldg(P + 2); }
+};
+// ... or the kernel parameter block (constant bank: the values become instruction operands, no loads at all) —
+// used by the flat-list kernel, where every lane of a warp tests the same primitive at the same time.
+struct ParamRec {
+  const float4* R;      // 4 consecutive float4 in param space
+  __device__ __forceinline__ float4 meta() const { return R[3]; }
+  __device__ __forceinline__ float4 r0() const { return R[0]; }
+  __device__ __forceinline__ float4 r1() const { return R[1]; }
+  __device__ __forceinline__ float4 r2() const { return R[2]; }
+};
+
 // one primitive; `skip_a` = geometry the ray ORIGIN lies on, `skip_b` = geometry of a hit at tmin
 // that must not be reported again (second boundary query of constantMedium, Geometry.hs:311).
 // F = scene feature bits (TF_*): code for absent primitive kinds / instances is compiled out.
-template <uint32_t F>
-__device__ __forceinline__ void intersect_prim(const DScene& sc, uint32_t i, const RayT& ray, float tmin,
-                                               uint32_t skip_a, uint32_t skip_b, Hit& best) {
-  const float4* P = sc.prims + 4 * (size_t)i;
-  const float4 m4 = __ldg(P + 3);
+template <uint32_t F, class Rec>
+__device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, uint32_t i, const RayT& ray, float tmin,
+                                              uint32_t skip_a, uint32_t skip_b, Hit& best) {
+  const float4 m4 = rec.meta();
   const uint32_t tf = __float_as_uint(m4.x), geom = __float_as_uint(m4.y);
-  const float4 p0 = __ldg(P);
+  const float4 p0 = rec.r0();
   f3 o = ray.o, d = ray.d;
   if constexpr ((F & TF_MOVING) != 0) {
     if (tf & PRIM_FLAG_MOVING) {  // transform / moving instance kept local (Geometry.hs:388-389,452-454)
@@ -112,7 +136,7 @@ __device__ __forceinline__ void intersect_prim(const DScene& sc, uint32_t i, con
     if constexpr ((F & TF_SPHERE) != 0) {
       const bool on_a = geom == skip_a, on_b = geom == skip_b;
       if (tf & PRIM_FLAG_BIG) {  // fp64 up to the discriminant, stable roots in fp32
-        const float4 p1 = __ldg(P + 1);
+        const float4 p1 = rec.r1();
         double cx = (double)p0.x + (double)p1.x, cy = (double)p0.y + (double)p1.y, cz = (double)p0.z + (double)p1.z;
         double r = (double)p0.w + (double)p1.w;
         double ox = cx - (double)o.x, oy = cy - (double)o.y, oz = cz - (double)o.z;
@@ -158,14 +182,15 @@ __device__ __forceinline__ void intersect_prim(const DScene& sc, uint32_t i, con
     } else return;
   } else {
     if constexpr ((F & TF_PLANAR) != 0) {
-      if (geom == skip_a || geom == skip_b) return;
-      const float4 p1 = __ldg(P + 1), p2 = __ldg(P + 2);
+      const float4 p1 = rec.r1();
       f3 q = mk3(p0.x, p0.y, p0.z), n = mk3(p0.w, p1.x, p1.y);
       float denom = dot3(n, d);
-      if (!(fabsf(denom) > 1e-8f)) return;
       f3 qo = q - o;
-      t = __fdividef(dot3(n, qo), denom);
-      if (!(t > tmin && t <= best.t)) return;
+      t = dot3(n, qo) * rcp_approx(denom);
+      // one exit for: parallel ray (Geometry.hs:125), outside the open interval, beyond the closest hit so far,
+      // the primitive the ray starts on / must not report again
+      if (!(fabsf(denom) > 1e-8f && t > tmin && t <= best.t) || geom == skip_a || geom == skip_b) return;
+      const float4 p2 = rec.r2();
       f3 pr = fma3(t, d, -qo);                   // p - q
       float a = dot3(mk3(p1.z, p1.w, p2.x), pr), b = dot3(mk3(p2.y, p2.z, p2.w), pr);
       if ((tf & PRIM_TYPE_MASK) == PRIM_PGRAM) { if (!(0.f <= a && a <= 1.f && 0.f <= b && b <= 1.f)) return; }
@@ -178,6 +203,12 @@ __device__ __forceinline__ void intersect_prim(const DScene& sc, uint32_t i, con
     best.prim = i;
     best.front = front;
   }
+}
+
+template <uint32_t F>
+__device__ __forceinline__ void intersect_prim(const DScene& sc, uint32_t i, const RayT& ray, float tmin,
+                                               uint32_t skip_a, uint32_t skip_b, Hit& best) {
+  intersect_rec<F>(sc, GlobalRec{sc.prims + 4 * (size_t)i}, i, ray, tmin, skip_a, skip_b, best);
 }
 
 // slab test of one 32-byte node against the clipped interval (tmin, tmax]
