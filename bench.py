@@ -51,6 +51,26 @@ def load_peaks():
     return 6650.0, "fallback"
 
 
+def measure_aux_peaks():
+    """FP32 FMA and L2 read peaks of THIS GPU (tools/peaks.cu): denominators MEASURED_PEAKS.json does not hold."""
+    exe = os.path.join(ROOT, "tools", "peaks")
+    try:
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=120).stdout.strip().splitlines()[-1]
+        return json.loads(out)
+    except Exception as e:  # noqa: BLE001
+        return {"error": str(e)}
+
+
+# F_shade of SURVEY §8(d): flops per shaded hit are small next to traversal; the per-ray traversal flops below use the
+# reference's own test counts (oracle counters): 24 per box test, 24 per sphere test, 64 per planar test.
+def flops_per_ray(n_node, n_sph, n_pl):
+    return 24 * n_node + 24 * n_sph + 64 * n_pl
+
+
+# DRAM bytes per k_traverse launch from the committed `ncu --set full` captures (profiles/, per workload; None = not captured)
+NCU_TRAFFIC = {}
+
+
 class ClockSampler:
     """nvidia-smi clocks + throttle reasons sampled DURING the timed region."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -270,16 +290,25 @@ def main():
                "mrays_per_s": cnt["rays"] / cnt["seconds"] / 1e6, "rays_per_sample": cnt["rays"] / cnt["samples"],
                "tests_per_ray": {"box": n_node, "sphere": n_sph, "planar": n_pl}}
     peak, peak_kind = load_peaks()
+    aux = measure_aux_peaks()
     roof = None
+    roof_fp32 = None
     if bytes_per_ray is not None and trav_ms > 0:
         achieved = rays * bytes_per_ray / (trav_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": "k_traverse", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
+                "traffic": NCU_TRAFFIC.get(args.scene), "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
                 "bytes_per_ray_algorithmic": bytes_per_ray, "avg_launch_ms": trav_ms / max(iters, 1),
                 "rays_per_launch": rays / max(iters, 1),
                 "note": "algorithmic bytes = SURVEY 8(d): 32*N_node + 16*N_sphere + 48*N_planar + 128 with the "
                         "reference's per-ray test counts (oracle counters); scene data is L1/L2 resident, so this is "
                         "a rate of algorithmic work, not DRAM traffic"}
+        if aux.get("fp32_fma_tflops"):
+            fl = flops_per_ray(n_node, n_sph, n_pl)
+            ach = rays * fl / (trav_ms * 1e-3) / 1e12
+            roof_fp32 = {"kernel": "k_traverse", "achieved": ach, "peak": aux["fp32_fma_tflops"], "unit": "TFLOP/s",
+                         "frac": ach / aux["fp32_fma_tflops"], "flops_per_ray_algorithmic": fl,
+                         "peak_source": "tools/peaks.cu, measured in this run (FFMA chains)",
+                         "l2_read_gbs_measured": aux.get("l2_read_gbs")}
     e2e_val = total_samples / (statistics.median(e2e_ms) * 1e-3) / 1e6
     line = {
         "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world_size, "steps": args.steps,
@@ -295,7 +324,7 @@ def main():
         "gpu_launches": int(launches),
         "e2e": {"value": e2e_val, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": W * H * 3 * 4,
                 "ms_per_step": statistics.median(e2e_ms)},
-        "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
+        "roofline": roof, "roofline_fp32": roof_fp32, "cpu_baseline": cpu, "clocks": clocks,
         "mean_radiance": lum, "wall_s": t_wall,
     }
     print(json.dumps(line), flush=True)
