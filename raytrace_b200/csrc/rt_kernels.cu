@@ -652,16 +652,25 @@ void destroy_device_scene(DeviceScene* d) {
 }
 
 static int32_t check_device(int device) {
+  static std::mutex mu;
+  static std::map<int, int> major_of;     // cudaGetDeviceProperties costs milliseconds: ask once per device
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
     set_error("no CUDA device visible: raytrace_b200 renders only on an sm_100 GPU (there is no CPU fallback)");
     return RT_ERR_NO_DEVICE;
   }
   if (device < 0 || device >= n) { set_error("device index out of range"); return RT_ERR_INVALID_ARG; }
-  cudaDeviceProp p;
-  RT_CUDA(cudaGetDeviceProperties(&p, device));
-  if (p.major < 10) {
-    set_error(std::string("device '") + p.name + "' is not sm_100 (kernels are built for sm_100a only)");
+  int major = 0;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = major_of.find(device);
+    if (it == major_of.end()) {
+      RT_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+      major_of[device] = major;
+    } else major = it->second;
+  }
+  if (major < 10) {
+    set_error("device " + std::to_string(device) + " is not sm_100 (kernels are built for sm_100a only)");
     return RT_ERR_NO_DEVICE;
   }
   return RT_OK;
