@@ -38,6 +38,9 @@ namespace rtb {
 
 constexpr int kTraverseBlock = 128;
 constexpr int kShadeBlock = 256;
+#ifndef RT_SHADE_MINB
+#define RT_SHADE_MINB 4   // resident k_shade blocks per SM the register allocation must allow (4 → 64 regs)
+#endif
 constexpr int kRaygenBlock = 256;
 
 struct Ctl {                      // device-resident control block of one render
@@ -427,18 +430,64 @@ static TraverseFn pick_traverse(uint32_t features) {
 }
 
 // ---- shading, accumulation, compaction -------------------------------------------------------------------
+// ---- TMA (bulk async copy) + mbarrier helpers: the shading kernel prefetches its next tile of queue records into
+// shared memory while it shades the current one (cp.async.bulk → UBLKCP in SASS) ---------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done)
+                 : "r"(smem_u32(bar)), "r"(parity)
+                 : "memory");
+  }
+}
+
 // One block-iteration = kShadeBlock consecutive queue slots.  Slot reservation is aggregated per BLOCK (warp
 // ballot/popc ranks → shared-memory warp counts → ONE global atomic): the per-warp atomic of round 1 spent half of the
 // kernel waiting on a single contended address (ncu: 49 % of stall samples on the SHFL after it).
 //   inplace = 1 (work items left for every live path): a finished path is replaced by a new camera path in its OWN slot;
 //               the atomic hands out work items; nothing moves, the queue stays full.
 //   inplace = 0 (draining): survivors are compacted into the next queue; the atomic hands out dense slots.
-__global__ void __launch_bounds__(kShadeBlock) k_shade(Ctl* __restrict__ ctl, Queue q, Queue qn, const __grid_constant__ DScene sc,
+__global__ void __launch_bounds__(kShadeBlock, RT_SHADE_MINB) k_shade(Ctl* __restrict__ ctl, Queue q, Queue qn, const __grid_constant__ DScene sc,
                                                        const __grid_constant__ RenderArgs A) {
   __shared__ float s_grad[256 * 3];
   __shared__ uint8_t s_perm[3 * 256];
   __shared__ uint32_t s_cnt[2][kShadeBlock / 32];
   __shared__ unsigned long long s_base[2];
+  // double-buffered tile of queue records, filled by TMA one iteration ahead (16 KB per stage)
+  __shared__ __align__(128) float4 s_o[2][kShadeBlock];
+  __shared__ __align__(128) float4 s_d[2][kShadeBlock];
+  __shared__ __align__(128) float4 s_t[2][kShadeBlock];
+  __shared__ __align__(128) uint2 s_m[2][kShadeBlock];
+  __shared__ __align__(128) float2 s_h[2][kShadeBlock];
+  __shared__ __align__(8) uint64_t s_bar[2];
+  constexpr uint32_t kTileBytes = kShadeBlock * (16 + 16 + 16 + 8 + 8);
+  auto issue_tile = [&](int st, uint32_t base) {   // one thread: arm the barrier, launch the five bulk copies
+    mbar_expect_tx(&s_bar[st], kTileBytes);
+    bulk_g2s(s_o[st], q.o + base, kShadeBlock * 16, &s_bar[st]);
+    bulk_g2s(s_d[st], q.d + base, kShadeBlock * 16, &s_bar[st]);
+    bulk_g2s(s_t[st], q.thr + base, kShadeBlock * 16, &s_bar[st]);
+    bulk_g2s(s_m[st], q.meta + base, kShadeBlock * 8, &s_bar[st]);
+    bulk_g2s(s_h[st], A.hits + base, kShadeBlock * 8, &s_bar[st]);
+  };
+  if (threadIdx.x == 0) {
+    mbar_init(&s_bar[0], 1);
+    mbar_init(&s_bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
   if (sc.has_noise) {      // Perlin tables staged in shared memory (Noise.hs:52-92)
     for (int k = threadIdx.x; k < 768; k += blockDim.x) {
       s_grad[k] = sc.noise_grad[k];
@@ -451,17 +500,27 @@ __global__ void __launch_bounds__(kShadeBlock) k_shade(Ctl* __restrict__ ctl, Qu
   const bool inplace = ctl->inplace != 0;
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   int par = 0;
-  for (uint32_t base = blockIdx.x * kShadeBlock; base < n; base += gridDim.x * kShadeBlock, par ^= 1) {
+  const uint32_t stride = gridDim.x * kShadeBlock;
+  if (threadIdx.x == 0 && blockIdx.x * kShadeBlock < n) issue_tile(0, blockIdx.x * kShadeBlock);
+  uint32_t tile = 0;
+  for (uint32_t base = blockIdx.x * kShadeBlock; base < n; base += stride, par ^= 1, tile++) {
     const uint32_t i = base + threadIdx.x;
+    // prefetch the NEXT tile (tiles never run past the allocation: the pool is a multiple of 1024 slots); the stage it
+    // lands in was last read one iteration ago, before that iteration's __syncthreads
+    if (threadIdx.x == 0 && base + stride < n) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      issue_tile(par ^ 1, base + stride);
+    }
+    mbar_wait(&s_bar[par], (tile >> 1) & 1u);
     bool alive = false;
     RayT ray{};
     f3 thr = mk3(0.f, 0.f, 0.f);
     uint32_t origin_geom = kNone, pixel = 0;
     uint2 meta = make_uint2(0, 0);
     if (i < n) {
-      const float4 o4 = q.o[i], d4 = q.d[i], t4 = q.thr[i];
-      const float2 h2 = A.hits[i];
-      meta = q.meta[i];
+      const float4 o4 = s_o[par][threadIdx.x], d4 = s_d[par][threadIdx.x], t4 = s_t[par][threadIdx.x];
+      const float2 h2 = s_h[par][threadIdx.x];
+      meta = s_m[par][threadIdx.x];
       ray = RayT{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
       thr = mk3(t4.x, t4.y, t4.z);
       pixel = __float_as_uint(t4.w);
@@ -849,7 +908,7 @@ static uint32_t choose_pool(const Scene& s, unsigned long long total_items) {
   uint32_t pool = s.pool_size;
   if (const char* e = std::getenv("RT_B200_POOL")) pool = (uint32_t)std::strtoul(e, nullptr, 10);
   if (pool == 0) pool = 1u << 22;   // fewer, larger iterations: launch gaps and kernel tails amortise (sweep in profiles/r01b)
-  pool = std::max<uint32_t>(pool, 1024);
+  pool = (std::max<uint32_t>(pool, 1024) + 1023u) / 1024u * 1024u;   // whole 256-slot tiles for the TMA prefetch in k_shade
   if (total_items < pool) pool = (uint32_t)std::max<unsigned long long>(1024, (total_items + 1023) / 1024 * 1024);
   return pool;
 }
