@@ -510,7 +510,7 @@ struct Builder {
   uint32_t kLeafMax = 24;
   // A bvhTree subtree with at most kCollapse primitives becomes one leaf (the reference's tree, truncated: same split
   // policy above, a short scan below).  RT_B200_COLLAPSE overrides.
-  uint32_t kCollapse = 1;
+  uint32_t kCollapse = 4;
   // number of primitives below a subtree made only of GROUPs and LEAFs; 0 if it contains a BVH node
   uint32_t flat_count(const RNode& n) const {
     if (n.kind == RNode::LEAF) return 1;

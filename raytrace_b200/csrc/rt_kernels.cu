@@ -74,6 +74,7 @@ struct RenderArgs {
   float* sumsq;
   float2* hits;                   // per queue slot: t, prim (bits)
   int refill;                     // persistent traversal: idle lanes per warp that trigger a fetch
+  int node_burst;                 // persistent traversal: node steps per vote
 };
 
 // Closes iteration k and prepares iteration k+1 (single thread: the last k_shade block, or k_begin for k = 0).
@@ -231,7 +232,10 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
 
     if (n_n + n_p != 0 && n_f < A.refill) {
       if (n_n >= n_p) {
-        if (want_n) {
+        // up to A.node_burst node steps per vote: the vote costs ~20 instructions for every lane, a step ~45 for the
+        // lanes that take it; lanes that reach a leaf early sit out the rest of the burst
+#pragma unroll 1
+        for (int burst = 0; burst < A.node_burst && !(cur & kLeafBit) && want_n; burst++) {
           const float4* N = sc.nodes + 2 * (size_t)cur;
           const float4 l0 = __ldg(N), h0 = __ldg(N + 1), l1 = __ldg(N + 2), h1 = __ldg(N + 3);
           float tn0, tn1;
@@ -258,7 +262,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
     // ---- FINISH step: next query of the segment, or its result --------------------------------------------------
     if (want_f) {
       if constexpr (!kMedia) {
-        A.hits[slot] = make_float2(h.front ? h.t : -h.t, __uint_as_float(h.prim));
+        __stcs(A.hits + slot, make_float2(h.front ? h.t : -h.t, __uint_as_float(h.prim)));
         active = false;
       } else {
         bool have_h = true;          // h holds a boundary / surface answer to evaluate
@@ -288,8 +292,8 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
             } else if (h.prim != kNone) { s1 = t1; s2 = fminf(best.t, h.t); }
             if (s2 >= s1) {
               const DMedium& md = sc.media[m - 1];
-              const uint32_t pixel = __float_as_uint(q.thr[slot].w);
-              const uint2 meta = q.meta[slot];
+              const uint32_t pixel = __float_as_uint(__ldcs(q.thr + slot).w);
+              const uint2 meta = __ldcs(q.meta + slot);
               const unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
               const uint32_t k = m - 1;
               const uint4 rnd = rng4(A.key, pixel, sample, meta.y, RNG_MEDIA + (k >> 2));
@@ -300,7 +304,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
             m++;
           }
           if (m > sc.n_media) {           // all media done: the segment's closest event
-            A.hits[slot] = make_float2(best.front ? best.t : -best.t, __uint_as_float(best.prim));
+            __stcs(A.hits + slot, make_float2(best.front ? best.t : -best.t, __uint_as_float(best.prim)));
             active = false;
             break;
           }
@@ -340,7 +344,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
         if (!active) {
           const uint32_t i = base + __popc(idle & ((1u << lane) - 1u));
           if (i < n) {
-            const float4 o4 = q.o[i], d4 = q.d[i];
+            const float4 o4 = __ldcs(q.o + i), d4 = __ldcs(q.d + i);   // streaming: queue records must not evict the BVH from L1
             ray = RayT{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
             origin_geom = __float_as_uint(d4.w);
             inv.x = fabsf(ray.d.x) > 1e-30f ? __frcp_rn(ray.d.x) : copysignf(1e30f, ray.d.x);
@@ -654,6 +658,7 @@ struct Workspace {
   float* sum = nullptr;
   float* sumsq = nullptr;
   float* out = nullptr;
+  float* h_out = nullptr;     // pinned staging for the image read-back (2 x accum_elems: image, sum of squares)
   size_t accum_elems = 0;
   std::vector<void*> allocs;
   std::vector<cudaEvent_t> events;
@@ -668,6 +673,7 @@ static void destroy_workspace(Workspace* w) {
   for (void* p : w->allocs) cudaFree(p);
   for (auto e : w->events) cudaEventDestroy(e);
   if (w->h_ctl) cudaFreeHost(w->h_ctl);
+  if (w->h_out) cudaFreeHost(w->h_out);
   if (w->stream) cudaStreamDestroy(w->stream);
   delete w;
 }
@@ -893,12 +899,22 @@ static int32_t ensure_workspace(Workspace& ds, uint32_t pool, size_t accum_elems
     ds.pool = pool;
   }
   if (ds.accum_elems < accum_elems) {
+    for (float* old : {ds.sum, ds.sumsq, ds.out}) {
+      if (!old) continue;
+      cudaFree(old);
+      ds.allocs.erase(std::remove(ds.allocs.begin(), ds.allocs.end(), (void*)old), ds.allocs.end());
+    }
+    ds.sum = ds.sumsq = ds.out = nullptr;
+    ds.accum_elems = 0;
     void* p[3] = {nullptr, nullptr, nullptr};
     for (int k = 0; k < 3; k++) {
       RT_CUDA(cudaMalloc(&p[k], accum_elems * sizeof(float)));
       ds.allocs.push_back(p[k]);
     }
     ds.sum = (float*)p[0]; ds.sumsq = (float*)p[1]; ds.out = (float*)p[2];
+    if (ds.h_out) cudaFreeHost(ds.h_out);
+    ds.h_out = nullptr;
+    RT_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ds.h_out), 2 * accum_elems * sizeof(float)));
     ds.accum_elems = accum_elems;
   }
   return RT_OK;
@@ -918,6 +934,10 @@ static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DC
                              uint64_t n_samples, float* d_sum, float* d_sumsq, cudaStream_t stream, RtStats* stats) {
   const uint32_t n_pixels = (uint32_t)cam.W * (uint32_t)cam.H;
   const unsigned long long total = (unsigned long long)n_pixels * n_samples;
+  if (cam.max_depth <= 0) {   // rayColor 0 _ _ = zero (Ray.hs:176): every path is black before its first segment
+    if (stats) { stats->samples = total; stats->pool = ds.pool; }
+    return RT_OK;
+  }
   RenderArgs A{};
   A.cam = cam;
   A.key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
@@ -927,6 +947,8 @@ static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DC
   A.sumsq = d_sumsq;
   A.hits = ds.hits;
   A.refill = 20;
+  A.node_burst = 4;
+  if (const char* e = std::getenv("RT_B200_NODE_BURST")) A.node_burst = std::min(8, std::max(1, std::atoi(e)));
   if (const char* e = std::getenv("RT_B200_REFILL")) A.refill = std::min(32, std::max(1, std::atoi(e)));
   Ctl init{};
   init.total_items = total;
@@ -1099,10 +1121,13 @@ int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed
   RT_CUDA(cudaEventCreate(&c1));
   k_scale<<<ds->sm_count * 4, 256, 0, stream>>>(ws.sum, ws.out, (int)elems, 1.0f / (float)cam.spp);   // Ray.hs:232
   RT_CUDA(cudaEventRecord(c0, stream));
-  RT_CUDA(cudaMemcpyAsync(rgb_out, ws.out, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
-  if (rgb_sumsq_out) RT_CUDA(cudaMemcpyAsync(rgb_sumsq_out, ws.sumsq, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  // device → pinned staging (full PCIe rate, asynchronous) → caller's pageable buffer
+  RT_CUDA(cudaMemcpyAsync(ws.h_out, ws.out, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  if (rgb_sumsq_out) RT_CUDA(cudaMemcpyAsync(ws.h_out + ws.accum_elems, ws.sumsq, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
   RT_CUDA(cudaEventRecord(c1, stream));
   RT_CUDA(cudaStreamSynchronize(stream));
+  std::memcpy(rgb_out, ws.h_out, elems * sizeof(float));
+  if (rgb_sumsq_out) std::memcpy(rgb_sumsq_out, ws.h_out + ws.accum_elems, elems * sizeof(float));
   if (stats) {
     float ms = 0;
     cudaEventElapsedTime(&ms, c0, c1);

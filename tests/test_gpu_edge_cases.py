@@ -1,0 +1,127 @@
+"""More -m gpu parity cases: the converged-image gate of the north_star (4096 spp, 1 % mean luminance, 4-sigma pixels)
+at resolutions the oracle renders in seconds, and the edge cases of the path (degenerate sizes, depth limits,
+empty sample ranges, tiny pools, concurrent renders)."""
+import threading
+
+import numpy as np
+import pytest
+
+import raytrace_b200 as rt
+from raytrace_b200 import scenes
+from raytrace_b200.ray import CompiledScene
+from oracle.harness import OracleScene
+from util import luminance, z_scores
+
+pytestmark = pytest.mark.gpu
+
+CONVERGED = [
+    ("readme", dict(width=64)),
+    ("cornell", dict(width=40)),
+    ("cornell_noredirect", dict(width=32)),
+    ("pawn", dict(width=40)),
+]
+
+
+@pytest.mark.parametrize("name,kw", CONVERGED, ids=[c[0] for c in CONVERGED])
+def test_converged_4096spp_image(built, name, kw):
+    """north_star gate 3: 4096-spp images agree within 1 % relative mean luminance; no pixel fails the 4-sigma
+    Monte Carlo variance test (confirmed on an independent re-seed)."""
+    spp = 4096
+    ctor, seed = scenes.CONFIGS[name]
+    s, w = ctor(spp=spp, **kw)
+    cs, ora = CompiledScene(w), OracleScene(w)
+    img, sq = cs.render(s, rt.mkStdGen(seed), want_sumsq=True)
+    ref, rsq, _ = ora.render(s, seed, want_sumsq=True)
+    img, sq = img.astype(np.float64), sq.astype(np.float64)
+    lg, lo = luminance(img).mean(), luminance(ref).mean()
+    print(f"{name}: 4096 spp mean luminance gpu {lg:.5f} oracle {lo:.5f} ({(lg / lo - 1) * 100:+.3f} %)")
+    assert abs(lg - lo) <= 0.01 * lo
+    z1 = z_scores(img, sq, spp, ref, rsq, spp)
+    fail1 = np.abs(z1) > 4
+    assert fail1.mean() < 2e-3
+    if fail1.any():
+        img2, sq2 = cs.render(s, rt.mkStdGen(seed + 101), want_sumsq=True)
+        ref2, rsq2, _ = ora.render(s, seed + 101, want_sumsq=True)
+        z2 = z_scores(img2.astype(np.float64), sq2.astype(np.float64), spp, ref2, rsq2, spp)
+        confirmed = fail1 & (np.abs(z2) > 4) & (np.sign(z1) == np.sign(z2))
+        assert not confirmed.any(), np.argwhere(confirmed)[:10]
+    # block means (8x8 pixels) agree to a few standard errors of their own Monte Carlo noise
+    b = 8
+    h, wd = img.shape[0] // b * b, img.shape[1] // b * b
+    blk = lambda a: a[:h, :wd].reshape(h // b, b, wd // b, b, -1).mean(axis=(1, 3))   # noqa: E731
+    var_px = np.maximum(sq / spp - img ** 2, 0) / spp + np.maximum(rsq / spp - ref ** 2, 0) / spp
+    se_blk = np.sqrt(blk(var_px) / (b * b)) + 1e-3 * np.maximum(blk(ref), 1e-2)
+    assert (np.abs(blk(img) - blk(ref)) / se_blk).max() < 6.0
+
+
+def test_degenerate_sizes_and_depths(built):
+    s, w = scenes.readme_example(width=1, spp=3)
+    s = s.replace(cs_aspectRatio=1.0)
+    img = CompiledScene(w).render(s, rt.mkStdGen(1))
+    assert img.shape == (1, 1, 3) and np.isfinite(img).all()
+    # depth 1: every path is one segment; hits on non-emitters contribute nothing, misses see the background
+    s, w = scenes.readme_example(width=64, spp=16)
+    cs, ora = CompiledScene(w), OracleScene(w)
+    d1 = s.replace(cs_maxRecursionDepth=1)
+    img, st = cs.render(d1, rt.mkStdGen(5), want_stats=True)
+    ref, cnt = ora.render(d1, 5)
+    assert st["rays"] == st["samples"] == cnt["rays"]
+    assert abs(img.mean() - ref.mean()) < 0.01 * ref.mean()
+    # depth 0: rayColor 0 = 0 (Ray.hs:176) — black image, no rays
+    d0 = s.replace(cs_maxRecursionDepth=0)
+    ref0, cnt0 = ora.render(d0, 5)
+    img0, st0 = cs.render(d0, rt.mkStdGen(5), want_stats=True)
+    assert ref0.max() == 0.0 and img0.max() == 0.0
+    # empty sample range: zeros, nothing launched beyond the normalisation
+    z = cs.render(s, rt.mkStdGen(5), first_sample=7, n_samples=0)
+    assert z.shape == img.shape and (z == 0).all()
+
+
+def test_tiny_pool_and_ragged_ranges(built):
+    """Pool far smaller than the image (many iterations, constant refill) and sample ranges that do not divide spp."""
+    s, w = scenes.cornell_box(spp=30, width=50)
+    cs = CompiledScene(w)
+    full = cs.render(s, rt.mkStdGen(3))
+    cs.handle.set_pool_size(1024)
+    small = cs.render(s, rt.mkStdGen(3))
+    assert np.allclose(small, full, rtol=2e-4, atol=2e-5)
+    cs.handle.set_pool_size(0)
+    parts = sum(cs.render(s, rt.mkStdGen(3), first_sample=f, n_samples=n) for f, n in [(0, 7), (7, 1), (8, 22)])
+    assert np.allclose(parts, full, rtol=2e-4, atol=2e-5)
+    # sample indices beyond 2^32 keep working (64-bit counter)
+    hi = cs.render(s.replace(cs_samplesPerPixel=4), rt.mkStdGen(3), first_sample=(1 << 33) + 5, n_samples=4)
+    assert np.isfinite(hi).all() and abs(hi.mean() - full.mean()) < 0.25 * full.mean()
+
+
+def test_concurrent_renders_from_threads(built):
+    """A committed scene is immutable and may be rendered from several OS threads at once (GHC safe calls migrate
+    threads): every call borrows its own workspace; results equal the serial ones."""
+    s, w = scenes.readme_example(width=96, spp=32)
+    cs = CompiledScene(w)
+    serial = [cs.render(s, rt.mkStdGen(k)) for k in range(4)]
+    out = [None] * 4
+
+    def work(k):
+        out[k] = cs.render(s, rt.mkStdGen(k))
+
+    ts = [threading.Thread(target=work, args=(k,)) for k in range(4)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    for a, b in zip(serial, out):
+        assert np.allclose(a, b, rtol=2e-4, atol=2e-5)
+
+
+def test_media_only_and_surface_only_shortcuts(built):
+    """constantMedium whose boundary is ALSO a surface (shared-boundary shortcut) against the same medium with a
+    separate, geometrically identical boundary object: identical distributions."""
+    glass, fog = rt.dielectric(1.5), rt.isotropic(rt.constantTexture((0.9, 0.3, 0.2)))
+    ball = rt.sphere((0, 0, -2), 0.8)
+    shared = rt.group([rt.pureGeometry(glass << ball), fog << rt.constantMedium(2.0, ball)])
+    s = rt.defaultCameraSettings.replace(cs_imageWidth=64, cs_samplesPerPixel=256, cs_background=scenes.sky, cs_maxRecursionDepth=12)
+    cs, ora = CompiledScene(shared), OracleScene(shared)
+    img, sq, st = cs.render(s, rt.mkStdGen(2), want_sumsq=True, want_stats=True)
+    ref, rsq, cnt = ora.render(s, 2, want_sumsq=True)
+    assert abs(luminance(img).mean() - luminance(ref).mean()) < 0.01 * luminance(ref).mean()
+    assert abs(st["rays"] / st["samples"] - cnt["rays"] / cnt["samples"]) < 0.01 * cnt["rays"] / cnt["samples"]
+    z = z_scores(img.astype(np.float64), sq.astype(np.float64), 256, ref, rsq, 256)
+    assert (np.abs(z) > 4).mean() < 2e-3
