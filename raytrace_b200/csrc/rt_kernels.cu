@@ -75,6 +75,7 @@ struct RenderArgs {
   float2* hits;                   // per queue slot: t, prim (bits)
   int refill;                     // persistent traversal: idle lanes per warp that trigger a fetch
   int node_burst;                 // persistent traversal: node steps per vote
+  uint32_t finish_max;            // k_finish takes over when at most this many paths are left (0 = never)
 };
 
 // Closes iteration k and prepares iteration k+1 (single thread: the last k_shade block, or k_begin for k = 0).
@@ -599,6 +600,68 @@ __global__ void __launch_bounds__(kShadeBlock, RT_SHADE_MINB) k_shade(Ctl* __res
 
 __global__ void k_begin(Ctl* ctl) { prepare_iteration(ctl, true); }
 
+// ---- tail kernel ------------------------------------------------------------------------------------------------
+// Once every camera path has been started and only a few long paths survive (depth up to 50: dozens of nearly empty
+// iterations, three launches each), one launch finishes them: each thread carries ONE path through its remaining
+// segments (closest hit + shading in a loop, no queue traffic).  Same device functions, same RNG counters → the same
+// samples as the wavefront iterations it replaces.  No-op unless the work items are exhausted and n_live <= A.finish_max.
+template <uint32_t F>
+__global__ void __launch_bounds__(kTraverseBlock) k_finish(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
+                                                           const __grid_constant__ RenderArgs A) {
+  extern __shared__ uint32_t s_stack[];
+  __shared__ float s_grad[256 * 3];
+  __shared__ uint8_t s_perm[3 * 256];
+  const uint32_t n = ctl->n_live;
+  if (n == 0 || n > A.finish_max || ctl->next_item < ctl->total_items) return;
+  if (sc.has_noise) {
+    for (int k = threadIdx.x; k < 768; k += blockDim.x) { s_grad[k] = sc.noise_grad[k]; s_perm[k] = sc.noise_perm[k]; }
+    __syncthreads();
+  }
+  const NoiseTab T{s_grad, s_perm};
+  uint32_t* stack = s_stack + threadIdx.x;
+  unsigned int segments = 0;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4 o4 = q.o[i], d4 = q.d[i], t4 = q.thr[i];
+    uint2 meta = q.meta[i];
+    RayT ray{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
+    f3 thr = mk3(t4.x, t4.y, t4.z);
+    const uint32_t pixel = __float_as_uint(t4.w);
+    uint32_t origin_geom = __float_as_uint(d4.w);
+    const unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
+    for (;;) {
+      const Hit hit = trace_segment<F>(sc, ray, origin_geom, true, A.key, pixel, sample, meta.y, stack, kTraverseBlock);
+      segments++;
+      const uint4 rnd = rng4(A.key, pixel, sample, meta.y, RNG_SHADE);
+      f3 contrib;
+      bool alive = shade_bounce(sc, A.cam, T, ray, hit, thr, origin_geom, rnd, contrib);
+      if (contrib.x != 0.f || contrib.y != 0.f || contrib.z != 0.f) {
+        float* s = A.sum + 3 * (size_t)pixel;
+        atomicAdd(s, contrib.x); atomicAdd(s + 1, contrib.y); atomicAdd(s + 2, contrib.z);
+        if (A.sumsq) {
+          float* s2 = A.sumsq + 3 * (size_t)pixel;
+          atomicAdd(s2, contrib.x * contrib.x); atomicAdd(s2 + 1, contrib.y * contrib.y); atomicAdd(s2 + 2, contrib.z * contrib.z);
+        }
+      }
+      meta.y += 1;
+      if (!alive || meta.y >= (uint32_t)A.cam.max_depth || (thr.x == 0.f && thr.y == 0.f && thr.z == 0.f)) break;
+    }
+  }
+  // bookkeeping: segments traced, and (last block) the render is complete
+  for (int o = 16; o > 0; o >>= 1) segments += __shfl_down_sync(0xFFFFFFFFu, segments, o);
+  if ((threadIdx.x & 31) == 0 && segments) atomicAdd(&ctl->rays, (unsigned long long)segments);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&ctl->blocks_done, 1u) == gridDim.x - 1) {
+      ctl->blocks_done = 0;
+      ctl->n_live = 0;
+      ctl->n_cur = 0;
+      ctl->iterations += 1;
+    }
+  }
+}
+template <uint32_t F> struct FinishK { static TraverseFn fn() { return k_finish<F>; } };
+
 // ---- deterministic primary-ray probe (parity gate: primitive id + t) --------------------------------------
 __global__ void __launch_bounds__(kTraverseBlock) k_probe(const __grid_constant__ DScene sc, const __grid_constant__ DCamera cam, float time,
                                                           uint32_t* __restrict__ ids, float* __restrict__ ts) {
@@ -948,6 +1011,8 @@ static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DC
   A.hits = ds.hits;
   A.refill = 20;
   A.node_burst = 4;
+  A.finish_max = 1u << 18;
+  if (const char* e = std::getenv("RT_B200_FINISH")) A.finish_max = (uint32_t)std::strtoul(e, nullptr, 10);
   if (const char* e = std::getenv("RT_B200_NODE_BURST")) A.node_burst = std::min(8, std::max(1, std::atoi(e)));
   if (const char* e = std::getenv("RT_B200_REFILL")) A.refill = std::min(32, std::max(1, std::atoi(e)));
   Ctl init{};
@@ -974,6 +1039,7 @@ static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DC
 
   const TraverseFn traverse = pick_traverse(s.flat.features);
   const FlatFn flat = dev.has_flat ? pick_flat(s.flat.features) : nullptr;
+  const TraverseFn finish = pick_by_features<FinishK>(s.flat.features);
   int g_trav = dev.sm_count * 8, g_shade = dev.sm_count * 8, g_gen = dev.sm_count * 4;
   if (const char* e = std::getenv("RT_B200_TRAV_BLOCKS")) g_trav = dev.sm_count * std::max(1, std::atoi(e));
   const size_t stack_bytes = (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t);
@@ -1003,6 +1069,10 @@ static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DC
       cur ^= 1;
       iter++;
     }
+    if (A.finish_max) {   // device-side decision: no-op until the work items are exhausted and few paths are left
+      finish<<<dev.sm_count * 4, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, ds.q[cur], dev.d, A);
+      launches++;
+    }
     RT_CUDA(cudaMemcpyAsync(ds.h_ctl, ds.ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, stream));
     RT_CUDA(cudaStreamSynchronize(stream));
     if (ds.h_ctl->n_live == 0) break;
@@ -1010,7 +1080,7 @@ static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DC
     const double per_iter = (double)(started - prev_started) / (double)batch;
     prev_started = started;
     if (left > 0 && per_iter >= 1.0) batch = (unsigned long long)std::min(4096.0, std::max(4.0, 0.9 * (double)left / per_iter));
-    else batch = 8;
+    else batch = A.finish_max ? 3 : 8;
     if (iter > 100000000u) { set_error("wavefront loop did not terminate"); return RT_ERR_CUDA; }
   }
   if (timing) { RT_CUDA(cudaEventRecord(ev_end, stream)); RT_CUDA(cudaEventSynchronize(ev_end)); }
