@@ -229,6 +229,12 @@ int32_t rt_render_device(RtScene* scene, int32_t device, const RtCamera* cam, ui
 int32_t rt_probe_primary(RtScene* scene, int32_t device, const RtCamera* cam, double time,
                          uint32_t* prim_id_out, float* t_out);
 
+/* Deterministic shading inputs of the same pixel-centre primary hit: 10 floats per pixel = world normal facing the ray
+ * (HitRecord hr_normal, Core.hs:158), uv (hr_uv), front flag (hr_frontSide), the material's texture colour at the hit
+ * (Texture.hs:15: tex point uv; zero for pitchBlack / dielectric) and the material kind; zeros on a miss or a medium.
+ * HOST buffer H*W*10. */
+int32_t rt_probe_surface(RtScene* scene, int32_t device, const RtCamera* cam, double time, float* out);
+
 /* tuning knobs (0 = default) */
 int32_t rt_set_pool_size(RtScene* scene, uint32_t n_paths);
 

@@ -64,6 +64,7 @@ def lib():
     L.orc_render.argtypes = [vp, C.POINTER(F.RtCamera), C.c_uint64, C.c_int32, C.c_int32, dp, dp,
                              C.POINTER(OrcCounters)]
     L.orc_probe_primary.argtypes = [vp, C.POINTER(F.RtCamera), C.c_double, C.c_double, C.c_double, u32p, dp]
+    L.orc_probe_surface.argtypes = [vp, C.POINTER(F.RtCamera), C.c_double, dp]
     L.orc_perlin.argtypes = [vp, C.c_double, C.c_double, C.c_double]
     L.orc_perlin.restype = C.c_double
     L.orc_fractal.argtypes = [vp, C.c_int32, C.c_double, C.c_double, C.c_double]
@@ -219,6 +220,14 @@ class OracleScene:
                                              ids.ctypes.data_as(C.POINTER(C.c_uint32)),
                                              ts.ctypes.data_as(C.POINTER(C.c_double))))
         return ids, ts
+
+    def probe_surface(self, settings: CameraSettings, time: float = 0.5):
+        """(H, W, 10): normal(3), uv(2), front, texture colour(3), material kind of the pixel-centre primary hit."""
+        cam = self.camera(settings)
+        h, w = imageHeight(settings), settings.cs_imageWidth
+        out = np.zeros((h, w, 10), np.float64)
+        self._check(self.L.orc_probe_surface(self.h, C.byref(cam), float(time), out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
 
     def probe_stable(self, settings: CameraSettings, time: float = 0.5, delta: float = None, t_tol: float = 1e-4,
                      eps_rad: float = 2e-6):

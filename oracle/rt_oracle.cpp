@@ -1061,6 +1061,35 @@ int32_t orc_probe_primary(void* sp, const RtCamera* rc, double time, double dx, 
   return 0;
 }
 
+// Deterministic shading inputs of the pixel-centre primary hit: world normal facing the ray (3), uv (2), front flag,
+// the material's texture colour at the hit (3; zero for texture-less materials) and the material kind.  10 doubles per
+// pixel (zeros on a miss).  Pins hit records, sphereUV, the cuboid uv orientation and every texture (checker / image /
+// Perlin) pointwise, without Monte Carlo noise.
+int32_t orc_probe_surface(void* sp, const RtCamera* rc, double time, double* out) {
+  Scene& s = *(Scene*)sp;
+  if (!s.root) { s.error = "oracle: not committed"; return RT_ERR_NOT_COMMITTED; }
+  Camera cam = makeCamera(*rc);
+  for (int j = 0; j < cam.H; j++)
+    for (int i = 0; i < cam.W; i++) {
+      V3 target = cam.topLeft + ((double)i + 0.5) * cam.pixelU + ((double)j + 0.5) * cam.pixelV;
+      Ray ray{cam.center, normalize(target - cam.center)};
+      Ctx ctx;
+      ctx.rng = mkStdGen(0);
+      ctx.skip_media = true;
+      HitRecord h;
+      const Material* m = nullptr;
+      double* o = out + 10 * ((size_t)j * cam.W + i);
+      for (int k = 0; k < 10; k++) o[k] = 0;
+      if (!s.root->hit(time, ray, 0.0001, INF, ctx, h, m) || !m) continue;
+      o[0] = h.n.x; o[1] = h.n.y; o[2] = h.n.z;
+      hitUV(h, o[3], o[4]);
+      o[5] = h.front ? 1 : 0;
+      if (m->tex) { V3 c = m->tex->eval(h.p, h); o[6] = c.x; o[7] = c.y; o[8] = c.z; }
+      o[9] = m->kind;
+    }
+  return 0;
+}
+
 // unit-test hooks
 double orc_perlin(void* sp, double x, double y, double z) { return perlinNoise(((Scene*)sp)->noise, {x, y, z}); }
 double orc_fractal(void* sp, int32_t depth, double x, double y, double z) { return fractalNoise(((Scene*)sp)->noise, depth, {x, y, z}); }

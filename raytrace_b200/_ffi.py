@@ -100,7 +100,7 @@ EXPORTS = [
     "rt_scene_create", "rt_scene_destroy", "rt_scene_add_texture", "rt_scene_add_material",
     "rt_scene_add_node", "rt_scene_set_noise_tables", "rt_scene_commit", "rt_scene_info",
     "rt_scene_get_bvh", "rt_scene_upload", "rt_image_height", "rt_render", "rt_render_device",
-    "rt_probe_primary", "rt_set_pool_size", "rt_tonemap_u8",
+    "rt_probe_primary", "rt_probe_surface", "rt_set_pool_size", "rt_tonemap_u8",
     "rt_obj_parse", "rt_mesh_sizes", "rt_mesh_data", "rt_mesh_destroy",
 ]
 
@@ -140,6 +140,7 @@ def lib() -> C.CDLL:
                                    C.c_uint64, vp, vp, vp, C.POINTER(RtStats)]
     L.rt_probe_primary.argtypes = [vp, C.c_int32, C.POINTER(RtCamera), C.c_double, u32p,
                                    C.POINTER(C.c_float)]
+    L.rt_probe_surface.argtypes = [vp, C.c_int32, C.POINTER(RtCamera), C.c_double, C.POINTER(C.c_float)]
     L.rt_set_pool_size.argtypes = [vp, C.c_uint32]
     L.rt_tonemap_u8.argtypes = [C.c_int32, C.POINTER(C.c_float), C.c_int32, C.c_int32,
                                 C.POINTER(C.c_uint8)]

@@ -680,6 +680,39 @@ __global__ void __launch_bounds__(kTraverseBlock) k_probe(const __grid_constant_
   }
 }
 
+// ---- deterministic surface probe: what the shader sees at the pixel-centre primary hit ------------------------------
+__global__ void __launch_bounds__(kTraverseBlock) k_probe_surface(const __grid_constant__ DScene sc, const __grid_constant__ DCamera cam,
+                                                                  float time, float* __restrict__ out) {
+  extern __shared__ uint32_t s_stack[];
+  __shared__ float s_grad[256 * 3];
+  __shared__ uint8_t s_perm[3 * 256];
+  for (int k = threadIdx.x; k < 768; k += blockDim.x) { s_grad[k] = sc.noise_grad[k]; s_perm[k] = sc.noise_perm[k]; }
+  __syncthreads();
+  const NoiseTab T{s_grad, s_perm};
+  const uint32_t n = (uint32_t)cam.W * (uint32_t)cam.H;
+  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
+    uint32_t j = p / (uint32_t)cam.W, i = p - j * (uint32_t)cam.W;
+    RayT ray;
+    ray.time = time;
+    ray.o = ld3(cam.center);
+    ray.d = normalize3(fma3((float)i + 0.5f, ld3(cam.pixel_u), fma3((float)j + 0.5f, ld3(cam.pixel_v), ld3(cam.top_left))));
+    Hit h = trace_segment<TF_SPHERE | TF_PLANAR | TF_MOVING>(sc, ray, kNone, false, make_uint2(0, 0), 0, 0, 0, s_stack + threadIdx.x, kTraverseBlock);
+    float* o = out + 10 * (size_t)p;
+    for (int k = 0; k < 10; k++) o[k] = 0.f;
+    if (h.prim == kNone) continue;
+    const Surf s = reconstruct(sc, ray, h);
+    const DMaterial mat = sc.materials[s.material];
+    float u, v;
+    surf_uv(s, u, v);
+    o[0] = s.n.x; o[1] = s.n.y; o[2] = s.n.z; o[3] = u; o[4] = v; o[5] = s.front ? 1.f : 0.f;
+    if (mat.kind != RT_MAT_PITCH_BLACK && mat.kind != RT_MAT_DIELECTRIC) {
+      const f3 c = eval_texture(sc, T, mat.texture, s);
+      o[6] = c.x; o[7] = c.y; o[8] = c.z;
+    }
+    o[9] = (float)mat.kind;
+  }
+}
+
 // ---- image output step (writeImage / writeImageSqrt, Ray.hs:248-260) -----------------------------------------
 __global__ void k_tonemap(const float* __restrict__ rgb, int n, int mode, uint8_t* __restrict__ out) {
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
@@ -1234,6 +1267,30 @@ int32_t rt_probe_primary(RtScene* sp, int32_t device, const RtCamera* rc, double
   if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
   cudaFree(d_ids);
   cudaFree(d_ts);
+  RT_CUDA(e);
+  return RT_OK;
+}
+
+int32_t rt_probe_surface(RtScene* sp, int32_t device, const RtCamera* rc, double time, float* out) {
+  if (!sp || !rc || !out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  Scene& s = *reinterpret_cast<Scene*>(sp);
+  DeviceScene* ds = nullptr;
+  int32_t st = get_device_scene(s, device, &ds);
+  if (st != RT_OK) return st;
+  DCamera cam;
+  st = make_camera(*rc, &cam);
+  if (st != RT_OK) return st;
+  WorkspaceLease lease;
+  st = acquire_workspace(device, &lease.w);
+  if (st != RT_OK) return st;
+  cudaStream_t stream = lease.w->stream;
+  const size_t n = (size_t)cam.W * cam.H * 10;
+  float* d_out = nullptr;
+  RT_CUDA(cudaMalloc((void**)&d_out, n * 4));
+  k_probe_surface<<<ds->sm_count * 8, kTraverseBlock, (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t), stream>>>(ds->d, cam, (float)time, d_out);
+  cudaError_t e = cudaMemcpyAsync(out, d_out, n * 4, cudaMemcpyDeviceToHost, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  cudaFree(d_out);
   RT_CUDA(e);
   return RT_OK;
 }

@@ -207,6 +207,17 @@ class CompiledScene:
                                       ts.ctypes.data_as(C.POINTER(C.c_float))))
         return ids, ts
 
+    def probe_surface(self, settings: CameraSettings, time: float = 0.5):
+        """(H, W, 10) float32: normal(3), uv(2), front, texture colour(3), material kind at the pixel-centre primary hit."""
+        L = _ffi.lib()
+        self.handle.upload(self.device)
+        cam = self.camera(settings)
+        h, w = imageHeight(settings), settings.cs_imageWidth
+        out = np.empty((h, w, 10), dtype=np.float32)
+        _ffi.check(L.rt_probe_surface(self.handle.handle, self.device, C.byref(cam), float(time),
+                                      out.ctypes.data_as(C.POINTER(C.c_float))))
+        return out
+
 
 def raytrace(settings: CameraSettings, world: Geometry, seed: StdGen, device: int = 0) -> np.ndarray:
     """``raytrace :: CameraSettings -> Geometry m Material -> StdGen -> Matrix D Color`` (Ray.hs:121)."""
