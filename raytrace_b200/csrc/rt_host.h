@@ -5,6 +5,7 @@
 #include <cstdint>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -66,6 +67,7 @@ struct Scene {
   FlatScene flat;
   uint32_t pool_size = 0;  // 0 = default
   std::map<int, DeviceScene*> devices;
+  std::mutex devices_mu;   // uploads may race: renders of one committed scene can come from several OS threads
   Scene();
   ~Scene();
 };

@@ -839,6 +839,7 @@ static int32_t check_device(int device) {
 
 static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
   if (!s.committed) { set_error("scene not committed"); return RT_ERR_NOT_COMMITTED; }
+  std::lock_guard<std::mutex> lock(s.devices_mu);
   auto it = s.devices.find(device);
   if (it != s.devices.end()) { *out = it->second; RT_CUDA(cudaSetDevice(device)); return RT_OK; }
   int32_t st = check_device(device);
