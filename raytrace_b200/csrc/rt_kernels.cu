@@ -1020,7 +1020,7 @@ static int32_t ensure_workspace(Workspace& ds, uint32_t pool, size_t accum_elems
 static uint32_t choose_pool(const Scene& s, unsigned long long total_items) {
   uint32_t pool = s.pool_size;
   if (const char* e = std::getenv("RT_B200_POOL")) pool = (uint32_t)std::strtoul(e, nullptr, 10);
-  if (pool == 0) pool = 1u << 22;   // fewer, larger iterations: launch gaps and kernel tails amortise (sweep in profiles/r01b)
+  if (pool == 0) pool = 1u << 24;   // fewer, larger iterations: launch gaps and kernel tails amortise (sweeps in profiles/); 1.9 GB
   pool = (std::max<uint32_t>(pool, 1024) + 1023u) / 1024u * 1024u;   // whole 256-slot tiles for the TMA prefetch in k_shade
   if (total_items < pool) pool = (uint32_t)std::max<unsigned long long>(1024, (total_items + 1023) / 1024 * 1024);
   return pool;
