@@ -69,9 +69,11 @@ def flops_per_ray(n_node, n_sph, n_pl):
 
 # DRAM bytes per k_traverse launch from the committed `ncu --set full` captures (profiles/, per workload; None = not captured)
 NCU_TRAFFIC = {
-    # (workload, kernel): dram__bytes_read.sum + dram__bytes_write.sum per launch, pool 4M (profiles/r01c_ncu_full_summary.txt)
-    ("cornell", "k_shade"): 400.5e6, ("cornell", "k_traverse"): 153.6e6,
-    ("pawn", "k_shade"): 415.8e6, ("pawn", "k_traverse"): 206.2e6,
+    # (workload, kernel): DRAM bytes PER RAY = (dram__bytes_read.sum + dram__bytes_write.sum) / rays of the captured launch
+    # (ncu --set full, full 4 Mi-path launches; profiles/r01c_ncu_full_summary.txt).  The bench line reports
+    # traffic = this x the measured mean rays per launch of the run, so it stays "per launch like achieved".
+    ("cornell", "k_shade"): 400.5e6 / 4194304, ("cornell", "k_traverse"): 153.6e6 / 4194304,
+    ("pawn", "k_shade"): 415.8e6 / 4194304, ("pawn", "k_traverse"): 206.2e6 / 4194304,
 }
 
 
@@ -306,12 +308,13 @@ def main():
         sh_bytes = 64.0 * rays + 56.0 * max(rays - samples_rendered, 0)
         ach = sh_bytes / (shade_ms * 1e-3) / 1e9
         kernels["k_shade"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                              "traffic": NCU_TRAFFIC.get((args.scene, "k_shade")), "bytes_per_ray_algorithmic": sh_bytes / max(rays, 1),
-                              "avg_launch_ms": shade_ms / max(iters, 1), "ms_per_step": shade_ms / args.steps}
+                              "traffic": (NCU_TRAFFIC[(args.scene, "k_shade")] * rays / max(iters, 1)) if (args.scene, "k_shade") in NCU_TRAFFIC else None, "bytes_per_ray_algorithmic": sh_bytes / max(rays, 1),
+                              "avg_launch_ms": shade_ms / max(iters, 1), "ms_per_step": shade_ms / args.steps,
+                              "algorithmic_bytes_per_launch": sh_bytes / max(iters, 1)}
     if bytes_per_ray is not None and trav_ms > 0:
         achieved = rays * bytes_per_ray / (trav_ms * 1e-3) / 1e9
         kernels["k_traverse"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                                 "traffic": NCU_TRAFFIC.get((args.scene, "k_traverse")), "bytes_per_ray_algorithmic": bytes_per_ray,
+                                 "traffic": (NCU_TRAFFIC[(args.scene, "k_traverse")] * rays / max(iters, 1)) if (args.scene, "k_traverse") in NCU_TRAFFIC else None, "bytes_per_ray_algorithmic": bytes_per_ray,
                                  "avg_launch_ms": trav_ms / max(iters, 1), "ms_per_step": trav_ms / args.steps,
                                  "frac_of_measured_l2": achieved / aux["l2_read_gbs"] if aux.get("l2_read_gbs") else None,
                                  "note": "SURVEY 8(d) algorithmic bytes (32*N_node + 16*N_sphere + 48*N_planar + 128, the REFERENCE's "
