@@ -1027,7 +1027,7 @@ static uint32_t choose_pool(const Scene& s, unsigned long long total_items) {
 }
 
 // the wavefront loop, accumulating UN-normalised sums into d_sum (+ d_sumsq)
-static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DCamera& cam, uint64_t seed, uint64_t first_sample,
+static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, const DCamera& cam, uint64_t seed, uint64_t first_sample,
                              uint64_t n_samples, float* d_sum, float* d_sumsq, cudaStream_t stream, RtStats* stats) {
   const uint32_t n_pixels = (uint32_t)cam.W * (uint32_t)cam.H;
   const unsigned long long total = (unsigned long long)n_pixels * n_samples;
@@ -1145,6 +1145,27 @@ static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DC
       stats->ms_raygen = std::max(0.0, (double)ms - tt - tsd);
     }
   }
+  return RT_OK;
+}
+
+// Queue records carry the low 32 bits of the global sample index (the high bits come from first_sample), so a range
+// that crosses a multiple of 2^32 is rendered as two consecutive ranges into the same accumulators.
+static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DCamera& cam, uint64_t seed, uint64_t first_sample,
+                             uint64_t n_samples, float* d_sum, float* d_sumsq, cudaStream_t stream, RtStats* stats) {
+  RtStats total{};
+  while (n_samples) {
+    const uint64_t room = 0x100000000ull - (first_sample & 0xFFFFFFFFull);
+    const uint64_t n = std::min<uint64_t>(n_samples, room);
+    RtStats part{};
+    int32_t st = run_wavefront_range(s, dev, ds, cam, seed, first_sample, n, d_sum, d_sumsq, stream, stats ? &part : nullptr);
+    if (st != RT_OK) return st;
+    total.samples += part.samples; total.rays += part.rays; total.launches += part.launches; total.iterations += part.iterations;
+    total.pool = part.pool; total.ms_total += part.ms_total; total.ms_traverse += part.ms_traverse; total.ms_shade += part.ms_shade;
+    total.ms_raygen += part.ms_raygen;
+    first_sample += n;
+    n_samples -= n;
+  }
+  if (stats) *stats = total;
   return RT_OK;
 }
 

@@ -91,6 +91,12 @@ def test_tiny_pool_and_ragged_ranges(built):
     # sample indices beyond 2^32 keep working (64-bit counter)
     hi = cs.render(s.replace(cs_samplesPerPixel=4), rt.mkStdGen(3), first_sample=(1 << 33) + 5, n_samples=4)
     assert np.isfinite(hi).all() and abs(hi.mean() - full.mean()) < 0.25 * full.mean()
+    # a range that crosses a multiple of 2^32 equals its two halves rendered separately
+    s8 = s.replace(cs_samplesPerPixel=8)
+    cross = cs.render(s8, rt.mkStdGen(3), first_sample=(1 << 32) - 3, n_samples=8)
+    lo = cs.render(s8, rt.mkStdGen(3), first_sample=(1 << 32) - 3, n_samples=3)
+    hi2 = cs.render(s8, rt.mkStdGen(3), first_sample=(1 << 32), n_samples=5)
+    assert np.allclose(cross, lo + hi2, rtol=2e-4, atol=2e-5)
 
 
 def test_concurrent_renders_from_threads(built):
