@@ -393,7 +393,7 @@ __global__ void __launch_bounds__(kFlatBlock) k_traverse_flat(const Ctl* __restr
 #pragma unroll
     for (int k = 0; k < (int)kLeafCap; k++) {
       if (k >= (int)L.n) break;
-      intersect_rec<F>(sc, ParamRec{L.rec[k]}, L.first + k, ray, 1e-4f, origin_geom, kNone, h);
+      intersect_rec<F, ParamRec, true>(sc, ParamRec{L.rec[k]}, L.first + k, ray, 1e-4f, origin_geom, kNone, h);
     }
     hits[i] = make_float2(h.front ? h.t : -h.t, __uint_as_float(h.prim));
   }

@@ -175,12 +175,12 @@ __device__ __forceinline__ float target_pdf(const DTarget& tg, f3 p, f3 dir) {
   float denom = dot3(n, dir);
   if (!(fabsf(denom) > 1e-8f)) return 0.f;
   f3 qo = ld3(tg.origin) - p;
-  float t = dot3(n, qo) / denom;
+  float t = __fdividef(dot3(n, qo), denom);      // 2-ulp fast division: these feed a Monte Carlo weight, not a hit distance
   if (!(t > 0.f)) return 0.f;
   f3 pr = fma3(t, dir, -qo);
   float a = dot3(ld3(tg.wa), pr), b = dot3(ld3(tg.wb), pr);
   if (!(0.f <= a && a <= 1.f && 0.f <= b && b <= 1.f)) return 0.f;
-  return t * t / fabsf(dot3(ld3(tg.crs), dir));
+  return __fdividef(t * t, fabsf(dot3(ld3(tg.crs), dir)));
 }
 
 // One bounce of rayColor (Ray.hs:178-224) after the closest-hit query.  Returns true when the path
@@ -258,14 +258,14 @@ __device__ __forceinline__ bool shade_bounce(const DScene& sc, const DCamera& ca
       float pdf = cam.rem_prob * pdf1;
       for (int k = 0; k < cam.n_targets; k++) pdf = fmaf(cam.targets[k].p, target_pdf(cam.targets[k], s.p, dir), pdf);
       f3 f = eval_texture(sc, T, mat.texture, s);
-      float w = cam.n_targets ? pdf1 / pdf : 1.f;
+      float w = cam.n_targets ? __fdividef(pdf1, pdf) : 1.f;
       if (mat.kind == RT_MAT_LOMMEL_SEELIGER) {                     // Material.hs:56-61
         float mu0 = -dot3(in_dir, s.n), mu1 = dot3(dir, s.n);
-        w *= 0.25f / (mu0 + mu1);
+        w *= __fdividef(0.25f, mu0 + mu1);
       } else if (mat.kind == RT_MAT_ANISOTROPIC) {                  // Material.hs:124-129
         float g = mat.param, mu = dot3(in_dir, dir);
         float b = 1.f + g * g - 2.f * g * mu;
-        w *= (1.f - g * g) / (b * sqrtf(b));
+        w *= __fdividef(1.f - g * g, b * sqrtf(b));
       }
       thr = w * (thr * f);
       break;

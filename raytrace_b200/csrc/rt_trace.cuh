@@ -114,7 +114,9 @@ struct ParamRec {
 // one primitive; `skip_a` = geometry the ray ORIGIN lies on, `skip_b` = geometry of a hit at tmin
 // that must not be reported again (second boundary query of constantMedium, Geometry.hs:311).
 // F = scene feature bits (TF_*): code for absent primitive kinds / instances is compiled out.
-template <uint32_t F, class Rec>
+// kScan: the caller tests primitives in increasing index order with skip_b == kNone (flat-list kernel): an exact tie
+// then always loses to the earlier primitive, and the skip_b comparison disappears.
+template <uint32_t F, class Rec, bool kScan = false>
 __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, uint32_t i, const RayT& ray, float tmin,
                                               uint32_t skip_a, uint32_t skip_b, Hit& best) {
   const float4 m4 = rec.meta();
@@ -134,7 +136,7 @@ __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, u
   const bool is_sphere = (F & TF_PLANAR) == 0 || ((F & TF_SPHERE) != 0 && (tf & PRIM_TYPE_MASK) == PRIM_SPHERE);
   if (is_sphere) {
     if constexpr ((F & TF_SPHERE) != 0) {
-      const bool on_a = geom == skip_a, on_b = geom == skip_b;
+      const bool on_a = geom == skip_a, on_b = !kScan && geom == skip_b;
       if (tf & PRIM_FLAG_BIG) {  // fp64 up to the discriminant, stable roots in fp32
         const float4 p1 = rec.r1();
         double cx = (double)p0.x + (double)p1.x, cy = (double)p0.y + (double)p1.y, cz = (double)p0.z + (double)p1.z;
@@ -189,7 +191,7 @@ __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, u
       t = dot3(n, qo) * rcp_approx(denom);
       // one exit for: parallel ray (Geometry.hs:125), outside the open interval, beyond the closest hit so far,
       // the primitive the ray starts on / must not report again
-      if (!(fabsf(denom) > 1e-8f && t > tmin && t <= best.t) || geom == skip_a || geom == skip_b) return;
+      if (!(fabsf(denom) > 1e-8f && t > tmin && (kScan ? t < best.t : t <= best.t)) || geom == skip_a || (!kScan && geom == skip_b)) return;
       const float4 p2 = rec.r2();
       f3 pr = fma3(t, d, -qo);                   // p - q
       float a = dot3(mk3(p1.z, p1.w, p2.x), pr), b = dot3(mk3(p2.y, p2.z, p2.w), pr);
@@ -198,7 +200,7 @@ __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, u
       front = denom < 0.f;
     } else return;
   }
-  if (t < best.t || (t == best.t && i < best.prim)) {
+  if (t < best.t || (!kScan && t == best.t && i < best.prim)) {
     best.t = t;
     best.prim = i;
     best.front = front;
