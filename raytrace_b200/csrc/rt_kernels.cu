@@ -703,7 +703,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_probe_surface(const __grid_c
     const Surf s = reconstruct(sc, ray, h);
     const DMaterial mat = sc.materials[s.material];
     float u, v;
-    surf_uv(s, u, v);
+    surf_uv(sc, s, u, v);
     o[0] = s.n.x; o[1] = s.n.y; o[2] = s.n.z; o[3] = u; o[4] = v; o[5] = s.front ? 1.f : 0.f;
     if (mat.kind != RT_MAT_PITCH_BLACK && mat.kind != RT_MAT_DIELECTRIC) {
       const f3 c = eval_texture(sc, T, mat.texture, s);

@@ -10,9 +10,11 @@ constexpr float kInvPi = 0.31830988618379067154f;
 
 struct Surf {          // HitRecord (Core.hs:155-162) + what `<$` attached
   f3 p, n;             // world point, unit normal facing the ray
-  f3 uvn;              // sphere: LOCAL outward normal (sphereUV input); planar: (u, v, -)
+  f3 uvn;              // sphere: LOCAL outward normal (sphereUV input); planar: hit point in the primitive's space
   bool front, sphere_uv;
   uint32_t material, geom;
+  uint32_t prim, tf;   // primitive index / type bits: hr_uv is LAZY as in the reference (Geometry.hs:90) — the planar
+                       // coordinates are only computed when a texture reads them (surf_uv)
 };
 
 // ---- hit record from (ray, t, primitive) ----------------------------------------------------------------
@@ -26,6 +28,8 @@ __device__ __forceinline__ Surf reconstruct(const DScene& sc, const RayT& ray, c
     s.uvn = mk3(0.f, 0.f, 0.f);
     s.material = sc.media[hit.prim - kMediumBase].material;
     s.geom = kNone;
+    s.prim = kNone;
+    s.tf = 0;
     return s;
   }
   const float4* P = sc.prims + 4 * (size_t)hit.prim;
@@ -33,6 +37,8 @@ __device__ __forceinline__ Surf reconstruct(const DScene& sc, const RayT& ray, c
   const uint32_t tf = __float_as_uint(m4.x);
   s.geom = __float_as_uint(m4.y);
   s.material = __float_as_uint(m4.w);
+  s.prim = hit.prim;
+  s.tf = tf;
   f3 o = ray.o, d = ray.d;
   const DXform* X = nullptr;
   if (tf & (PRIM_FLAG_MOVING | PRIM_FLAG_UVXFORM)) X = sc.xforms + __float_as_uint(m4.z);
@@ -60,30 +66,38 @@ __device__ __forceinline__ Surf reconstruct(const DScene& sc, const RayT& ray, c
     s.n = s.front ? onw : -onw;
     s.sphere_uv = true;
   } else {
-    const float4 p1 = __ldg(P + 1), p2 = __ldg(P + 2);
+    const float4 p1 = __ldg(P + 1);
     f3 n = mk3(p0.w, p1.x, p1.y);
-    f3 pr = fma3(hit.t, d, o - mk3(p0.x, p0.y, p0.z));
-    float a = dot3(mk3(p1.z, p1.w, p2.x), pr), b = dot3(mk3(p2.y, p2.z, p2.w), pr);
     if (tf & PRIM_FLAG_MOVING) n = mat3(X->A, n);
     s.front = hit.front;
     s.n = s.front ? n : -n;
     s.sphere_uv = false;
-    if ((tf & PRIM_TYPE_MASK) == PRIM_TRI) {                 // Geometry.hs:175
-      const float4 u0 = __ldg(sc.tri_uv + 2 * (size_t)hit.prim), u1 = __ldg(sc.tri_uv + 2 * (size_t)hit.prim + 1);
-      float c0 = 1.f - a - b;
-      s.uvn = mk3(c0 * u0.x + a * u0.z + b * u1.x, c0 * u0.y + a * u0.w + b * u1.y, 0.f);
-    } else s.uvn = mk3(a, b, 0.f);
+    s.uvn = fma3(hit.t, d, o);                               // local-space hit point, for surf_uv
   }
   return s;
 }
 
-__device__ __forceinline__ void surf_uv(const Surf& s, float& u, float& v) {
+__device__ __forceinline__ void surf_uv(const DScene& sc, const Surf& s, float& u, float& v) {
   if (s.sphere_uv) {   // sphereUV, Geometry.hs:100-104
     u = atan2f(s.uvn.x, s.uvn.z) * (0.5f * kInvPi) + 0.5f;
     v = acosf(fminf(1.f, fmaxf(-1.f, -s.uvn.y))) * kInvPi;
-  } else {
-    u = s.uvn.x;
-    v = s.uvn.y;
+  } else if (s.prim == kNone) {   // constantMedium hit: uv = (0, 0) (Geometry.hs:326)
+    u = 0.f;
+    v = 0.f;
+  } else {             // planar coordinates a, b (Geometry.hs:130-131), then the shape's own uv map
+    const float4* P = sc.prims + 4 * (size_t)s.prim;
+    const float4 p0 = __ldg(P), p1 = __ldg(P + 1), p2 = __ldg(P + 2);
+    const f3 pr = s.uvn - mk3(p0.x, p0.y, p0.z);
+    const float a = dot3(mk3(p1.z, p1.w, p2.x), pr), b = dot3(mk3(p2.y, p2.z, p2.w), pr);
+    if ((s.tf & PRIM_TYPE_MASK) == PRIM_TRI) {               // Geometry.hs:175
+      const float4 u0 = __ldg(sc.tri_uv + 2 * (size_t)s.prim), u1 = __ldg(sc.tri_uv + 2 * (size_t)s.prim + 1);
+      const float c0 = 1.f - a - b;
+      u = c0 * u0.x + a * u0.z + b * u1.x;
+      v = c0 * u0.y + a * u0.w + b * u1.y;
+    } else {
+      u = a;
+      v = b;
+    }
   }
 }
 
@@ -134,13 +148,13 @@ __device__ f3 eval_texture(const DScene& sc, const NoiseTab& T, uint32_t id, con
   switch (tx.kind) {
     case RT_TEX_CHECKER: {
       float u, v;
-      surf_uv(s, u, v);
+      surf_uv(sc, s, u, v);
       int i = (int)floorf(u * (float)tx.i0), j = (int)floorf(v * (float)tx.i1);
       return ((i + j) & 1) == 0 ? ld3(tx.c0) : ld3(tx.c1);
     }
     case RT_TEX_IMAGE: {
       float u, v;
-      surf_uv(s, u, v);
+      surf_uv(sc, s, u, v);
       int i = floor_mod((int)floorf(u * (float)tx.w), tx.w);
       int j = floor_mod((int)floorf((1.f - v) * (float)tx.h), tx.h);
       float4 t = __ldg(sc.texels + tx.image_offset + (size_t)j * tx.w + i);
