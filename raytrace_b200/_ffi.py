@@ -13,7 +13,8 @@ from typing import Dict, List, Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+# RT_B200_LIB: an alternative build of the SAME library (A/B runs of compile-time knobs, tools/gpu_sweep.py)
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")
 
 RT_OK = 0
 STATUS_NAMES = {

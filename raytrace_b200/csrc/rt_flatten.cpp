@@ -17,6 +17,8 @@
 //   * primitives are numbered in the reference's evaluation order so that "lower index wins an
 //     exact tie" equals the reference's tie rules (earlier child / left child wins).
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -131,9 +133,15 @@ struct Builder {
   std::vector<HNode> hnodes;
   std::map<std::vector<uint32_t>, uint32_t> xform_ids;
   std::vector<XfState> xforms;      // index = xform id (0 = identity)
-  std::map<std::pair<uint32_t, uint32_t>, uint32_t> canon_first;   // (desc node, sub) -> canonical
-  std::map<std::tuple<uint32_t, uint32_t, uint32_t>, uint32_t> geom_ids;
-  uint32_t next_canonical = 0;
+  // Ids are handed out in blocks of one description node's sub-shapes (1; 6 cuboid faces; a mesh's triangles), at the
+  // node's first encounter: the same numbering as one id per (node, sub) in walk order, with one map lookup per node
+  // instead of one per triangle.
+  std::map<uint32_t, uint32_t> canon_base;                          // desc node -> canonical id of its sub-shape 0
+  std::map<std::pair<uint32_t, uint32_t>, uint32_t> geom_base;      // (desc node, xform) -> geometry id of sub-shape 0
+  uint32_t next_canonical = 0, next_geom = 0;
+  std::vector<uint32_t> memo_chain;
+  uint32_t memo_chain_id = kNone;
+  uint32_t memo_node = kNone, memo_xf = kNone, memo_canon = 0, memo_geom = 0;   // last (node, xform) looked up
   struct MediumRec { double density; int rtree; uint32_t material; };
   std::vector<MediumRec> media;
   std::vector<char> mat_used, tex_used;
@@ -147,29 +155,37 @@ struct Builder {
 
   [[noreturn]] void fail(int32_t st, const std::string& m) { throw FlattenError{st, m}; }
 
-  uint32_t canonical_for(uint32_t node, uint32_t sub) {
-    auto key = std::make_pair(node, sub);
-    auto it = canon_first.find(key);
-    if (it != canon_first.end()) return it->second;
-    uint32_t id = next_canonical++;
-    canon_first[key] = id;
-    return id;
+  uint32_t sub_shapes(uint32_t node) const {
+    const HostNode& n = sc.nodes[node];
+    if (n.kind == RT_NODE_CUBOID) return 6;
+    if (n.kind == RT_NODE_MESH) return (uint32_t)(n.faces.size() / 6);
+    return 1;
   }
-  uint32_t geom_for(uint32_t node, uint32_t sub, uint32_t xf) {
-    auto key = std::make_tuple(node, sub, xf);
-    auto it = geom_ids.find(key);
-    if (it != geom_ids.end()) return it->second;
-    uint32_t id = (uint32_t)geom_ids.size();
-    geom_ids[key] = id;
-    return id;
+  void assign_ids(HPrim& p, uint32_t node, uint32_t sub) {
+    if (node != memo_node || p.xform != memo_xf) {
+      const uint32_t k = sub_shapes(node);
+      auto c = canon_base.find(node);
+      if (c == canon_base.end()) { c = canon_base.emplace(node, next_canonical).first; next_canonical += k; }
+      auto g = geom_base.find({node, p.xform});
+      if (g == geom_base.end()) { g = geom_base.emplace(std::make_pair(node, p.xform), next_geom).first; next_geom += k; }
+      memo_node = node; memo_xf = p.xform; memo_canon = c->second; memo_geom = g->second;
+    }
+    p.canonical = memo_canon + sub;
+    p.geom = memo_geom + sub;
   }
   uint32_t xform_id(const XfState& x) {
     if (x.identity) return 0;
+    if (memo_chain_id != kNone && x.chain == memo_chain) return memo_chain_id;   // consecutive faces of one instance
     auto it = xform_ids.find(x.chain);
-    if (it != xform_ids.end()) return it->second;
-    uint32_t id = (uint32_t)xforms.size();
-    xforms.push_back(x);
-    xform_ids[x.chain] = id;
+    uint32_t id;
+    if (it != xform_ids.end()) id = it->second;
+    else {
+      id = (uint32_t)xforms.size();
+      xforms.push_back(x);
+      xform_ids[x.chain] = id;
+    }
+    memo_chain = x.chain;
+    memo_chain_id = id;
     return id;
   }
 
@@ -210,8 +226,7 @@ struct Builder {
 
   void finish_prim(HPrim& p, const XfState& xf, uint32_t node, uint32_t sub, uint32_t material, const BoxD& local_box) {
     p.xform = xform_id(xf);
-    p.geom = geom_for(node, sub, p.xform);
-    p.canonical = canonical_for(node, sub);
+    assign_ids(p, node, sub);
     p.material = material;
     // world box: corners of the local box mapped forward (at both shutter ends when moving)
     BoxD wb;
@@ -278,17 +293,28 @@ struct Builder {
     return leaf_for(std::move(p), ref);
   }
 
+  // stable sort of node ids by box centre along axis d (sortOn, Geometry.hs:375): keys are gathered once into a
+  // contiguous array instead of being recomputed through two indirections per comparison
+  template <class BoxOf>
+  void sort_by_centre(std::vector<int>& ids, BoxOf box_of, int d) {
+    sort_keys.resize(ids.size());
+    for (size_t i = 0; i < ids.size(); i++) {
+      const BoxD& b = box_of(ids[i]);
+      sort_keys[i] = {(b.lo[d] + b.hi[d]) / 2, ids[i]};
+    }
+    std::stable_sort(sort_keys.begin(), sort_keys.end(),
+                     [](const std::pair<double, int>& a, const std::pair<double, int>& b) { return a.first < b.first; });
+    for (size_t i = 0; i < ids.size(); i++) ids[i] = sort_keys[i].second;
+  }
+  std::vector<std::pair<double, int>> sort_keys;
+
   // ---- reference-policy BVH over RNodes (Geometry.hs:369-377) ------------------------------------
   int bvh_tree(std::vector<int> obs) {
     if (obs.size() == 1) return obs[0];
     BoxD all;
     for (int o : obs) all.join(rnodes[o].ref_box);
     int d = longest_dim(all);
-    std::stable_sort(obs.begin(), obs.end(), [&](int a, int b) {
-      const BoxD& A = rnodes[a].ref_box;
-      const BoxD& B = rnodes[b].ref_box;
-      return (A.lo[d] + A.hi[d]) / 2 < (B.lo[d] + B.hi[d]) / 2;
-    });
+    sort_by_centre(obs, [&](int o) -> const BoxD& { return rnodes[o].ref_box; }, d);
     size_t n = obs.size() / 2;
     std::vector<int> left(obs.begin(), obs.begin() + n), right(obs.begin() + n, obs.end());
     int l = bvh_tree(std::move(left));
@@ -351,6 +377,8 @@ struct Builder {
         static const double def_uv[3][2] = {{0, 0}, {1, 0}, {0, 1}};
         std::vector<int> tris;
         tris.reserve(nf);
+        prims.reserve(prims.size() + nf);
+        rnodes.reserve(rnodes.size() + 2 * nf);
         size_t nv = n.verts.size() / 3, nt = n.uvs.size() / 2;
         for (size_t f = 0; f < nf; f++) {
           const int32_t* fi = &n.faces[6 * f];
@@ -538,9 +566,7 @@ struct Builder {
     BoxD all;
     for (int h : hs) all.join(hnodes[h].box);
     int d = longest_dim(all);
-    std::stable_sort(hs.begin(), hs.end(), [&](int a, int b) {
-      return (hnodes[a].box.lo[d] + hnodes[a].box.hi[d]) / 2 < (hnodes[b].box.lo[d] + hnodes[b].box.hi[d]) / 2;
-    });
+    sort_by_centre(hs, [&](int h) -> const BoxD& { return hnodes[h].box; }, d);
     size_t n = hs.size() / 2;
     std::vector<int> l(hs.begin(), hs.begin() + n), r(hs.begin() + n, hs.end());
     int li = median_build(std::move(l)), ri = median_build(std::move(r));
@@ -750,6 +776,15 @@ void default_noise_tables(int32_t perm[3][256], double grad[256][3]) {
 int32_t flatten_scene(Scene& sc, uint32_t root) {
   try {
     Builder b(sc);
+    // RT_B200_TRACE_COMMIT=1: phase times of the host scene pipeline on stderr (tuning aid)
+    const bool trace = std::getenv("RT_B200_TRACE_COMMIT") != nullptr;
+    auto t_last = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+      if (!trace) return;
+      auto now = std::chrono::steady_clock::now();
+      std::fprintf(stderr, "[rt_b200 commit] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+      t_last = now;
+    };
     if (const char* e = std::getenv("RT_B200_LEAF")) b.kLeafMax = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
     if (const char* e = std::getenv("RT_B200_COLLAPSE")) b.kCollapse = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
     b.mat_used.assign(sc.materials.size(), 0);
@@ -757,8 +792,10 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
     XfState id;
     BoxD rb;
     int surf = b.walk(root, id, kNone, &rb);
+    lap("walk (description tree)");
     if (surf >= 0) b.number(surf, true);
     for (auto& m : b.media) b.number(m.rtree, false);
+    lap("number");
     if (b.media.size() > (size_t)kMaxMedia) b.fail(RT_ERR_UNSUPPORTED, "more than 16 constantMedium volumes in one scene");
 
     FlatScene fs;
@@ -767,6 +804,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
       int h = b.to_device(surf);
       fs.surface_root = b.emit_ref(fs, h, 0, max_depth);
     }
+    lap("surface tree to device");
     std::vector<uint32_t> surf_geoms;
     if (surf >= 0) b.collect_geoms(surf, surf_geoms);
     std::sort(surf_geoms.begin(), surf_geoms.end());
@@ -792,7 +830,9 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
     fs.max_depth = max_depth;
     if (max_depth + 1 > (uint32_t)kStackDepth)
       b.fail(RT_ERR_UNSUPPORTED, "flattened BVH is deeper than the shared-memory traversal stack (32 levels)");
+    lap("media trees to device");
     b.pack_prims(fs);
+    lap("pack primitives");
     if (fs.canonical.size() >= (1u << 26)) b.fail(RT_ERR_UNSUPPORTED, "more than 2^26 primitives");
     for (const HPrim& p : b.prims) {
       if (p.index == kNone) continue;
@@ -829,11 +869,11 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
         d.w = t.d.width; d.h = t.d.height;
         d.image_offset = (uint32_t)(fs.texels.size() / 4);
         size_t n = (size_t)d.w * d.h;
-        fs.texels.reserve(fs.texels.size() + n * 4);
-        for (size_t k = 0; k < n; k++) {
-          fs.texels.push_back(t.image[3 * k]); fs.texels.push_back(t.image[3 * k + 1]);
-          fs.texels.push_back(t.image[3 * k + 2]); fs.texels.push_back(0.f);
-        }
+        const size_t at = fs.texels.size();
+        fs.texels.resize(at + n * 4);
+        float* dst = fs.texels.data() + at;
+        const float* src = t.image.data();
+        for (size_t k = 0; k < n; k++, dst += 4, src += 3) { dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2]; dst[3] = 0.f; }
       }
       if (t.d.kind == RT_TEX_NOISE || t.d.kind == RT_TEX_MARBLE) fs.has_noise = 1;
     }
@@ -845,6 +885,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
         fs.noise_perm[k * 256 + i] = (uint8_t)(sc.perm[k][i] & 255);
       }
     }
+    lap("materials, textures, noise");
     sc.flat = std::move(fs);
     sc.committed = true;
     return RT_OK;

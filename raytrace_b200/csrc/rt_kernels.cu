@@ -5,10 +5,12 @@
 //                Philox counter RNG keyed by (seed; pixel, global sample, bounce, block)
 //   k_traverse : closest hit per live ray — BVH traversal with __ldg float4 node-pair fetches and a
 //                shared-memory short stack; media boundary queries + free-flight sampling
-//   k_shade    : material / texture / redirect-mixture evaluation, radiance accumulation, and
-//                warp-ballot/popc stream compaction of the surviving rays into the next queue
-//                (steady state: finished paths are REPLACED in their own slot by new camera paths, nothing moves);
-//                the last block to finish prepares the next iteration (keeps the loop free of host round trips)
+//                (three variants: flat constant-bank list for leaf-only scenes, persistent vote-scheduled warps for BVH
+//                scenes, static while-while as the A/B baseline)
+//   k_shade    : material / texture / redirect-mixture evaluation, radiance accumulation, and block-aggregated
+//                ballot/popc stream compaction of the surviving rays into the next queue (queue tiles prefetched by TMA
+//                bulk copies); the last block to finish prepares the next iteration (no host round trip, no extra launch)
+//   k_finish   : tail kernel — once few paths are left, one thread carries one path to its end
 // The host reads the control block back only once per batch of iterations.
 #include <cuda_runtime.h>
 
@@ -50,12 +52,9 @@ struct Ctl {                      // device-resident control block of one render
   unsigned long long fill_item0;  // this iteration: first work item k_raygen turns into a camera ray
   unsigned int n_cur, n_next;     // live paths entering the iteration / compacted survivors leaving it
   unsigned int n_live, fill_lo;   // this iteration: queue slots [0, n_live) are live, [fill_lo, n_live) freshly generated
-  unsigned int inplace;           // this iteration: every finished path can be replaced by a new camera path in its own
-                                  //   slot (enough work items left) → no compaction, the queue stays full
   unsigned int iterations, pool;
   unsigned int trav_next;         // next queue slot the persistent traversal warps fetch
   unsigned int blocks_done;       // k_shade blocks finished (the last one prepares the next iteration)
-  unsigned int allow_inplace;
 };
 
 struct Queue {                    // SoA live-ray queue (56 B per path)
@@ -82,7 +81,7 @@ struct RenderArgs {
 __device__ void prepare_iteration(volatile Ctl* ctl, bool first) {
   unsigned int n_cur = 0;
   if (!first) {
-    n_cur = ctl->inplace ? ctl->n_live : ctl->n_next;
+    n_cur = ctl->n_next;
     ctl->rays += ctl->n_live;
     ctl->iterations += 1;
   }
@@ -96,7 +95,6 @@ __device__ void prepare_iteration(volatile Ctl* ctl, bool first) {
   ctl->n_live = n_cur + fill;
   ctl->fill_item0 = ctl->next_item;
   ctl->next_item += fill;
-  ctl->inplace = (ctl->allow_inplace && n_cur + fill > 0 && ctl->total_items - ctl->next_item >= (unsigned long long)(n_cur + fill)) ? 1u : 0u;
 }
 
 // ---- camera rays -----------------------------------------------------------------------------------
@@ -462,30 +460,35 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // One block-iteration = kShadeBlock consecutive queue slots.  Slot reservation is aggregated per BLOCK (warp
 // ballot/popc ranks → shared-memory warp counts → ONE global atomic): the per-warp atomic of round 1 spent half of the
 // kernel waiting on a single contended address (ncu: 49 % of stall samples on the SHFL after it).
-//   inplace = 1 (work items left for every live path): a finished path is replaced by a new camera path in its OWN slot;
-//               the atomic hands out work items; nothing moves, the queue stays full.
-//   inplace = 0 (draining): survivors are compacted into the next queue; the atomic hands out dense slots.
-__global__ void __launch_bounds__(kShadeBlock, RT_SHADE_MINB) k_shade(Ctl* __restrict__ ctl, Queue q, Queue qn, const __grid_constant__ DScene sc,
-                                                       const __grid_constant__ RenderArgs A) {
+// Survivors are compacted into the next queue; the atomic hands out dense slots.  (Replacing finished paths by new camera
+// paths in their own slot — no compaction — was measured and dropped: it mixes fresh camera rays with bounced rays inside
+// warps, traversal +15 %, shading +20 %; profiles/r01b.)
+//
+// FF != 0 (flat scenes, see k_trace_flat below): the closest-hit query runs HERE, over the constant-bank primitive list,
+// instead of being read from `hits`, and with GEN the camera rays of the refilled tail are generated here too — the whole
+// iteration is one launch, and new paths never touch the queue before their first bounce.
+template <uint32_t FF, bool GEN>
+__device__ __forceinline__ void shade_tiles(Ctl* __restrict__ ctl, const Queue& q, const Queue& qn, const DScene& sc, const RenderArgs& A,
+                                            const FlatList* L) {
   __shared__ float s_grad[256 * 3];
   __shared__ uint8_t s_perm[3 * 256];
   __shared__ uint32_t s_cnt[2][kShadeBlock / 32];
-  __shared__ unsigned long long s_base[2];
+  __shared__ uint32_t s_base[2];
   // double-buffered tile of queue records, filled by TMA one iteration ahead (16 KB per stage)
   __shared__ __align__(128) float4 s_o[2][kShadeBlock];
   __shared__ __align__(128) float4 s_d[2][kShadeBlock];
   __shared__ __align__(128) float4 s_t[2][kShadeBlock];
   __shared__ __align__(128) uint2 s_m[2][kShadeBlock];
-  __shared__ __align__(128) float2 s_h[2][kShadeBlock];
+  __shared__ __align__(128) float2 s_h[2][FF ? 1 : kShadeBlock];
   __shared__ __align__(8) uint64_t s_bar[2];
-  constexpr uint32_t kTileBytes = kShadeBlock * (16 + 16 + 16 + 8 + 8);
-  auto issue_tile = [&](int st, uint32_t base) {   // one thread: arm the barrier, launch the five bulk copies
+  constexpr uint32_t kTileBytes = kShadeBlock * (16 + 16 + 16 + 8 + (FF ? 0 : 8));
+  auto issue_tile = [&](int st, uint32_t base) {   // one thread: arm the barrier, launch the bulk copies
     mbar_expect_tx(&s_bar[st], kTileBytes);
     bulk_g2s(s_o[st], q.o + base, kShadeBlock * 16, &s_bar[st]);
     bulk_g2s(s_d[st], q.d + base, kShadeBlock * 16, &s_bar[st]);
     bulk_g2s(s_t[st], q.thr + base, kShadeBlock * 16, &s_bar[st]);
     bulk_g2s(s_m[st], q.meta + base, kShadeBlock * 8, &s_bar[st]);
-    bulk_g2s(s_h[st], A.hits + base, kShadeBlock * 8, &s_bar[st]);
+    if (!FF) bulk_g2s(s_h[st], A.hits + base, kShadeBlock * 8, &s_bar[st]);
   };
   if (threadIdx.x == 0) {
     mbar_init(&s_bar[0], 1);
@@ -502,34 +505,56 @@ __global__ void __launch_bounds__(kShadeBlock, RT_SHADE_MINB) k_shade(Ctl* __res
   }
   const NoiseTab T{s_grad, s_perm};
   const uint32_t n = ctl->n_live;
-  const bool inplace = ctl->inplace != 0;
+  // queue slots below n_stored hold paths written by the previous iteration; with GEN the refilled tail
+  // [fill_lo, n_live) is generated here (its tiles are a suffix of every block's tile sequence: no loads for them)
+  const uint32_t n_stored = GEN ? ctl->fill_lo : n;
+  const unsigned long long item0 = GEN ? ctl->fill_item0 : 0ull;
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   int par = 0;
   const uint32_t stride = gridDim.x * kShadeBlock;
-  if (threadIdx.x == 0 && blockIdx.x * kShadeBlock < n) issue_tile(0, blockIdx.x * kShadeBlock);
+  if (threadIdx.x == 0 && blockIdx.x * kShadeBlock < n_stored) issue_tile(0, blockIdx.x * kShadeBlock);
   uint32_t tile = 0;
   for (uint32_t base = blockIdx.x * kShadeBlock; base < n; base += stride, par ^= 1, tile++) {
     const uint32_t i = base + threadIdx.x;
     // prefetch the NEXT tile (tiles never run past the allocation: the pool is a multiple of 1024 slots); the stage it
     // lands in was last read one iteration ago, before that iteration's __syncthreads
-    if (threadIdx.x == 0 && base + stride < n) {
+    if (threadIdx.x == 0 && base + stride < n_stored) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       issue_tile(par ^ 1, base + stride);
     }
-    mbar_wait(&s_bar[par], (tile >> 1) & 1u);
+    if (base < n_stored) mbar_wait(&s_bar[par], (tile >> 1) & 1u);
     bool alive = false;
     RayT ray{};
     f3 thr = mk3(0.f, 0.f, 0.f);
     uint32_t origin_geom = kNone, pixel = 0;
     uint2 meta = make_uint2(0, 0);
     if (i < n) {
-      const float4 o4 = s_o[par][threadIdx.x], d4 = s_d[par][threadIdx.x], t4 = s_t[par][threadIdx.x];
-      const float2 h2 = s_h[par][threadIdx.x];
-      meta = s_m[par][threadIdx.x];
-      ray = RayT{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
-      thr = mk3(t4.x, t4.y, t4.z);
-      pixel = __float_as_uint(t4.w);
-      Hit hit{fabsf(h2.x), __float_as_uint(h2.y), !(h2.x < 0.f)};
+      if (GEN && i >= n_stored) {   // Ray.hs:229-231 for work item fill_item0 + (slot - fill_lo), as k_raygen numbers them
+        const NewPath np = new_camera_path(A, item0 + (i - n_stored));
+        ray = np.ray;
+        thr = mk3(1.f, 1.f, 1.f);
+        pixel = np.pixel;
+        meta = make_uint2(np.sample_lo, 0u);
+      } else {
+        const float4 o4 = s_o[par][threadIdx.x], d4 = s_d[par][threadIdx.x], t4 = s_t[par][threadIdx.x];
+        meta = s_m[par][threadIdx.x];
+        ray = RayT{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
+        thr = mk3(t4.x, t4.y, t4.z);
+        pixel = __float_as_uint(t4.w);
+        origin_geom = __float_as_uint(d4.w);
+      }
+      Hit hit;
+      if (FF) {   // closest hit over the constant-bank list (same code and order as k_traverse_flat)
+        hit = Hit{__int_as_float(0x7f800000), kNone, false};
+#pragma unroll
+        for (int k = 0; k < (int)kLeafCap; k++) {
+          if (k >= (int)L->n) break;
+          intersect_rec<FF ? FF : TF_SPHERE, ParamRec, true>(sc, ParamRec{L->rec[k]}, L->first + k, ray, 1e-4f, origin_geom, kNone, hit);
+        }
+      } else {
+        const float2 h2 = s_h[par][threadIdx.x];
+        hit = Hit{fabsf(h2.x), __float_as_uint(h2.y), !(h2.x < 0.f)};
+      }
       unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
       uint4 rnd = rng4(A.key, pixel, sample, meta.y, RNG_SHADE);
       f3 contrib;
@@ -550,9 +575,7 @@ __global__ void __launch_bounds__(kShadeBlock, RT_SHADE_MINB) k_shade(Ctl* __res
       if (meta.y >= (uint32_t)A.cam.max_depth) alive = false;   // rayColor 0 = zero (Ray.hs:176)
       if (thr.x == 0.f && thr.y == 0.f && thr.z == 0.f) alive = false;   // nothing downstream can contribute
     }
-    // lanes that need an index from the block's reservation: finished paths (a work item) or survivors (a dense slot)
-    const bool need = inplace ? (i < n && !alive) : alive;
-    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, need);
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, alive);
     if (lane == 0) s_cnt[par][warp] = __popc(mask);
     __syncthreads();
     uint32_t before = 0, total = 0;
@@ -562,24 +585,10 @@ __global__ void __launch_bounds__(kShadeBlock, RT_SHADE_MINB) k_shade(Ctl* __res
       before += (w < (int)warp) ? c : 0u;
       total += c;
     }
-    if (threadIdx.x == 0 && total)
-      s_base[par] = inplace ? atomicAdd(&ctl->next_item, (unsigned long long)total)
-                            : (unsigned long long)atomicAdd(&ctl->n_next, total);
+    if (threadIdx.x == 0 && total) s_base[par] = atomicAdd(&ctl->n_next, total);
     __syncthreads();
-    const unsigned long long mine = s_base[par] + before + __popc(mask & ((1u << lane) - 1u));
-    uint32_t slot = i;
-    if (inplace) {
-      if (need) {   // path regeneration: Ray.hs:229-231 for the next (pixel, sample) work item
-        const NewPath np = new_camera_path(A, mine);
-        ray = np.ray;
-        thr = mk3(1.f, 1.f, 1.f);
-        pixel = np.pixel;
-        meta = make_uint2(np.sample_lo, 0u);
-        origin_geom = kNone;
-        alive = true;
-      }
-    } else slot = (uint32_t)mine;
     if (alive) {
+      const uint32_t slot = s_base[par] + before + __popc(mask & ((1u << lane) - 1u));
       qn.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
       qn.d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(origin_geom));
       qn.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(pixel));
@@ -598,6 +607,37 @@ __global__ void __launch_bounds__(kShadeBlock, RT_SHADE_MINB) k_shade(Ctl* __res
   }
 }
 
+__global__ void __launch_bounds__(kShadeBlock, RT_SHADE_MINB) k_shade(Ctl* __restrict__ ctl, Queue q, Queue qn, const __grid_constant__ DScene sc,
+                                                                      const __grid_constant__ RenderArgs A) {
+  shade_tiles<0, false>(ctl, q, qn, sc, A, nullptr);
+}
+
+// Flat scenes (no BVH, no media, no moving instances): raygen + closest hit + shading + compaction of one wavefront
+// iteration in ONE launch.  The traversal part is issue-bound (constant-bank FFMAs), the shading part waits on HBM and
+// atomics: in one kernel the warp schedulers overlap the two, and the `hits` round trip (16 B per ray), the second read
+// of origin/direction (32 B) and the first write + read of every new camera path (112 B) disappear.
+#ifndef RT_TRACE_FLAT_MINB
+#define RT_TRACE_FLAT_MINB 4
+#endif
+template <uint32_t F>
+__global__ void __launch_bounds__(kShadeBlock, RT_TRACE_FLAT_MINB) k_trace_flat(Ctl* __restrict__ ctl, Queue q, Queue qn, const __grid_constant__ DScene sc,
+                                                                                const __grid_constant__ RenderArgs A,
+                                                                                const __grid_constant__ FlatList L) {
+  shade_tiles<F, true>(ctl, q, qn, sc, A, &L);
+}
+
+using TraceFlatFn = void (*)(Ctl*, Queue, Queue, const DScene, const RenderArgs, const FlatList);
+static TraceFlatFn pick_trace_flat(uint32_t features) {
+  if (features & (TF_MOVING | TF_MEDIA)) return nullptr;
+  if (const char* e = std::getenv("RT_B200_TRAVERSE")) if (std::strcmp(e, "fused") != 0) return nullptr;
+  switch (features & (TF_SPHERE | TF_PLANAR)) {
+    case TF_SPHERE: return k_trace_flat<TF_SPHERE>;
+    case TF_PLANAR: return k_trace_flat<TF_PLANAR>;
+    case TF_SPHERE | TF_PLANAR: return k_trace_flat<TF_SPHERE | TF_PLANAR>;
+    default: return nullptr;
+  }
+}
+
 __global__ void k_begin(Ctl* ctl) { prepare_iteration(ctl, true); }
 
 // ---- tail kernel ------------------------------------------------------------------------------------------------
@@ -612,7 +652,9 @@ __global__ void __launch_bounds__(kTraverseBlock) k_finish(Ctl* __restrict__ ctl
   __shared__ float s_grad[256 * 3];
   __shared__ uint8_t s_perm[3 * 256];
   const uint32_t n = ctl->n_live;
-  if (n == 0 || n > A.finish_max || ctl->next_item < ctl->total_items) return;
+  // not yet: work items left, too many paths, or the prepared iteration still has camera rays to generate in
+  // [fill_lo, n_live) (those slots hold no paths until k_raygen / k_trace_flat has run)
+  if (n == 0 || n > A.finish_max || ctl->next_item < ctl->total_items || ctl->fill_lo != n) return;
   if (sc.has_noise) {
     for (int k = threadIdx.x; k < 768; k += blockDim.x) { s_grad[k] = sc.noise_grad[k]; s_perm[k] = sc.noise_perm[k]; }
     __syncthreads();
@@ -1052,9 +1094,6 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   Ctl init{};
   init.total_items = total;
   init.pool = ds.pool;
-  init.allow_inplace = 0;   // measured (profiles/r01b): replacing paths in place mixes fresh camera rays with bounced rays inside
-                            // every warp; traversal and shading both lose more to divergence than compaction costs
-  if (const char* e = std::getenv("RT_B200_INPLACE")) init.allow_inplace = std::atoi(e) != 0;
   *ds.h_ctl = init;
   RT_CUDA(cudaMemcpyAsync(ds.ctl, ds.h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, stream));
 
@@ -1073,6 +1112,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
 
   const TraverseFn traverse = pick_traverse(s.flat.features);
   const FlatFn flat = dev.has_flat ? pick_flat(s.flat.features) : nullptr;
+  const TraceFlatFn fused = dev.has_flat ? pick_trace_flat(s.flat.features) : nullptr;
   const TraverseFn finish = pick_by_features<FinishK>(s.flat.features);
   int g_trav = dev.sm_count * 8, g_shade = dev.sm_count * 8, g_gen = dev.sm_count * 4;
   if (const char* e = std::getenv("RT_B200_TRAV_BLOCKS")) g_trav = dev.sm_count * std::max(1, std::atoi(e));
@@ -1092,14 +1132,20 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
       Queue& q = ds.q[cur];
       Queue& qn = ds.q[cur ^ 1];
       const bool t_this = timing && timed < kMaxTimed;
-      k_raygen<<<g_gen, kRaygenBlock, 0, stream>>>(ds.ctl, q, A);
-      if (t_this) cudaEventRecord(ds.events[timed * 4 + 0], stream);
-      if (flat) flat<<<dev.sm_count * 8, kFlatBlock, 0, stream>>>(ds.ctl, q, dev.d, dev.flat, ds.hits);
-      else traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, dev.d, A);
-      if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
-      k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
+      if (fused) {   // one launch per iteration; reported as shade time (ms_traverse = ms_raygen = 0)
+        if (t_this) { cudaEventRecord(ds.events[timed * 4 + 0], stream); cudaEventRecord(ds.events[timed * 4 + 1], stream); }
+        fused<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A, dev.flat);
+        launches += 1;
+      } else {
+        k_raygen<<<g_gen, kRaygenBlock, 0, stream>>>(ds.ctl, q, A);
+        if (t_this) cudaEventRecord(ds.events[timed * 4 + 0], stream);
+        if (flat) flat<<<dev.sm_count * 8, kFlatBlock, 0, stream>>>(ds.ctl, q, dev.d, dev.flat, ds.hits);
+        else traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, dev.d, A);
+        if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
+        k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
+        launches += 3;
+      }
       if (t_this) { cudaEventRecord(ds.events[timed * 4 + 2], stream); timed++; }
-      launches += 3;
       cur ^= 1;
       iter++;
     }

@@ -189,6 +189,26 @@ __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, u
       float denom = dot3(n, d);
       f3 qo = q - o;
       t = dot3(n, qo) * rcp_approx(denom);
+#ifndef RT_SCAN_BRANCHY
+      if constexpr (kScan) {
+        // Linear scan over a constant-bank list: every lane tests every primitive, and in a warp of 32 incoherent rays
+        // some lane nearly always passes the distance test, so an early exit saves no issue slots — it only adds
+        // BSSY/BSYNC pairs and branch-resolve stalls.  Straight-line code, one predicated update at the end.
+        // (t is inf/NaN for a parallel ray: every comparison below is then false.)
+        const float4 p2 = rec.r2();
+        const f3 pr = fma3(t, d, -qo);             // p - q
+        const float a = dot3(mk3(p1.z, p1.w, p2.x), pr), b = dot3(mk3(p2.y, p2.z, p2.w), pr);
+        const bool pgram = (tf & PRIM_TYPE_MASK) == PRIM_PGRAM;           // uniform (constant bank)
+        const float lim = pgram ? fmaxf(a, b) : a + b;                    // a, b <= 1  |  a + b <= 1
+        const bool ok = (a >= 0.f) & (b >= 0.f) & (lim <= 1.f) & (fabsf(denom) > 1e-8f) & (t > tmin) & (t < best.t) & (geom != skip_a);
+        if (ok) {
+          best.t = t;
+          best.prim = i;
+          best.front = denom < 0.f;
+        }
+        return;
+      }
+#endif
       // one exit for: parallel ray (Geometry.hs:125), outside the open interval, beyond the closest hit so far,
       // the primitive the ray starts on / must not report again
       if (!(fabsf(denom) > 1e-8f && t > tmin && (kScan ? t < best.t : t <= best.t)) || geom == skip_a || (!kScan && geom == skip_b)) return;
