@@ -14,7 +14,15 @@
 //                      with wa = v x nS, wb = nS x u (planar coords a = wa.(p-q), b = wb.(p-q);
 //                      Geometry.hs:130-131 rewritten by the scalar triple product)
 //             meta   : {type|flags, geom id, xform id, material id} as uint32 bit patterns
-//   tri_uv  : per primitive 2 x float4 {uv0, uv1} {uv2, -, -} (triangles only)
+//   tri_uv  : 32 bytes of auxiliary data per primitive: a triangle's {uv0, uv1} {uv2, -, -}; for an AGGREGATED CUBOID
+//             (below) the 80-byte box record {c.xyz, h0} {e0.xyz, h1} {e1.xyz, h2} {e2.xyz, -} (centre, unit axes = images
+//             of the local x, y, z axes, half extents) starts in the head face's slot and runs over the next two
+//             (parallelogram faces have no uv data of their own)
+// Aggregated cuboids: the reference's `cuboid` is a group of six parallelograms (Geometry.hs:154-166).  All six face
+// records stay in `prims` (shading reads the face that was hit), but traversal answers the closest hit of the whole
+// solid with ONE slab test at the head face (PRIM_FLAG_BOXHEAD, ~60 instructions instead of 6 x 33) and treats the
+// other five (PRIM_FLAG_BOXTAIL) as already answered.  The six faces are consecutive in index order (+z -z -x +x +y -y),
+// their geometry ids are consecutive too, and the flattener never splits them across leaves.
 #pragma once
 #include <stdint.h>
 
@@ -36,9 +44,12 @@ constexpr uint32_t PRIM_TYPE_MASK = 3u;
 constexpr uint32_t PRIM_FLAG_BIG = 4u;      // large-radius sphere: fp64 discriminant
 constexpr uint32_t PRIM_FLAG_MOVING = 8u;   // stays in local space; ray is mapped by xform(time)
 constexpr uint32_t PRIM_FLAG_UVXFORM = 16u; // sphere under a rotation: uv needs the local normal
+constexpr uint32_t PRIM_FLAG_BOXHEAD = 32u; // face 0 of an aggregated cuboid: traversal tests the whole box here
+constexpr uint32_t PRIM_FLAG_BOXTAIL = 64u; // faces 1..5 of an aggregated cuboid: answered by the head
 
 // scene feature bits: which code the traversal kernel must contain (template specialisation)
 constexpr uint32_t TF_SPHERE = 1u, TF_PLANAR = 2u, TF_MOVING = 4u, TF_MEDIA = 8u;
+constexpr uint32_t TF_BOX = 16u;   // some cuboids are aggregated (PRIM_FLAG_BOXHEAD / BOXTAIL occur)
 
 struct DNode {  // 32 bytes
   float lo[3];

@@ -104,6 +104,8 @@ struct HPrim {            // one primitive instance (double precision, final spa
   uint32_t geom = kNone, xform = 0, material = kNone, canonical = kNone;
   BoxD box;               // world-space box (swept over the shutter for moving instances)
   uint32_t index = kNone; // final device index (reference evaluation order)
+  D3 box_c, box_e[3];     // PRIM_FLAG_BOXHEAD: centre and unit axes of the aggregated cuboid (same space as c / n)
+  double box_h[3] = {0, 0, 0};   // ... and its half extents
 };
 
 // reference-shaped tree: exactly the structure the reference would evaluate
@@ -366,6 +368,19 @@ struct Builder {
           ch.push_back(leaf);
           rb.join(rnodes[leaf].ref_box);
         }
+        // A proper solid (positive extents) whose six faces will share one leaf is traversed as ONE slab test
+        // (rt_device.h, "aggregated cuboids"): same closest face, same t up to rounding.
+        if (aggregate_boxes && kLeafMax >= 6 && xmax > xmin && ymax > ymin && zmax > zmin && std::isfinite(xmax - xmin) &&
+            std::isfinite(ymax - ymin) && std::isfinite(zmax - zmin)) {
+          HPrim& head = prims[rnodes[ch[0]].prim];
+          const D3 c_local{(xmin + xmax) / 2, (ymin + ymax) / 2, (zmin + zmax) / 2};
+          const D3 ax[3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+          head.box_c = xf.moving ? c_local : xf.fwd.pt(c_local, 0);
+          for (int k = 0; k < 3; k++) head.box_e[k] = xf.moving ? ax[k] : xf.fwd.lin(ax[k]);
+          head.box_h[0] = (xmax - xmin) / 2; head.box_h[1] = (ymax - ymin) / 2; head.box_h[2] = (zmax - zmin) / 2;
+          head.flags |= PRIM_FLAG_BOXHEAD;
+          for (int f = 1; f < 6; f++) prims[rnodes[ch[f]].prim].flags |= PRIM_FLAG_BOXTAIL;
+        }
         rnodes[g].children = ch;
         rnodes[g].ref_box = rb;
         result = g;
@@ -539,6 +554,7 @@ struct Builder {
   // A bvhTree subtree with at most kCollapse primitives becomes one leaf (the reference's tree, truncated: same split
   // policy above, a short scan below).  RT_B200_COLLAPSE overrides.
   uint32_t kCollapse = 4;
+  bool aggregate_boxes = true;      // RT_B200_NO_BOXES=1: every cuboid face is tested on its own (A/B runs)
   // number of primitives below a subtree made only of GROUPs and LEAFs; 0 if it contains a BVH node
   uint32_t flat_count(const RNode& n) const {
     if (n.kind == RNode::LEAF) return 1;
@@ -683,7 +699,15 @@ struct Builder {
       uint32_t meta[4] = {p.type | p.flags, p.geom, p.xform, p.material};
       std::memcpy(o + 12, meta, 16);
       float* u = &fs.tri_uv[(size_t)p.index * 8];
-      for (int k = 0; k < 3; k++) { u[2 * k] = (float)p.uv[k][0]; u[2 * k + 1] = (float)p.uv[k][1]; }
+      if (p.flags & PRIM_FLAG_BOXHEAD) {   // box record over the aux slots of faces 0..1 (parallelograms have no uv data)
+        const float rec[16] = {(float)p.box_c.x, (float)p.box_c.y, (float)p.box_c.z, (float)p.box_h[0],
+                               (float)p.box_e[0].x, (float)p.box_e[0].y, (float)p.box_e[0].z, (float)p.box_h[1],
+                               (float)p.box_e[1].x, (float)p.box_e[1].y, (float)p.box_e[1].z, (float)p.box_h[2],
+                               (float)p.box_e[2].x, (float)p.box_e[2].y, (float)p.box_e[2].z, 0.f};
+        std::memcpy(u, rec, sizeof rec);
+      } else if (p.type == PRIM_TRI) {
+        for (int k = 0; k < 3; k++) { u[2 * k] = (float)p.uv[k][0]; u[2 * k + 1] = (float)p.uv[k][1]; }
+      }
       fs.canonical[p.index] = p.canonical;
     }
   }
@@ -786,6 +810,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
       t_last = now;
     };
     if (const char* e = std::getenv("RT_B200_LEAF")) b.kLeafMax = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
+    if (const char* e = std::getenv("RT_B200_NO_BOXES")) b.aggregate_boxes = std::atoi(e) == 0;
     if (const char* e = std::getenv("RT_B200_COLLAPSE")) b.kCollapse = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
     b.mat_used.assign(sc.materials.size(), 0);
     b.tex_used.assign(sc.textures.size(), 0);
@@ -838,6 +863,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
       if (p.index == kNone) continue;
       fs.features |= (p.type == PRIM_SPHERE) ? TF_SPHERE : TF_PLANAR;
       if (p.flags & PRIM_FLAG_MOVING) fs.features |= TF_MOVING;
+      if (p.flags & PRIM_FLAG_BOXHEAD) fs.features |= TF_BOX;
     }
     if (!b.media.empty()) fs.features |= TF_MEDIA;
 

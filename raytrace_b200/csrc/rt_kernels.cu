@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
         }
       } else if (want_p) {
         const uint32_t stop = min(pe, pc + (uint32_t)kPrimBurst);
-        for (; pc < stop; pc++) intersect_prim<F>(sc, pc, ray, tmin, origin_geom, skip_b, h);
+        while (pc < stop) pc += intersect_prim<F>(sc, pc, ray, tmin, origin_geom, skip_b, h);   // a cuboid head answers 6 (never past pe)
       }
       continue;
     }
@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
                   const uint32_t root = sc.media[m - 1].root;
                   if (root & kLeafBit) {    // boundary is a short primitive list: answer the query right here
                     const uint32_t first = (root & ~kLeafBit) >> kLeafShift, count = (root & kLeafCountMask) + 1u;
-                    for (uint32_t k = 0; k < count; k++) intersect_prim<F>(sc, first + k, ray, tmin, origin_geom, skip_b, h);
+                    for (uint32_t k = 0; k < count;) k += intersect_prim<F>(sc, first + k, ray, tmin, origin_geom, skip_b, h);
                     continue;
                   }
                   cur = root;
@@ -322,7 +322,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
           h = Hit{inf, kNone, false};
           if (md.root & kLeafBit) {
             const uint32_t first = (md.root & ~kLeafBit) >> kLeafShift, count = (md.root & kLeafCountMask) + 1u;
-            for (uint32_t k = 0; k < count; k++) intersect_prim<F>(sc, first + k, ray, tmin, origin_geom, skip_b, h);
+            for (uint32_t k = 0; k < count;) k += intersect_prim<F>(sc, first + k, ray, tmin, origin_geom, skip_b, h);
             continue;
           }
           cur = md.root;
@@ -372,27 +372,48 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__
 // Cornell box) need no tree and no stack: every lane tests the same primitive at the same time, so the list travels in
 // the KERNEL PARAMETER block and, with the loop unrolled, each record field is an immediate constant-bank operand of
 // the FFMA that uses it — zero loads, zero divergence between lanes.
+// Aggregated cuboids (rt_device.h) travel in a list of their own: their six faces are left out of `rec`, and one slab
+// test per box runs after the face scan (with the full tie rule, so the result is that of a scan in index order).
+constexpr int kFlatBoxes = 4;
 struct FlatList {
-  uint32_t n, first, _pad[2];
+  uint32_t n, n_box, _pad[2];
+  uint32_t index[kLeafCap];         // primitive index of rec[k] (increasing)
   float4 rec[kLeafCap][4];
+  float4 box[kFlatBoxes][4];        // box records
+  uint32_t box_first[kFlatBoxes];   // primitive index / geometry id of face 0
+  uint32_t box_geom[kFlatBoxes];
 };
+
+// closest hit over the whole list: unrolled, every record field a constant-bank operand
+template <uint32_t F>
+__device__ __forceinline__ Hit scan_flat(const DScene& sc, const FlatList& L, const RayT& ray, uint32_t origin_geom) {
+  Hit h{__int_as_float(0x7f800000), kNone, false};
+#pragma unroll
+  for (int k = 0; k < (int)kLeafCap; k++) {
+    if (k >= (int)L.n) break;
+    intersect_rec<F, ParamRec, true>(sc, ParamRec{L.rec[k]}, L.index[k], ray, 1e-4f, origin_geom, kNone, h);
+  }
+  if constexpr ((F & TF_PLANAR) != 0) {
+#pragma unroll
+    for (int k = 0; k < kFlatBoxes; k++) {
+      if (k >= (int)L.n_box) break;
+      intersect_box(L.box[k][0], L.box[k][1], L.box[k][2], L.box[k][3], L.box_first[k], L.box_geom[k], ray.o, ray.d, 1e-4f,
+                    origin_geom, kNone, false, h);
+    }
+  }
+  return h;
+}
 constexpr int kFlatBlock = 256;
 
 template <uint32_t F>
 __global__ void __launch_bounds__(kFlatBlock) k_traverse_flat(const Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
                                                               const __grid_constant__ FlatList L, float2* __restrict__ hits) {
   const uint32_t n = ctl->n_live;
-  const float inf = __int_as_float(0x7f800000);
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const float4 o4 = q.o[i], d4 = q.d[i];
     const RayT ray{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
     const uint32_t origin_geom = __float_as_uint(d4.w);
-    Hit h{inf, kNone, false};
-#pragma unroll
-    for (int k = 0; k < (int)kLeafCap; k++) {
-      if (k >= (int)L.n) break;
-      intersect_rec<F, ParamRec, true>(sc, ParamRec{L.rec[k]}, L.first + k, ray, 1e-4f, origin_geom, kNone, h);
-    }
+    const Hit h = scan_flat<F>(sc, L, ray, origin_geom);
     hits[i] = make_float2(h.front ? h.t : -h.t, __uint_as_float(h.prim));
   }
 }
@@ -410,18 +431,25 @@ static FlatFn pick_flat(uint32_t features) {
 }
 
 using TraverseFn = void (*)(Ctl*, Queue, const DScene, const RenderArgs);
+template <template <uint32_t> class K, uint32_t B>   // B = TF_BOX or 0
+static TraverseFn pick_planar_variant(uint32_t features) {
+  if (features & TF_MOVING) return K<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_MEDIA | B>::fn();
+  switch (features & (TF_SPHERE | TF_PLANAR | TF_MEDIA)) {
+    case TF_PLANAR: return K<TF_PLANAR | B>::fn();
+    case TF_SPHERE | TF_PLANAR: return K<TF_SPHERE | TF_PLANAR | B>::fn();
+    case TF_PLANAR | TF_MEDIA: return K<TF_PLANAR | TF_MEDIA | B>::fn();
+    case TF_SPHERE | TF_PLANAR | TF_MEDIA: return K<TF_SPHERE | TF_PLANAR | TF_MEDIA | B>::fn();
+    default: return K<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_MEDIA | B>::fn();
+  }
+}
 template <template <uint32_t> class K>
 static TraverseFn pick_by_features(uint32_t features) {
-  if (features & TF_MOVING) return K<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_MEDIA>::fn();
-  switch (features & (TF_SPHERE | TF_PLANAR | TF_MEDIA)) {
-    case TF_SPHERE: return K<TF_SPHERE>::fn();
-    case TF_PLANAR: return K<TF_PLANAR>::fn();
-    case TF_SPHERE | TF_PLANAR: return K<TF_SPHERE | TF_PLANAR>::fn();
-    case TF_SPHERE | TF_MEDIA: return K<TF_SPHERE | TF_MEDIA>::fn();
-    case TF_PLANAR | TF_MEDIA: return K<TF_PLANAR | TF_MEDIA>::fn();
-    case TF_SPHERE | TF_PLANAR | TF_MEDIA: return K<TF_SPHERE | TF_PLANAR | TF_MEDIA>::fn();
-    default: return K<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_MEDIA>::fn();
+  if (features & TF_BOX) return pick_planar_variant<K, TF_BOX>(features);   // aggregated cuboids present (implies planar)
+  if (!(features & TF_MOVING)) {
+    if ((features & (TF_SPHERE | TF_PLANAR | TF_MEDIA)) == TF_SPHERE) return K<TF_SPHERE>::fn();
+    if ((features & (TF_SPHERE | TF_PLANAR | TF_MEDIA)) == (TF_SPHERE | TF_MEDIA)) return K<TF_SPHERE | TF_MEDIA>::fn();
   }
+  return pick_planar_variant<K, 0u>(features);
 }
 template <uint32_t F> struct StaticK { static TraverseFn fn() { return k_traverse<F>; } };
 template <uint32_t F> struct PersistentK { static TraverseFn fn() { return k_traverse_p<F>; } };
@@ -545,12 +573,7 @@ __device__ __forceinline__ void shade_tiles(Ctl* __restrict__ ctl, const Queue& 
       }
       Hit hit;
       if (FF) {   // closest hit over the constant-bank list (same code and order as k_traverse_flat)
-        hit = Hit{__int_as_float(0x7f800000), kNone, false};
-#pragma unroll
-        for (int k = 0; k < (int)kLeafCap; k++) {
-          if (k >= (int)L->n) break;
-          intersect_rec<FF ? FF : TF_SPHERE, ParamRec, true>(sc, ParamRec{L->rec[k]}, L->first + k, ray, 1e-4f, origin_geom, kNone, hit);
-        }
+        hit = scan_flat<FF ? FF : TF_SPHERE>(sc, *L, ray, origin_geom);
       } else {
         const float2 h2 = s_h[par][threadIdx.x];
         hit = Hit{fabsf(h2.x), __float_as_uint(h2.y), !(h2.x < 0.f)};
@@ -716,7 +739,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_probe(const __grid_constant_
     ray.time = time;
     ray.o = ld3(c.center);
     ray.d = normalize3(fma3((float)i + 0.5f, ld3(c.pixel_u), fma3((float)j + 0.5f, ld3(c.pixel_v), ld3(c.top_left))));
-    Hit h = trace_segment<TF_SPHERE | TF_PLANAR | TF_MOVING>(sc, ray, kNone, false, make_uint2(0, 0), 0, 0, 0, s_stack + threadIdx.x, kTraverseBlock);
+    Hit h = trace_segment<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_BOX>(sc, ray, kNone, false, make_uint2(0, 0), 0, 0, 0, s_stack + threadIdx.x, kTraverseBlock);
     ids[p] = h.prim == kNone ? kNone : sc.canonical[h.prim];
     ts[p] = h.t;
   }
@@ -738,7 +761,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_probe_surface(const __grid_c
     ray.time = time;
     ray.o = ld3(cam.center);
     ray.d = normalize3(fma3((float)i + 0.5f, ld3(cam.pixel_u), fma3((float)j + 0.5f, ld3(cam.pixel_v), ld3(cam.top_left))));
-    Hit h = trace_segment<TF_SPHERE | TF_PLANAR | TF_MOVING>(sc, ray, kNone, false, make_uint2(0, 0), 0, 0, 0, s_stack + threadIdx.x, kTraverseBlock);
+    Hit h = trace_segment<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_BOX>(sc, ray, kNone, false, make_uint2(0, 0), 0, 0, 0, s_stack + threadIdx.x, kTraverseBlock);
     float* o = out + 10 * (size_t)p;
     for (int k = 0; k < 10; k++) o[k] = 0.f;
     if (h.prim == kNone) continue;
@@ -923,10 +946,27 @@ static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
   d.noise_grad = reinterpret_cast<const float*>(base + secs[8].off);
   d.noise_perm = reinterpret_cast<const uint8_t*>(base + secs[9].off);
   if (f.surface_root != kNone && (f.surface_root & kLeafBit)) {
-    ds->flat.first = (f.surface_root & ~kLeafBit) >> kLeafShift;
-    ds->flat.n = (f.surface_root & kLeafCountMask) + 1u;
-    std::memcpy(ds->flat.rec, f.prims.data() + (size_t)ds->flat.first * 16, (size_t)ds->flat.n * 64);
-    ds->has_flat = true;
+    const uint32_t first = (f.surface_root & ~kLeafBit) >> kLeafShift, count = (f.surface_root & kLeafCountMask) + 1u;
+    FlatList& L = ds->flat;
+    bool fits = true;
+    for (uint32_t i = first; i < first + count; i++) {
+      const float* rec = f.prims.data() + (size_t)i * 16;
+      uint32_t meta[4];
+      std::memcpy(meta, rec + 12, 16);
+      if (meta[0] & PRIM_FLAG_BOXTAIL) continue;
+      if (meta[0] & PRIM_FLAG_BOXHEAD) {
+        if (L.n_box == (uint32_t)kFlatBoxes) { fits = false; break; }   // (cannot happen with leaves of <= 24 primitives)
+        std::memcpy(L.box[L.n_box], f.tri_uv.data() + (size_t)i * 8, 64);
+        L.box_first[L.n_box] = i;
+        L.box_geom[L.n_box] = meta[1];
+        L.n_box++;
+        continue;
+      }
+      std::memcpy(L.rec[L.n], rec, 64);
+      L.index[L.n] = i;
+      L.n++;
+    }
+    ds->has_flat = fits;
   }
   std::memcpy(d.media, f.media, sizeof d.media);
   d.n_media = f.n_media;

@@ -96,7 +96,9 @@ __device__ __forceinline__ float rcp_approx(float x) {
 // Where a primitive record comes from: global memory (__ldg float4, fetched on demand) ...
 struct GlobalRec {
   const float4* P;
-  __device__ __forceinline__ float4 meta() const { return __ldg(P + 3); }
+  float4 m4;            // the record's meta word, already fetched by the caller
+  static constexpr bool kBoxes = true;    // aggregated cuboids are answered at their head face
+  __device__ __forceinline__ float4 meta() const { return m4; }
   __device__ __forceinline__ float4 r0() const { return __ldg(P); }
   __device__ __forceinline__ float4 r1() const { return __ldg(P + 1); }
   __device__ __forceinline__ float4 r2() const { return __ldg(P + 2); }
@@ -105,11 +107,64 @@ struct GlobalRec {
 // used by the flat-list kernel, where every lane of a warp tests the same primitive at the same time.
 struct ParamRec {
   const float4* R;      // 4 consecutive float4 in param space
+  static constexpr bool kBoxes = false;   // the flat-list kernels keep boxes in a list of their own
   __device__ __forceinline__ float4 meta() const { return R[3]; }
   __device__ __forceinline__ float4 r0() const { return R[0]; }
   __device__ __forceinline__ float4 r1() const { return R[1]; }
   __device__ __forceinline__ float4 r2() const { return R[2]; }
 };
+
+// Closest hit of an aggregated cuboid = closest hit over its six parallelogram faces (Geometry.hs:154-166 + :117-144),
+// by the slab method: the boundary of a convex solid is crossed at most twice, at t_in (from outside: front = True) and
+// t_out (from inside).  Per face the reference requires |n.d| > 1e-8 (a parallel ray misses both faces of that axis; the
+// closed interior test 0 <= a, b <= 1 of the other faces then decides by |coordinate| <= half extent), t in (tmin, best]
+// and that the face is not the one the ray starts on (skip_a) / must not report again (skip_b).  The closest face passing
+// all of that is t_in's face if it passes, else t_out's.  b0..b3 = box record (rt_device.h), `first` / `geom0` = primitive
+// index / geometry id of face 0; faces +z -z -x +x +y -y = 0..5, axes tested z, x, y so that an exact edge tie goes to the
+// lower face index like the reference's scan.  strict: caller scans in index order (ties lose to earlier primitives).
+__device__ __forceinline__ void intersect_box(const float4 b0, const float4 b1, const float4 b2, const float4 b3, uint32_t first,
+                                              uint32_t geom0, f3 o, f3 d, float tmin, uint32_t skip_a, uint32_t skip_b, bool strict,
+                                              Hit& best) {
+  const float inf = __int_as_float(0x7f800000);
+  const f3 oc = mk3(b0.x, b0.y, b0.z) - o;
+  float t_in = -inf, t_out = inf;
+  uint32_t f_in = 0, f_out = 0;
+  auto axis = [&](f3 e, float h, uint32_t face_minus, uint32_t face_plus) {
+    const float D = dot3(e, d), P = dot3(e, oc);       // local coordinate of the ray: -P + t D
+    const float inv = rcp_approx(D);
+    const float tm = (P - h) * inv, tp = (P + h) * inv; // planes at -h and +h
+    const bool fwd = D > 0.f;
+    float tn = fminf(tm, tp), tf = fmaxf(tm, tp);
+    if (!(fabsf(D) > 1e-8f)) {                          // parallel: inside the slab for all t, or never
+      const bool inside = fabsf(P) <= h;
+      tn = inside ? -inf : inf;
+      tf = inside ? inf : -inf;
+    }
+    if (tn > t_in) { t_in = tn; f_in = fwd ? face_minus : face_plus; }
+    if (tf < t_out) { t_out = tf; f_out = fwd ? face_plus : face_minus; }
+  };
+  axis(mk3(b3.x, b3.y, b3.z), b2.w, 1u, 0u);   // z: faces 1 (-z) / 0 (+z)
+  axis(mk3(b1.x, b1.y, b1.z), b0.w, 2u, 3u);   // x: faces 2 (-x) / 3 (+x)
+  axis(mk3(b2.x, b2.y, b2.z), b1.w, 5u, 4u);   // y: faces 5 (-y) / 4 (+y)
+  const bool crosses = t_in <= t_out;
+  const uint32_t g_in = geom0 + f_in, g_out = geom0 + f_out;
+  const bool ok_in = crosses & (t_in > tmin) & (g_in != skip_a) & (g_in != skip_b);
+  const bool ok_out = crosses & (t_out > tmin) & (g_out != skip_a) & (g_out != skip_b);
+  const float t = ok_in ? t_in : t_out;
+  const uint32_t idx = first + (ok_in ? f_in : f_out);
+  if ((ok_in | ok_out) && (t < best.t || (!strict && t == best.t && idx < best.prim))) {
+    best.t = t;
+    best.prim = idx;
+    best.front = ok_in;
+  }
+}
+
+// BVH kernels: the box record comes from global memory.  (Out of line — __noinline__ — was tried to keep the slab test's
+// registers out of the traversal loop: the by-reference result then lives on the stack, 80 registers + spills; inline: 72.)
+__device__ __forceinline__ void intersect_box_global(const float4* __restrict__ B, uint32_t first, uint32_t geom0, f3 o, f3 d, float tmin,
+                                                     uint32_t skip_a, uint32_t skip_b, Hit& best) {
+  intersect_box(__ldg(B), __ldg(B + 1), __ldg(B + 2), __ldg(B + 3), first, geom0, o, d, tmin, skip_a, skip_b, false, best);
+}
 
 // one primitive; `skip_a` = geometry the ray ORIGIN lies on, `skip_b` = geometry of a hit at tmin
 // that must not be reported again (second boundary query of constantMedium, Geometry.hs:311).
@@ -184,6 +239,12 @@ __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, u
     } else return;
   } else {
     if constexpr ((F & TF_PLANAR) != 0) {
+      if constexpr (Rec::kBoxes && (F & TF_BOX) != 0) {
+        if (tf & (PRIM_FLAG_BOXHEAD | PRIM_FLAG_BOXTAIL)) {   // aggregated cuboid: one slab test at the head face
+          if (tf & PRIM_FLAG_BOXHEAD) intersect_box_global(sc.tri_uv + 2 * (size_t)i, i, geom, o, d, tmin, skip_a, skip_b, best);
+          return;
+        }
+      }
       const float4 p1 = rec.r1();
       f3 q = mk3(p0.x, p0.y, p0.z), n = mk3(p0.w, p1.x, p1.y);
       float denom = dot3(n, d);
@@ -227,10 +288,16 @@ __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, u
   }
 }
 
+// Tests primitive i and returns how many consecutive primitives that answered (6 for the head face of an aggregated
+// cuboid, else 1): leaf loops advance by it.
 template <uint32_t F>
-__device__ __forceinline__ void intersect_prim(const DScene& sc, uint32_t i, const RayT& ray, float tmin,
-                                               uint32_t skip_a, uint32_t skip_b, Hit& best) {
-  intersect_rec<F>(sc, GlobalRec{sc.prims + 4 * (size_t)i}, i, ray, tmin, skip_a, skip_b, best);
+__device__ __forceinline__ uint32_t intersect_prim(const DScene& sc, uint32_t i, const RayT& ray, float tmin,
+                                                   uint32_t skip_a, uint32_t skip_b, Hit& best) {
+  const float4* P = sc.prims + 4 * (size_t)i;
+  const float4 m4 = __ldg(P + 3);
+  intersect_rec<F>(sc, GlobalRec{P, m4}, i, ray, tmin, skip_a, skip_b, best);
+  if constexpr ((F & TF_BOX) != 0) return (__float_as_uint(m4.x) & PRIM_FLAG_BOXHEAD) ? 6u : 1u;
+  return 1u;
 }
 
 // slab test of one 32-byte node against the clipped interval (tmin, tmax]
@@ -277,7 +344,7 @@ __device__ __forceinline__ void closest_hit(const DScene& sc, uint32_t root, con
     }
     if (cur == kNone) break;
     const uint32_t first = (cur & ~kLeafBit) >> kLeafShift, count = (cur & kLeafCountMask) + 1u;
-    for (uint32_t k = 0; k < count; k++) intersect_prim<F>(sc, first + k, ray, tmin, skip_a, skip_b, best);
+    for (uint32_t k = 0; k < count;) k += intersect_prim<F>(sc, first + k, ray, tmin, skip_a, skip_b, best);
     if (sp > 0) { sp--; cur = stack[sp * stride]; }
     else cur = kNone;
   }
