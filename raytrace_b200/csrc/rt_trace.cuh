@@ -125,27 +125,26 @@ struct ParamRec {
 __device__ __forceinline__ void intersect_box(const float4 b0, const float4 b1, const float4 b2, const float4 b3, uint32_t first,
                                               uint32_t geom0, f3 o, f3 d, float tmin, uint32_t skip_a, uint32_t skip_b, bool strict,
                                               Hit& best) {
-  const float inf = __int_as_float(0x7f800000);
   const f3 oc = mk3(b0.x, b0.y, b0.z) - o;
-  float t_in = -inf, t_out = inf;
-  uint32_t f_in = 0, f_out = 0;
-  auto axis = [&](f3 e, float h, uint32_t face_minus, uint32_t face_plus) {
+  // one axis: entry / exit distance of its slab and the face the ray enters through (the exit face is that ^ 1).
+  // A parallel ray (|D| <= 1e-8, Geometry.hs:125) gets a huge finite 1/D: inside the slab the two distances become
+  // -huge / +huge (no constraint), outside both take the same sign (the box test below fails) — no branch, no NaN.
+  auto axis = [&](f3 e, float h, uint32_t face_minus, float& tn, float& tf, uint32_t& near_face) {
     const float D = dot3(e, d), P = dot3(e, oc);       // local coordinate of the ray: -P + t D
-    const float inv = rcp_approx(D);
+    const float inv = fabsf(D) > 1e-8f ? rcp_approx(D) : copysignf(1e30f, D);
     const float tm = (P - h) * inv, tp = (P + h) * inv; // planes at -h and +h
-    const bool fwd = D > 0.f;
-    float tn = fminf(tm, tp), tf = fmaxf(tm, tp);
-    if (!(fabsf(D) > 1e-8f)) {                          // parallel: inside the slab for all t, or never
-      const bool inside = fabsf(P) <= h;
-      tn = inside ? -inf : inf;
-      tf = inside ? inf : -inf;
-    }
-    if (tn > t_in) { t_in = tn; f_in = fwd ? face_minus : face_plus; }
-    if (tf < t_out) { t_out = tf; f_out = fwd ? face_plus : face_minus; }
+    tn = fminf(tm, tp);
+    tf = fmaxf(tm, tp);
+    near_face = face_minus ^ (D > 0.f ? 0u : 1u);      // moving up the axis: enters through the -h face
   };
-  axis(mk3(b3.x, b3.y, b3.z), b2.w, 1u, 0u);   // z: faces 1 (-z) / 0 (+z)
-  axis(mk3(b1.x, b1.y, b1.z), b0.w, 2u, 3u);   // x: faces 2 (-x) / 3 (+x)
-  axis(mk3(b2.x, b2.y, b2.z), b1.w, 5u, 4u);   // y: faces 5 (-y) / 4 (+y)
+  float nz, fz, nx, fx, ny, fy;
+  uint32_t az, ax, ay;
+  axis(mk3(b3.x, b3.y, b3.z), b2.w, 1u, nz, fz, az);   // z: faces 1 (-z) / 0 (+z)
+  axis(mk3(b1.x, b1.y, b1.z), b0.w, 2u, nx, fx, ax);   // x: faces 2 (-x) / 3 (+x)
+  axis(mk3(b2.x, b2.y, b2.z), b1.w, 5u, ny, fy, ay);   // y: faces 5 (-y) / 4 (+y)
+  const float t_in = fmaxf(fmaxf(nz, nx), ny), t_out = fminf(fminf(fz, fx), fy);
+  const uint32_t f_in = t_in == nz ? az : (t_in == nx ? ax : ay);
+  const uint32_t f_out = (t_out == fz ? az : (t_out == fx ? ax : ay)) ^ 1u;
   const bool crosses = t_in <= t_out;
   const uint32_t g_in = geom0 + f_in, g_out = geom0 + f_out;
   const bool ok_in = crosses & (t_in > tmin) & (g_in != skip_a) & (g_in != skip_b);
