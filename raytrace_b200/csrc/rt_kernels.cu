@@ -485,6 +485,33 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Shading of ONE path segment whose closest hit is known (Ray.hs:176-198): material / texture / redirect mixture,
+// radiance into the accumulators, depth limit.  Updates ray / thr / origin_geom / meta for the next segment and returns
+// whether the path continues.  Shared by k_shade, k_trace_regions and k_finish: same RNG counters, same results.
+__device__ __forceinline__ bool shade_path(const DScene& sc, const RenderArgs& A, const NoiseTab& T, RayT& ray, const Hit& hit, f3& thr,
+                                           uint32_t& origin_geom, uint32_t pixel, uint2& meta) {
+  const unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
+  const uint4 rnd = rng4(A.key, pixel, sample, meta.y, RNG_SHADE);
+  f3 contrib;
+  bool alive = shade_bounce(sc, A.cam, T, ray, hit, thr, origin_geom, rnd, contrib);
+  if (contrib.x != 0.f || contrib.y != 0.f || contrib.z != 0.f) {
+    float* s = A.sum + 3 * (size_t)pixel;
+    atomicAdd(s, contrib.x);
+    atomicAdd(s + 1, contrib.y);
+    atomicAdd(s + 2, contrib.z);
+    if (A.sumsq) {
+      float* s2 = A.sumsq + 3 * (size_t)pixel;
+      atomicAdd(s2, contrib.x * contrib.x);
+      atomicAdd(s2 + 1, contrib.y * contrib.y);
+      atomicAdd(s2 + 2, contrib.z * contrib.z);
+    }
+  }
+  meta.y += 1;
+  if (meta.y >= (uint32_t)A.cam.max_depth) alive = false;             // rayColor 0 = zero (Ray.hs:176)
+  if (thr.x == 0.f && thr.y == 0.f && thr.z == 0.f) alive = false;     // nothing downstream can contribute
+  return alive;
+}
+
 // One block-iteration = kShadeBlock consecutive queue slots.  Slot reservation is aggregated per BLOCK (warp
 // ballot/popc ranks → shared-memory warp counts → ONE global atomic): the per-warp atomic of round 1 spent half of the
 // kernel waiting on a single contended address (ncu: 49 % of stall samples on the SHFL after it).
@@ -578,25 +605,7 @@ __device__ __forceinline__ void shade_tiles(Ctl* __restrict__ ctl, const Queue& 
         const float2 h2 = s_h[par][threadIdx.x];
         hit = Hit{fabsf(h2.x), __float_as_uint(h2.y), !(h2.x < 0.f)};
       }
-      unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
-      uint4 rnd = rng4(A.key, pixel, sample, meta.y, RNG_SHADE);
-      f3 contrib;
-      alive = shade_bounce(sc, A.cam, T, ray, hit, thr, origin_geom, rnd, contrib);
-      if (contrib.x != 0.f || contrib.y != 0.f || contrib.z != 0.f) {
-        float* s = A.sum + 3 * (size_t)pixel;
-        atomicAdd(s, contrib.x);
-        atomicAdd(s + 1, contrib.y);
-        atomicAdd(s + 2, contrib.z);
-        if (A.sumsq) {
-          float* s2 = A.sumsq + 3 * (size_t)pixel;
-          atomicAdd(s2, contrib.x * contrib.x);
-          atomicAdd(s2 + 1, contrib.y * contrib.y);
-          atomicAdd(s2 + 2, contrib.z * contrib.z);
-        }
-      }
-      meta.y += 1;
-      if (meta.y >= (uint32_t)A.cam.max_depth) alive = false;   // rayColor 0 = zero (Ray.hs:176)
-      if (thr.x == 0.f && thr.y == 0.f && thr.z == 0.f) alive = false;   // nothing downstream can contribute
+      alive = shade_path(sc, A, T, ray, hit, thr, origin_geom, pixel, meta);
     }
     const uint32_t mask = __ballot_sync(0xFFFFFFFFu, alive);
     if (lane == 0) s_cnt[par][warp] = __popc(mask);
@@ -696,19 +705,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_finish(Ctl* __restrict__ ctl
     for (;;) {
       const Hit hit = trace_segment<F>(sc, ray, origin_geom, true, A.key, pixel, sample, meta.y, stack, kTraverseBlock);
       segments++;
-      const uint4 rnd = rng4(A.key, pixel, sample, meta.y, RNG_SHADE);
-      f3 contrib;
-      bool alive = shade_bounce(sc, A.cam, T, ray, hit, thr, origin_geom, rnd, contrib);
-      if (contrib.x != 0.f || contrib.y != 0.f || contrib.z != 0.f) {
-        float* s = A.sum + 3 * (size_t)pixel;
-        atomicAdd(s, contrib.x); atomicAdd(s + 1, contrib.y); atomicAdd(s + 2, contrib.z);
-        if (A.sumsq) {
-          float* s2 = A.sumsq + 3 * (size_t)pixel;
-          atomicAdd(s2, contrib.x * contrib.x); atomicAdd(s2 + 1, contrib.y * contrib.y); atomicAdd(s2 + 2, contrib.z * contrib.z);
-        }
-      }
-      meta.y += 1;
-      if (!alive || meta.y >= (uint32_t)A.cam.max_depth || (thr.x == 0.f && thr.y == 0.f && thr.z == 0.f)) break;
+      if (!shade_path(sc, A, T, ray, hit, thr, origin_geom, pixel, meta)) break;
     }
   }
   // bookkeeping: segments traced, and (last block) the render is complete
