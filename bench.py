@@ -10,8 +10,9 @@ split across ranks (strong scaling; scene replicated) and one NCCL reduce assemb
 
 Prints ONE JSON line on rank 0.  `value` = whole-job Msamples/s with the scene resident in HBM;
 `e2e` = the same metric through the public API with host buffers (scene commit + upload, render, image
-read-back inside the timed region); `roofline` = the traversal kernel against the measured HBM peak using
-SURVEY §8(d)'s algorithmic bytes per ray; `cpu_baseline` = the CPU oracle (a C++ port of the reference's
+read-back inside the timed region); `roofline` = the dominant kernel of the workload against the measured HBM peak
+with its algorithmic bytes, `roofline_fp32` = the same kernel's SURVEY §8(d) flops against the measured
+FP32 peak (the limiter of this path is instruction issue, not bandwidth); `cpu_baseline` = the CPU oracle (a C++ port of the reference's
 algorithm; the Haskell reference cannot be built here) on all host cores, on a bounded sample.
 `--impl reference` times that CPU oracle as the reference arm.
 """
@@ -40,7 +41,8 @@ WORKLOADS = {
     "pawn": ("pawn", dict(width=1920, aspect=16 / 9, spp=1024), "pawn_1920x1080_1024spp_depth20"),
     "bunny_volume": ("bunny_volume", dict(), "bunny_volume_1920x1080_1024spp_depth20"),
 }
-CPU_SAMPLE_SPP = {"cornell": 32, "cornell_noredirect": 16, "readme": 200, "demo1": 16, "demo2": 8, "pawn": 4, "bunny_volume": 4}
+# spp of the timed CPU sample (full resolution): a few seconds on 16 host cores = tens of core-seconds per workload
+CPU_SAMPLE_SPP = {"cornell": 200, "cornell_noredirect": 64, "readme": 50, "demo1": 64, "demo2": 32, "pawn": 16, "bunny_volume": 16}
 
 
 def load_peaks():
@@ -74,6 +76,9 @@ NCU_TRAFFIC = {
     # traffic = this x the measured mean rays per launch of the run, so it stays "per launch like achieved".
     ("cornell", "k_shade"): 400.5e6 / 4194304, ("cornell", "k_traverse"): 153.6e6 / 4194304,
     ("pawn", "k_shade"): 415.8e6 / 4194304, ("pawn", "k_traverse"): 206.2e6 / 4194304,
+    # fused flat-scene kernel (raygen + closest hit + shading + compaction in one launch), full 16 Mi-path launch,
+    # profiles/r01f_ncu_full_summary.txt: 660.0 MB read + 608.6 MB written
+    ("cornell", "k_trace_flat"): (660.0e6 + 608.6e6) / 16777216,
 }
 
 
@@ -301,7 +306,32 @@ def main():
     roof_fp32 = None
     kernels = {}
     samples_rendered = count * W * H * args.steps
-    if shade_ms > 0:
+    # flat scenes run ONE fused kernel per iteration (k_trace_flat: raygen + closest hit + shading + compaction); the
+    # library then reports its time as ms_shade and ms_traverse ~ 0
+    fused = shade_ms > 0 and trav_ms < 0.05 * shade_ms
+    if fused:
+        # compulsory HBM traffic of the fused kernel: every segment except a path's first reads its 56-byte record, and
+        # every path that continues writes one (new camera paths are generated in registers; no hit buffer)
+        fz_bytes = 112.0 * max(rays - samples_rendered, 0)
+        ach = fz_bytes / (shade_ms * 1e-3) / 1e9
+        kernels["k_trace_flat"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                                   "traffic": (NCU_TRAFFIC[(args.scene, "k_trace_flat")] * rays / max(iters, 1)) if (args.scene, "k_trace_flat") in NCU_TRAFFIC else None,
+                                   "bytes_per_ray_algorithmic": fz_bytes / max(rays, 1),
+                                   "avg_launch_ms": shade_ms / max(iters, 1), "ms_per_step": shade_ms / args.steps,
+                                   "algorithmic_bytes_per_launch": fz_bytes / max(iters, 1),
+                                   "note": "queue traffic only: the scene list is constant-bank resident.  The kernel's limiter is "
+                                           "instruction issue (ncu: 73 % issue-active, 27 of 32 threads per instruction) - see roofline_fp32"}
+        if bytes_per_ray is not None and aux.get("fp32_fma_tflops"):
+            # traversal flops from the reference's test counts + F_shade (lambertian + cosine sample ~ 40,
+            # each redirect target one planar test + 10)
+            f_shade = 40 + 74 * len(settings.cs_redirectTargets)
+            fl = flops_per_ray(n_node, n_sph, n_pl) + f_shade
+            ach = rays * fl / (shade_ms * 1e-3) / 1e12
+            roof_fp32 = {"kernel": "k_trace_flat", "achieved": ach, "peak": aux["fp32_fma_tflops"], "unit": "TFLOP/s",
+                         "frac": ach / aux["fp32_fma_tflops"], "flops_per_ray_algorithmic": fl,
+                         "peak_source": "tools/peaks.cu, measured in this run (FFMA chains)",
+                         "l2_read_gbs_measured": aux.get("l2_read_gbs")}
+    elif shade_ms > 0:
         # k_shade streams the wavefront state (SURVEY 8(d)'s constant term): per ray segment it reads the 56-byte path
         # record + the 8-byte hit, and writes a 56-byte record for every path that continues (rays - samples of them:
         # each sample ends exactly once).  This is compulsory HBM traffic (the queues exceed L2).
@@ -311,7 +341,7 @@ def main():
                               "traffic": (NCU_TRAFFIC[(args.scene, "k_shade")] * rays / max(iters, 1)) if (args.scene, "k_shade") in NCU_TRAFFIC else None, "bytes_per_ray_algorithmic": sh_bytes / max(rays, 1),
                               "avg_launch_ms": shade_ms / max(iters, 1), "ms_per_step": shade_ms / args.steps,
                               "algorithmic_bytes_per_launch": sh_bytes / max(iters, 1)}
-    if bytes_per_ray is not None and trav_ms > 0:
+    if bytes_per_ray is not None and trav_ms > 0 and not fused:
         achieved = rays * bytes_per_ray / (trav_ms * 1e-3) / 1e9
         kernels["k_traverse"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                                  "traffic": (NCU_TRAFFIC[(args.scene, "k_traverse")] * rays / max(iters, 1)) if (args.scene, "k_traverse") in NCU_TRAFFIC else None, "bytes_per_ray_algorithmic": bytes_per_ray,
