@@ -165,3 +165,52 @@ def test_surface_probe_pointwise(built, name, ctor, kw):
     print(f"{name}: {int(ok.sum())} px, texture colour max diff {dc.max():.2e}, > 1e-3 on {(dc > 1e-3).mean() * 100:.4f} %")
     assert (dc > 2e-3).mean() < 2e-3
     assert np.median(dc) < 1e-4
+
+
+def _cuboid_zoo(tree):
+    """Cuboids in every role the reference allows: glass (rays run inside and leave through the far face), rotated,
+    moving, boundary of a constantMedium, with and without a bvhTree above them."""
+    V3 = rt.V3
+    glass, fog = rt.dielectric(1.5), rt.isotropic(rt.constantTexture((0.2, 0.4, 0.9)))
+    white = rt.lambertian(rt.constantTexture((0.73, 0.73, 0.73)))
+    red = rt.lambertian(rt.constantTexture((0.65, 0.05, 0.05)))
+    light = rt.lightSource(rt.constantTexture((7, 7, 7)))
+    box = lambda a, b: rt.cuboid(rt.fromCorners(V3(*a), V3(*b)))
+    parts = [
+        rt.pureGeometry(white << rt.parallelogram(V3(-6, -1, -9), V3(12, 0, 0), V3(0, 0, 12))),              # floor
+        rt.pureGeometry(light << rt.parallelogram(V3(-1.5, 3.5, -5), V3(3, 0, 0), V3(0, 0, 2))),
+        rt.pureGeometry(glass << box((-2.6, -1, -4.2), (-1.4, 0.4, -3.0))),
+        rt.pureGeometry(rt.transform(rt.translate(V3(0.2, -1, -4.6)) @ rt.rotateY(0.5), red << box((0, 0, 0), (1.0, 1.8, 1.0)))),
+        rt.pureGeometry(rt.moving(V3(0, 0, 0), V3(0.4, 0.3, 0), white << box((1.8, -1, -3.6), (2.6, -0.2, -2.8)))),
+        fog << rt.constantMedium(1.5, box((-0.8, -1, -2.6), (0.6, 0.2, -1.6))),
+    ]
+    world = rt.bvhTree(parts) if tree else rt.group(parts)
+    s = rt.defaultCameraSettings.replace(cs_imageWidth=96, cs_aspectRatio=1.5, cs_samplesPerPixel=512, cs_maxRecursionDepth=12,
+                                         cs_background=scenes.sky, cs_center=V3(0, 1.0, 2.5), cs_lookAt=V3(0, 0, -3.5), cs_vfov=0.9)
+    return s, world
+
+
+@pytest.mark.parametrize("tree", [False, True], ids=["group", "bvhTree"])
+def test_aggregated_cuboids(built, tree, monkeypatch):
+    """One slab test per cuboid (PRIM_FLAG_BOXHEAD) must pick the same face at the same distance as six independent
+    parallelogram tests (RT_B200_NO_BOXES=1, the reference's formulation) and converge to the oracle's image."""
+    s, world = _cuboid_zoo(tree)
+    agg = CompiledScene(world)
+    monkeypatch.setenv("RT_B200_NO_BOXES", "1")
+    faces = CompiledScene(world)
+    monkeypatch.delenv("RT_B200_NO_BOXES")
+    probe_s = s.replace(cs_imageWidth=480)
+    for t in (0.0, 0.5, 1.0):
+        ia, ta = agg.probe_primary(probe_s, time=t)
+        ib, tb = faces.probe_primary(probe_s, time=t)
+        same = ia == ib
+        assert same.mean() > 0.999, f"face ids differ on {(~same).sum()} pixels at time {t}"      # edges only
+        hit = same & (ia != 0xFFFFFFFF)
+        assert hit.any() and np.all(np.abs(ta[hit] - tb[hit]) <= 1e-5 * np.abs(tb[hit]))
+    ora = OracleScene(world)
+    img, sq, st = agg.render(s, rt.mkStdGen(5), want_sumsq=True, want_stats=True)
+    ref, rsq, cnt = ora.render(s, 5, want_sumsq=True)
+    assert abs(luminance(img).mean() - luminance(ref).mean()) < 0.01 * luminance(ref).mean()
+    assert abs(st["rays"] / st["samples"] - cnt["rays"] / cnt["samples"]) < 0.01 * cnt["rays"] / cnt["samples"]
+    z = z_scores(img.astype(np.float64), sq.astype(np.float64), 512, ref, rsq, 512)
+    assert (np.abs(z) > 4).mean() < 2e-3
