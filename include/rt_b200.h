@@ -198,6 +198,10 @@ int32_t rt_scene_info(const RtScene* scene, RtSceneInfo* info);
 /* read back the flattened host-side buffers (tests: BVH shape equality with the oracle) */
 int32_t rt_scene_get_bvh(const RtScene* scene, float* nodes /*n_bvh_nodes*8, may be NULL*/,
                          uint32_t* prim_canonical_id /*n_prims, may be NULL*/);
+/* canonical primitive ids in the REFERENCE's evaluation order (group: list order, Geometry.hs:340-345; bvhNode / bvhTree:
+ * left subtree first, :356-361,369-377) — the order that decides exact ties.  The device tree is free to store the
+ * primitives in another order (its own leaf order); this is the order the oracle's traversal must reproduce. */
+int32_t rt_scene_get_eval_order(const RtScene* scene, uint32_t* canonical_id_out /*n_prims*/);
 
 /* upload to a device (one scene may be resident on several devices) */
 int32_t rt_scene_upload(RtScene* scene, int32_t device);

@@ -99,7 +99,7 @@ class RtSceneInfo(C.Structure):
 EXPORTS = [
     "rt_version", "rt_last_error", "rt_device_count",
     "rt_scene_create", "rt_scene_destroy", "rt_scene_add_texture", "rt_scene_add_material",
-    "rt_scene_add_node", "rt_scene_set_noise_tables", "rt_scene_commit", "rt_scene_info",
+    "rt_scene_add_node", "rt_scene_set_noise_tables", "rt_scene_commit", "rt_scene_info", "rt_scene_get_eval_order",
     "rt_scene_get_bvh", "rt_scene_upload", "rt_image_height", "rt_render", "rt_render_device",
     "rt_probe_primary", "rt_probe_surface", "rt_set_pool_size", "rt_tonemap_u8",
     "rt_obj_parse", "rt_mesh_sizes", "rt_mesh_data", "rt_mesh_destroy",
@@ -131,6 +131,7 @@ def lib() -> C.CDLL:
     L.rt_scene_set_noise_tables.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                             C.POINTER(C.c_int32), C.POINTER(C.c_double)]
     L.rt_scene_commit.argtypes = [vp, C.c_uint32]
+    L.rt_scene_get_eval_order.argtypes = [vp, u32p]
     L.rt_scene_info.argtypes = [vp, C.POINTER(RtSceneInfo)]
     L.rt_scene_get_bvh.argtypes = [vp, C.POINTER(C.c_float), u32p]
     L.rt_scene_upload.argtypes = [vp, C.c_int32]
@@ -322,6 +323,12 @@ class SceneHandle:
         check(self._L.rt_scene_get_bvh(self._h, nodes.ctypes.data_as(C.POINTER(C.c_float)),
                                        canon.ctypes.data_as(C.POINTER(C.c_uint32))))
         return nodes, canon
+
+    def get_eval_order(self):
+        """canonical primitive ids in the reference's evaluation order (the order that decides exact ties)"""
+        out = np.zeros(self.info()["n_prims"], dtype=np.uint32)
+        check(self._L.rt_scene_get_eval_order(self._h, out.ctypes.data_as(C.POINTER(C.c_uint32))))
+        return out
 
     def upload(self, device: int = 0):
         if device not in self.uploaded:

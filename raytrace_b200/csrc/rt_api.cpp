@@ -282,6 +282,14 @@ int32_t rt_scene_get_bvh(const RtScene* sp, float* nodes, uint32_t* canon) {
   return RT_OK;
 }
 
+int32_t rt_scene_get_eval_order(const RtScene* sp, uint32_t* out) {
+  if (!sp || !out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  const Scene& s = *reinterpret_cast<const Scene*>(sp);
+  if (!s.committed) { set_error("scene not committed"); return RT_ERR_NOT_COMMITTED; }
+  for (size_t i = 0; i < s.flat.ref_order.size(); i++) out[s.flat.ref_order[i]] = s.flat.canonical[i];
+  return RT_OK;
+}
+
 int32_t rt_image_height(const RtCamera* cam, int32_t* height) {
   if (!cam || !height) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
   if (!(cam->aspect_ratio > 0) || cam->image_width <= 0) { set_error("bad image width / aspect ratio"); return RT_ERR_INVALID_ARG; }

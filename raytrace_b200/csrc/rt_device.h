@@ -6,9 +6,10 @@
 //             fetch tests both children).  a = node reference: inner → index of the pair holding its children;
 //             leaf → kLeafBit | first primitive << 5 | (count - 1), count <= 32.  b = primitive count (leaf) or 0.
 //             Roots are bare references (no node, no box test of their own, as in the reference).
-//   prims   : 64-byte records, 4 x float4; index order = the reference's evaluation order
-//             (group: list order, Geometry.hs:340-345; bvhNode: left first, :356-361), so
-//             "lower index wins an exact tie" reproduces the reference's tie rules.
+//   prims   : 64-byte records, 4 x float4, stored in the leaf order of the device tree (a leaf = a contiguous range,
+//             in the reference's evaluation order inside the leaf).  The reference's evaluation order (group: list
+//             order, Geometry.hs:340-345; bvhNode: left first, :356-361) is kept in `ref_order`: on an exact tie
+//             the primitive that the reference evaluates first wins, whatever the shape of the device tree.
 //             sphere : {c.xyz, r}        {-}                {-}                  {meta}
 //             planar : {q.xyz, n.x} {n.y, n.z, wa.xy} {wa.z, wb.xyz} {meta}
 //                      with wa = v x nS, wb = nS x u (planar coords a = wa.(p-q), b = wb.(p-q);
@@ -118,6 +119,7 @@ struct DScene {     // device pointers of one uploaded scene
   const DTexture* textures;
   const float4* texels;
   const uint32_t* canonical;   // prim index -> canonical primitive id (probe output)
+  const uint32_t* ref_order;   // prim index -> position in the reference's evaluation order (exact ties only)
   const float* noise_grad;     // 256*3
   const uint8_t* noise_perm;   // 3*256
   DMedium media[kMaxMedia];

@@ -103,7 +103,8 @@ struct HPrim {            // one primitive instance (double precision, final spa
   double uv[3][2] = {{0, 0}, {1, 0}, {0, 1}};
   uint32_t geom = kNone, xform = 0, material = kNone, canonical = kNone;
   BoxD box;               // world-space box (swept over the shutter for moving instances)
-  uint32_t index = kNone; // final device index (reference evaluation order)
+  uint32_t ref_index = kNone;   // position in the reference's evaluation order (decides exact ties)
+  uint32_t index = kNone;       // device (storage) index: leaf order of the device tree
   D3 box_c, box_e[3];     // PRIM_FLAG_BOXHEAD: centre and unit axes of the aggregated cuboid (same space as c / n)
   double box_h[3] = {0, 0, 0};   // ... and its half extents
 };
@@ -540,7 +541,8 @@ struct Builder {
       HPrim& p = prims[n.prim];
       if (surface && p.material == kNone)
         fail(RT_ERR_TYPE, "raytrace: world is a Geometry m () — attach materials with `<$` (Ray.hs:121)");
-      p.index = next_index++;
+      p.ref_index = next_index++;
+      if (!sah) p.index = p.ref_index;   // reference-shaped device tree: storage order = evaluation order
       return;
     }
     for (int c : n.children) number(c, surface);
@@ -593,7 +595,135 @@ struct Builder {
     hnodes[me].box.join(hnodes[ri].box);
     return me;
   }
+  // ---- device tree, default policy: binned SAH over ALL primitives below a root ------------------------------------
+  // The reference's tree fixes only the EVALUATION ORDER of the primitives (ref_index: who wins an exact tie); closest
+  // hit over a set does not depend on how the set is searched, so the device tree is free to be a better one (SURVEY
+  // §8f4).  The reference's policy — object median along the longest axis, Geometry.hs:369-377 — ages badly with mixed
+  // sizes (demo1's ground sphere of radius 1000 sits deep inside a tree of 0.2-radius spheres and inflates every
+  // ancestor box), and a `group` of bvhTrees is several trees searched one after the other.  Here: one tree per root,
+  // top-down, 16 centroid bins x 3 axes, surface-area cost; leaves of <= kCollapse primitives (an aggregated cuboid is
+  // one item); leaves store their primitives in evaluation order, storage indices follow the leaf order.
+  // RT_B200_BVH=reference keeps the reference-shaped tree (A/B runs, tests).
+  bool sah = true;
+  uint32_t next_storage = 0;
+  struct Item { uint32_t prim, n; BoxD box; double c[3]; };
+  static double half_area(const BoxD& b) {
+    if (b.empty()) return 0.0;
+    double x = b.hi[0] - b.lo[0], y = b.hi[1] - b.lo[1], z = b.hi[2] - b.lo[2];
+    return x * y + y * z + z * x;
+  }
+  void collect_items(int r, std::vector<Item>& out) {   // DFS = evaluation order
+    const RNode& n = rnodes[r];
+    if (n.kind == RNode::LEAF) {
+      const HPrim& p = prims[n.prim];
+      if ((p.flags & PRIM_FLAG_BOXTAIL) && !out.empty()) {   // faces 1..5 travel with their head
+        out.back().n++;
+        out.back().box.join(p.box);
+        return;
+      }
+      out.push_back(Item{n.prim, 1u, p.box, {0, 0, 0}});
+      return;
+    }
+    for (int c : n.children) collect_items(c, out);
+  }
+  int sah_leaf(std::vector<Item>& items, size_t lo, size_t hi) {
+    std::sort(items.begin() + lo, items.begin() + hi, [&](const Item& a, const Item& b) { return prims[a.prim].ref_index < prims[b.prim].ref_index; });
+    hnodes.emplace_back();
+    const int me = (int)hnodes.size() - 1;
+    HNode& h = hnodes[me];
+    h.first = next_storage;
+    for (size_t i = lo; i < hi; i++) {
+      // an item's primitives are consecutive entries of `prims` (make_planar appends the six faces in order)
+      for (uint32_t k = 0; k < items[i].n; k++) prims[items[i].prim + k].index = next_storage++;
+      h.box.join(items[i].box);
+    }
+    h.count = next_storage - h.first;
+    return me;
+  }
+  int sah_node(std::vector<Item>& items, size_t lo, size_t hi, int depth) {
+    uint32_t n_prims = 0;
+    BoxD cb;   // centroid bounds
+    for (size_t i = lo; i < hi; i++) { n_prims += items[i].n; cb.add({items[i].c[0], items[i].c[1], items[i].c[2]}); }
+    if (hi - lo == 1) return sah_leaf(items, lo, hi);
+    auto item_cost = [](const Item& it) { return it.n == 6 ? 2.0 : 1.0; };   // slab test ~ two planar tests
+    const double kNodeCost = 1.5;     // one node step (two slab tests + stack work) ~ 1.5 primitive tests
+    size_t mid = lo;
+    bool split_found = false;
+    if (depth < 26) {
+      constexpr int kBins = 16;
+      BoxD all;
+      double leaf_cost = 0;
+      for (size_t i = lo; i < hi; i++) { all.join(items[i].box); leaf_cost += item_cost(items[i]); }
+      double best = std::numeric_limits<double>::infinity();
+      int best_axis = -1, best_bin = 0;
+      for (int ax = 0; ax < 3; ax++) {
+        const double ext = cb.hi[ax] - cb.lo[ax];
+        if (!(ext > 0) || !std::isfinite(ext)) continue;
+        BoxD bb[kBins];
+        double bc[kBins] = {0};
+        for (size_t i = lo; i < hi; i++) {
+          int k = std::min(kBins - 1, (int)((items[i].c[ax] - cb.lo[ax]) / ext * kBins));
+          bb[k].join(items[i].box);
+          bc[k] += item_cost(items[i]);
+        }
+        BoxD r;
+        double rc = 0, ra[kBins], rn[kBins];
+        for (int k = kBins - 1; k > 0; k--) { r.join(bb[k]); rc += bc[k]; ra[k] = half_area(r); rn[k] = rc; }
+        BoxD l;
+        double lc = 0;
+        for (int k = 0; k < kBins - 1; k++) {
+          l.join(bb[k]);
+          lc += bc[k];
+          if (lc == 0 || rn[k + 1] == 0) continue;
+          const double c = half_area(l) * lc + ra[k + 1] * rn[k + 1];
+          if (c < best) { best = c; best_axis = ax; best_bin = k; }
+        }
+      }
+      const double area = half_area(all);
+      const bool must_split = n_prims > kCollapse;
+      if (best_axis >= 0 && area > 0 && (must_split || kNodeCost + best / area < leaf_cost)) {
+        const double ext = cb.hi[best_axis] - cb.lo[best_axis];
+        auto it = std::partition(items.begin() + lo, items.begin() + hi, [&](const Item& x) {
+          int k = std::min(kBins - 1, (int)((x.c[best_axis] - cb.lo[best_axis]) / ext * kBins));
+          return k <= best_bin;
+        });
+        mid = (size_t)(it - items.begin());
+        split_found = mid > lo && mid < hi;
+      } else if (!must_split) {
+        return sah_leaf(items, lo, hi);
+      }
+    }
+    if (!split_found) {   // coincident centroids, or too deep for the traversal stack: balanced object-median split
+      if (n_prims <= kCollapse) return sah_leaf(items, lo, hi);
+      const int ax = longest_dim(cb.empty() ? BoxD() : cb);
+      mid = lo + (hi - lo) / 2;
+      std::nth_element(items.begin() + lo, items.begin() + mid, items.begin() + hi,
+                       [&](const Item& a, const Item& b) { return a.c[ax] < b.c[ax]; });
+    }
+    const int l = sah_node(items, lo, mid, depth + 1);
+    const int r = sah_node(items, mid, hi, depth + 1);
+    hnodes.emplace_back();
+    const int me = (int)hnodes.size() - 1;
+    hnodes[me].left = l;
+    hnodes[me].right = r;
+    hnodes[me].box = hnodes[l].box;
+    hnodes[me].box.join(hnodes[r].box);
+    return me;
+  }
+  int to_device_sah(int r) {
+    std::vector<Item> items;
+    collect_items(r, items);
+    uint32_t n_prims = 0;
+    for (Item& it : items) {
+      n_prims += it.n;
+      for (int k = 0; k < 3; k++) it.c[k] = (it.box.lo[k] + it.box.hi[k]) / 2;
+    }
+    if (n_prims <= kLeafMax) return sah_leaf(items, 0, items.size());   // short list: one leaf, scanned (flat kernels)
+    return sah_node(items, 0, items.size(), 0);
+  }
+
   int to_device(int r) {
+    if (sah) return to_device_sah(r);
     const RNode n = rnodes[r];  // copy: hnodes/rnodes may grow
     if (n.kind == RNode::LEAF) {
       hnodes.emplace_back();
@@ -680,6 +810,7 @@ struct Builder {
     fs.prims.assign(n * 16, 0.f);
     fs.tri_uv.assign(n * 8, 0.f);
     fs.canonical.assign(n, kNone);
+    fs.ref_order.assign(n, kNone);
     for (const HPrim& p : prims) {
       if (p.index == kNone) continue;
       float* o = &fs.prims[(size_t)p.index * 16];
@@ -709,6 +840,7 @@ struct Builder {
         for (int k = 0; k < 3; k++) { u[2 * k] = (float)p.uv[k][0]; u[2 * k + 1] = (float)p.uv[k][1]; }
       }
       fs.canonical[p.index] = p.canonical;
+      fs.ref_order[p.index] = p.ref_index;
     }
   }
 };
@@ -810,6 +942,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
       t_last = now;
     };
     if (const char* e = std::getenv("RT_B200_LEAF")) b.kLeafMax = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
+    if (const char* e = std::getenv("RT_B200_BVH")) b.sah = std::strcmp(e, "reference") != 0;
     if (const char* e = std::getenv("RT_B200_NO_BOXES")) b.aggregate_boxes = std::atoi(e) == 0;
     if (const char* e = std::getenv("RT_B200_COLLAPSE")) b.kCollapse = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
     b.mat_used.assign(sc.materials.size(), 0);

@@ -39,6 +39,7 @@ struct FlatScene {
   std::vector<float> prims;      // 16 floats per primitive
   std::vector<float> tri_uv;     // 8 floats per primitive
   std::vector<uint32_t> canonical;
+  std::vector<uint32_t> ref_order;   // device primitive index -> position in the reference's evaluation order
   std::vector<DXform> xforms;
   std::vector<DMaterial> materials;
   std::vector<DTexture> textures;

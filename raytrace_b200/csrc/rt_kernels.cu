@@ -397,7 +397,7 @@ __device__ __forceinline__ Hit scan_flat(const DScene& sc, const FlatList& L, co
 #pragma unroll
     for (int k = 0; k < kFlatBoxes; k++) {
       if (k >= (int)L.n_box) break;
-      intersect_box(L.box[k][0], L.box[k][1], L.box[k][2], L.box[k][3], L.box_first[k], L.box_geom[k], ray.o, ray.d, 1e-4f,
+      intersect_box(sc.ref_order, L.box[k][0], L.box[k][1], L.box[k][2], L.box[k][3], L.box_first[k], L.box_geom[k], ray.o, ray.d, 1e-4f,
                     origin_geom, kNone, false, h);
     }
   }
@@ -914,12 +914,13 @@ static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
   DScene& d = ds->d;
   // one arena, one staging buffer, one H2D copy (256-byte aligned sections)
   struct Sec { const void* src; size_t bytes; size_t off; };
-  Sec secs[10] = {
+  Sec secs[11] = {
       {f.nodes.data(), f.nodes.size() * sizeof(DNode), 0},   {f.prims.data(), f.prims.size() * sizeof(float), 0},
       {f.tri_uv.data(), f.tri_uv.size() * sizeof(float), 0}, {f.xforms.data(), f.xforms.size() * sizeof(DXform), 0},
       {f.materials.data(), f.materials.size() * sizeof(DMaterial), 0}, {f.textures.data(), f.textures.size() * sizeof(DTexture), 0},
       {f.texels.data(), f.texels.size() * sizeof(float), 0}, {f.canonical.data(), f.canonical.size() * sizeof(uint32_t), 0},
-      {f.noise_grad.data(), f.noise_grad.size() * sizeof(float), 0}, {f.noise_perm.data(), f.noise_perm.size(), 0}};
+      {f.noise_grad.data(), f.noise_grad.size() * sizeof(float), 0}, {f.noise_perm.data(), f.noise_perm.size(), 0},
+      {f.ref_order.data(), f.ref_order.size() * sizeof(uint32_t), 0}};
   size_t total_bytes = 0;
   for (Sec& x : secs) { x.off = total_bytes; total_bytes += (x.bytes + 255) / 256 * 256 + 256; }
   std::vector<unsigned char> staging(total_bytes, 0);
@@ -942,6 +943,7 @@ static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
   d.canonical = reinterpret_cast<const uint32_t*>(base + secs[7].off);
   d.noise_grad = reinterpret_cast<const float*>(base + secs[8].off);
   d.noise_perm = reinterpret_cast<const uint8_t*>(base + secs[9].off);
+  d.ref_order = reinterpret_cast<const uint32_t*>(base + secs[10].off);
   if (f.surface_root != kNone && (f.surface_root & kLeafBit)) {
     const uint32_t first = (f.surface_root & ~kLeafBit) >> kLeafShift, count = (f.surface_root & kLeafCountMask) + 1u;
     FlatList& L = ds->flat;

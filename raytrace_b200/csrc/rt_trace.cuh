@@ -114,6 +114,13 @@ struct ParamRec {
   __device__ __forceinline__ float4 r2() const { return R[2]; }
 };
 
+// Exact tie between two primitives (same t to the last bit: coplanar duplicates, shared edges): the reference keeps the
+// one it evaluates first (Geometry.hs:340-345,356-361).  Device indices follow the device tree, so the evaluation order
+// is looked up — on ties only.
+__device__ __forceinline__ bool evaluated_before(const uint32_t* __restrict__ ref_order, uint32_t a, uint32_t b) {
+  return b == kNone || __ldg(ref_order + a) < __ldg(ref_order + b);
+}
+
 // Closest hit of an aggregated cuboid = closest hit over its six parallelogram faces (Geometry.hs:154-166 + :117-144),
 // by the slab method: the boundary of a convex solid is crossed at most twice, at t_in (from outside: front = True) and
 // t_out (from inside).  Per face the reference requires |n.d| > 1e-8 (a parallel ray misses both faces of that axis; the
@@ -122,9 +129,9 @@ struct ParamRec {
 // all of that is t_in's face if it passes, else t_out's.  b0..b3 = box record (rt_device.h), `first` / `geom0` = primitive
 // index / geometry id of face 0; faces +z -z -x +x +y -y = 0..5, axes tested z, x, y so that an exact edge tie goes to the
 // lower face index like the reference's scan.  strict: caller scans in index order (ties lose to earlier primitives).
-__device__ __forceinline__ void intersect_box(const float4 b0, const float4 b1, const float4 b2, const float4 b3, uint32_t first,
-                                              uint32_t geom0, f3 o, f3 d, float tmin, uint32_t skip_a, uint32_t skip_b, bool strict,
-                                              Hit& best) {
+__device__ __forceinline__ void intersect_box(const uint32_t* __restrict__ ref_order, const float4 b0, const float4 b1, const float4 b2,
+                                              const float4 b3, uint32_t first, uint32_t geom0, f3 o, f3 d, float tmin, uint32_t skip_a,
+                                              uint32_t skip_b, bool strict, Hit& best) {
   const f3 oc = mk3(b0.x, b0.y, b0.z) - o;
   // one axis: entry / exit distance of its slab and the face the ray enters through (the exit face is that ^ 1).
   // A parallel ray (|D| <= 1e-8, Geometry.hs:125) gets a huge finite 1/D: inside the slab the two distances become
@@ -151,7 +158,7 @@ __device__ __forceinline__ void intersect_box(const float4 b0, const float4 b1, 
   const bool ok_out = crosses & (t_out > tmin) & (g_out != skip_a) & (g_out != skip_b);
   const float t = ok_in ? t_in : t_out;
   const uint32_t idx = first + (ok_in ? f_in : f_out);
-  if ((ok_in | ok_out) && (t < best.t || (!strict && t == best.t && idx < best.prim))) {
+  if ((ok_in | ok_out) && (t < best.t || (!strict && t == best.t && evaluated_before(ref_order, idx, best.prim)))) {
     best.t = t;
     best.prim = idx;
     best.front = ok_in;
@@ -160,9 +167,9 @@ __device__ __forceinline__ void intersect_box(const float4 b0, const float4 b1, 
 
 // BVH kernels: the box record comes from global memory.  (Out of line — __noinline__ — was tried to keep the slab test's
 // registers out of the traversal loop: the by-reference result then lives on the stack, 80 registers + spills; inline: 72.)
-__device__ __forceinline__ void intersect_box_global(const float4* __restrict__ B, uint32_t first, uint32_t geom0, f3 o, f3 d, float tmin,
+__device__ __forceinline__ void intersect_box_global(const uint32_t* __restrict__ sc_ref_order, const float4* __restrict__ B, uint32_t first, uint32_t geom0, f3 o, f3 d, float tmin,
                                                      uint32_t skip_a, uint32_t skip_b, Hit& best) {
-  intersect_box(__ldg(B), __ldg(B + 1), __ldg(B + 2), __ldg(B + 3), first, geom0, o, d, tmin, skip_a, skip_b, false, best);
+  intersect_box(sc_ref_order, __ldg(B), __ldg(B + 1), __ldg(B + 2), __ldg(B + 3), first, geom0, o, d, tmin, skip_a, skip_b, false, best);
 }
 
 // one primitive; `skip_a` = geometry the ray ORIGIN lies on, `skip_b` = geometry of a hit at tmin
@@ -240,7 +247,7 @@ __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, u
     if constexpr ((F & TF_PLANAR) != 0) {
       if constexpr (Rec::kBoxes && (F & TF_BOX) != 0) {
         if (tf & (PRIM_FLAG_BOXHEAD | PRIM_FLAG_BOXTAIL)) {   // aggregated cuboid: one slab test at the head face
-          if (tf & PRIM_FLAG_BOXHEAD) intersect_box_global(sc.tri_uv + 2 * (size_t)i, i, geom, o, d, tmin, skip_a, skip_b, best);
+          if (tf & PRIM_FLAG_BOXHEAD) intersect_box_global(sc.ref_order, sc.tri_uv + 2 * (size_t)i, i, geom, o, d, tmin, skip_a, skip_b, best);
           return;
         }
       }
@@ -280,7 +287,7 @@ __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, u
       front = denom < 0.f;
     } else return;
   }
-  if (t < best.t || (!kScan && t == best.t && i < best.prim)) {
+  if (t < best.t || (!kScan && t == best.t && evaluated_before(sc.ref_order, i, best.prim))) {
     best.t = t;
     best.prim = i;
     best.front = front;

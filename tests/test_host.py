@@ -48,17 +48,24 @@ def test_product_never_imports_the_oracle():
                 assert "oracle" not in src.replace("no oracle", ""), f
 
 
+@pytest.mark.parametrize("policy", ["sah", "reference"])
 @pytest.mark.parametrize("name", ["readme", "cornell", "demo1", "demo2", "pawn", "bunny_volume"])
-def test_flattened_tree_matches_reference_evaluation_order(built, name):
-    """bvhTree policy (Geometry.hs:369-377) + group order: the device primitive order must equal the oracle's
-    evaluation-order leaf sequence (same split axis, same stable sort, same n div 2 split)."""
+def test_flattened_tree_matches_reference_evaluation_order(built, name, policy, monkeypatch):
+    """bvhTree policy (Geometry.hs:369-377) + group order: the evaluation order the flattener records (it decides exact
+    ties) must equal the oracle's evaluation-order leaf sequence (same split axis, same stable sort, same n div 2
+    split) — whether the device tree is the default SAH tree (its own storage order) or the reference-shaped one
+    (storage order = evaluation order)."""
+    monkeypatch.setenv("RT_B200_BVH", policy)
     ctor, _ = scenes.CONFIGS[name]
     s, w = ctor()
     cs = CompiledScene(w, upload=False)
     nodes, canon = cs.handle.get_bvh()
     ora = OracleScene(w)
     order = ora.leaf_order()
-    assert np.array_equal(canon[: len(order)], order)
+    assert np.array_equal(cs.handle.get_eval_order()[: len(order)], order)
+    assert sorted(canon.tolist()) == sorted(cs.handle.get_eval_order().tolist())
+    if policy == "reference":
+        assert np.array_equal(canon[: len(order)], order)
     info = cs.info()
     assert info["n_bvh_nodes"] == len(nodes) and info["max_depth"] < 32
     # every inner node's box contains its children's boxes; leaf references address valid primitive ranges
