@@ -605,6 +605,7 @@ struct Builder {
   // one item); leaves store their primitives in evaluation order, storage indices follow the leaf order.
   // RT_B200_BVH=reference keeps the reference-shaped tree (A/B runs, tests).
   bool sah = true;
+  double sah_node_cost = 1.0;   // RT_B200_SAH_NODE_COST overrides (sweep: profiles/r01g_sweep_sah.txt)
   uint32_t next_storage = 0;
   struct Item { uint32_t prim, n; BoxD box; double c[3]; };
   static double half_area(const BoxD& b) {
@@ -646,7 +647,7 @@ struct Builder {
     for (size_t i = lo; i < hi; i++) { n_prims += items[i].n; cb.add({items[i].c[0], items[i].c[1], items[i].c[2]}); }
     if (hi - lo == 1) return sah_leaf(items, lo, hi);
     auto item_cost = [](const Item& it) { return it.n == 6 ? 2.0 : 1.0; };   // slab test ~ two planar tests
-    const double kNodeCost = 1.5;     // one node step (two slab tests + stack work) ~ 1.5 primitive tests
+    const double kNodeCost = sah_node_cost;   // one node step (two slab tests + stack work) in units of a primitive test
     size_t mid = lo;
     bool split_found = false;
     if (depth < 26) {
@@ -943,6 +944,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
     };
     if (const char* e = std::getenv("RT_B200_LEAF")) b.kLeafMax = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
     if (const char* e = std::getenv("RT_B200_BVH")) b.sah = std::strcmp(e, "reference") != 0;
+    if (const char* e = std::getenv("RT_B200_SAH_NODE_COST")) b.sah_node_cost = std::max(0.0, std::atof(e));
     if (const char* e = std::getenv("RT_B200_NO_BOXES")) b.aggregate_boxes = std::atoi(e) == 0;
     if (const char* e = std::getenv("RT_B200_COLLAPSE")) b.kCollapse = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
     b.mat_used.assign(sc.materials.size(), 0);

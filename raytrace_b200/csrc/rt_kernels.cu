@@ -1124,7 +1124,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   A.sum = d_sum;
   A.sumsq = d_sumsq;
   A.hits = ds.hits;
-  A.refill = 20;
+  A.refill = 24;
   A.node_burst = 4;
   A.finish_max = 1u << 18;
   if (const char* e = std::getenv("RT_B200_FINISH")) A.finish_max = (uint32_t)std::strtoul(e, nullptr, 10);
