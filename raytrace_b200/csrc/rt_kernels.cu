@@ -182,8 +182,11 @@ __global__ void __launch_bounds__(kTraverseBlock) k_traverse(Ctl* __restrict__ c
 
 constexpr int kPrimBurst = 8;   // primitives tested per PRIMITIVE step
 
+#ifndef RT_TRAV_MINB
+#define RT_TRAV_MINB 8   // resident-block floor of k_traverse_p: caps it at 64 registers (profiles/r01g_sweep_sah.txt)
+#endif
 template <uint32_t F>
-__global__ void __launch_bounds__(kTraverseBlock) k_traverse_p(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
+__global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
                                                                const __grid_constant__ RenderArgs A) {
   extern __shared__ uint32_t s_stack[];   // (scene BVH depth + 1) x kTraverseBlock words: a deeper static stack would only eat L1
   uint32_t* const stack = s_stack + threadIdx.x;
