@@ -650,7 +650,11 @@ struct Builder {
     const double kNodeCost = sah_node_cost;   // one node step (two slab tests + stack work) in units of a primitive test
     size_t mid = lo;
     bool split_found = false;
-    if (depth < 26) {
+    // The traversal stack holds kStackDepth (32) entries: SAH may split as unevenly as it likes only while a balanced
+    // median split of what is left would still fit (depth + ceil(log2 n) stays below 30).
+    int log2n = 0;
+    while (((size_t)1 << log2n) < hi - lo) log2n++;
+    if (depth + 1 + log2n < 30) {
       constexpr int kBins = 16;
       BoxD all;
       double leaf_cost = 0;

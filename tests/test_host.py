@@ -234,3 +234,35 @@ def test_bounding_boxes_follow_the_reference():
     t = rt.transform(rt.translate((1, 0, 0)) @ rt.rotateY(math.pi / 2), rt.sphere((0, 0, 0), 1))
     assert np.allclose(np.array(rt.boundingBox(t)), [[0, 2], [-1, 1], [-1, 1]])
     assert rt.longestDim(((0, 1), (0, 1), (0, 1))) == 2 and rt.longestDim(((0, 2), (0, 2), (0, 1))) == 1  # argMax ties, Core.hs:43-46
+
+
+@pytest.mark.parametrize("case", ["coincident", "peeling", "single", "collinear"])
+def test_sah_builder_pathological_inputs(built, case):
+    """The SAH device tree must stay within the 32-entry traversal stack and reach every primitive whatever the input:
+    identical centroids (no SAH split exists), sizes growing geometrically along a line (SAH peels one primitive per
+    level), a single primitive, thousands of primitives on a line."""
+    mat = rt.lambertian(rt.constantTexture(0.5))
+    if case == "coincident":
+        prims = [mat << rt.sphere((0, 0, -5), 0.5 + 1e-3 * k) for k in range(300)]
+    elif case == "peeling":
+        prims = [mat << rt.sphere((1.5 ** k, 0, -5), 0.4 * 1.5 ** k) for k in range(60)]
+    elif case == "single":
+        prims = [mat << rt.sphere((0, 0, -5), 1)]
+    else:
+        prims = [mat << rt.sphere((0.01 * k, 0, -5), 0.004) for k in range(5000)]
+    cs = CompiledScene(rt.bvhTree(prims), upload=False)
+    info = cs.info()
+    nodes, canon = cs.handle.get_bvh()
+    assert info["n_prims"] == len(prims) and info["max_depth"] < 32
+    assert sorted(cs.handle.get_eval_order().tolist()) == sorted(canon.tolist())
+    if len(prims) <= 24:
+        assert info["n_bvh_nodes"] == 0          # short list: one leaf
+        return
+    ref = nodes[:, 3].view(np.uint32)
+    seen = np.zeros(len(prims), bool)
+    for k in range(len(nodes)):
+        if ref[k] & 0x80000000:
+            first, c = int(ref[k] & 0x7FFFFFFF) >> 5, int(ref[k] & 31) + 1
+            assert not seen[first:first + c].any()
+            seen[first:first + c] = True
+    assert seen.all()
