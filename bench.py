@@ -75,7 +75,9 @@ NCU_TRAFFIC = {
     # (ncu --set full, full 4 Mi-path launches; profiles/r01c_ncu_full_summary.txt).  The bench line reports
     # traffic = this x the measured mean rays per launch of the run, so it stays "per launch like achieved".
     ("cornell", "k_shade"): 400.5e6 / 4194304, ("cornell", "k_traverse"): 153.6e6 / 4194304,
-    ("pawn", "k_shade"): 415.8e6 / 4194304, ("pawn", "k_traverse"): 206.2e6 / 4194304,
+    ("pawn", "k_shade"): 415.8e6 / 4194304,
+    # k_traverse_p on the SAH tree, full 16 Mi-ray launch (profiles/r01g_ncu_full_summary_pawn.txt): 633.9 MB + 106.8 MB
+    ("pawn", "k_traverse"): (633.9e6 + 106.8e6) / 16777216,
     # fused flat-scene kernel (raygen + closest hit + shading + compaction in one launch), full 16 Mi-path launch,
     # profiles/r01f_ncu_full_summary.txt: 660.0 MB read + 608.6 MB written
     ("cornell", "k_trace_flat"): (660.0e6 + 608.6e6) / 16777216,
