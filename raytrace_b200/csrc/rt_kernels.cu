@@ -239,7 +239,8 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
 #pragma unroll 1
         for (int burst = 0; burst < A.node_burst && !(cur & kLeafBit) && want_n; burst++) {
           const float4* N = sc.nodes + 2 * (size_t)cur;
-          const float4 l0 = __ldg(N), h0 = __ldg(N + 1), l1 = __ldg(N + 2), h1 = __ldg(N + 3);
+          const F8 c0 = ldg256(N), c1 = ldg256(N + 2);
+          const float4 l0 = c0.a, h0 = c0.b, l1 = c1.a, h1 = c1.b;
           float tn0, tn1;
           const bool hit0 = box_hit(l0, h0, inv, oinv, tmin, h.t, tn0);
           const bool hit1 = box_hit(l1, h1, inv, oinv, tmin, h.t, tn1);
