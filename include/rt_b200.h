@@ -239,6 +239,15 @@ int32_t rt_probe_primary(RtScene* scene, int32_t device, const RtCamera* cam, do
  * HOST buffer H*W*10. */
 int32_t rt_probe_surface(RtScene* scene, int32_t device, const RtCamera* cam, double time, float* out);
 
+/* Optional page-locked host buffers for rt_render's outputs.  rt_render accepts ANY host pointer; when rgb_out (and
+ * rgb_sumsq_out) point into page-locked memory - from rt_host_alloc, cudaMallocHost or cudaHostRegister - the image is
+ * DMA-copied straight into them, otherwise it goes through the library's pinned staging buffer plus one host memcpy
+ * (0.5 ms for a 600x600 image).  Freed buffers are kept on a small free list and handed out again (cudaMallocHost costs
+ * more than the copy it saves).  The Haskell binding wraps the pointer in a ForeignPtr whose finaliser is rt_host_free,
+ * which is what the massiv array of the result (Ray.hs:238) is built over. */
+int32_t rt_host_alloc(size_t bytes, void** out);
+int32_t rt_host_free(void* p);
+
 /* tuning knobs (0 = default) */
 int32_t rt_set_pool_size(RtScene* scene, uint32_t n_paths);
 

@@ -75,6 +75,8 @@ struct RenderArgs {
   int refill;                     // persistent traversal: idle lanes per warp that trigger a fetch
   int node_burst;                 // persistent traversal: node steps per vote
   uint32_t finish_max;            // k_finish takes over when at most this many paths are left (0 = never)
+  int finish_refill;              // k_finish: idle lanes per warp that trigger a claim of new paths
+  uint32_t tile;                  // camera paths start in 8x4 pixel tiles (1) or in row-major pixel order (0)
 };
 
 // Closes iteration k and prepares iteration k+1 (single thread: the last k_shade block, or k_begin for k = 0).
@@ -83,7 +85,7 @@ __device__ void prepare_iteration(volatile Ctl* ctl, bool first) {
   if (!first) {
     n_cur = ctl->n_next;
     ctl->rays += ctl->n_live;
-    ctl->iterations += 1;
+    if (ctl->n_live) ctl->iterations += 1;   // launches past the end of the render are empty and do not count
   }
   const unsigned long long rem = ctl->total_items - ctl->next_item;
   const unsigned int room = ctl->pool - n_cur;
@@ -116,11 +118,25 @@ __device__ __forceinline__ RayT camera_ray(const DCamera& cam, uint32_t pixel, f
   return r;
 }
 
+// Position p of a sample pass → pixel, walking the image in 8x4 tiles (bands of four rows, eight columns at a time;
+// the last band / last tile of a band may be smaller): the 32 camera rays of a warp then span a compact patch instead
+// of a 32x1 strip, so they visit the same BVH nodes for longer.  A bijection on [0, W*H) for every W, H; the sample
+// set is unchanged because the RNG is keyed by the pixel, not by p.
+__device__ __forceinline__ uint32_t tiled_pixel(uint32_t p, uint32_t W, uint32_t H) {
+  const uint32_t band = p / (4u * W), k = p - band * 4u * W;
+  const uint32_t bh = min(4u, H - 4u * band);
+  const uint32_t t = k / (8u * bh), r = k - t * 8u * bh;
+  const uint32_t tw = min(8u, W - 8u * t);
+  const uint32_t jj = r / tw, ii = r - jj * tw;
+  return (4u * band + jj) * W + 8u * t + ii;
+}
+
 struct NewPath { RayT ray; uint32_t pixel; uint32_t sample_lo; };
-// work item → camera path (Ray.hs:157-172,229): item = local sample index * n_pixels + pixel
+// work item → camera path (Ray.hs:157-172,229): item = local sample index * n_pixels + position in the pass
 __device__ __forceinline__ NewPath new_camera_path(const RenderArgs& A, unsigned long long item) {
   const unsigned long long s_local = item / A.n_pixels;
-  const uint32_t pixel = (uint32_t)(item - s_local * A.n_pixels);
+  uint32_t pixel = (uint32_t)(item - s_local * A.n_pixels);
+  if (A.tile) pixel = tiled_pixel(pixel, (uint32_t)A.cam.W, (uint32_t)A.cam.H);
   const unsigned long long sample = A.first_sample + s_local;
   const uint4 r0 = rng4(A.key, pixel, sample, 0, RNG_RAYGEN);
   float lu = 0.f, lv = 0.f;
@@ -681,9 +697,9 @@ __global__ void k_begin(Ctl* ctl) { prepare_iteration(ctl, true); }
 // iterations, three launches each), one launch finishes them: each thread carries ONE path through its remaining
 // segments (closest hit + shading in a loop, no queue traffic).  Same device functions, same RNG counters → the same
 // samples as the wavefront iterations it replaces.  No-op unless the work items are exhausted and n_live <= A.finish_max.
-template <uint32_t F>
-__global__ void __launch_bounds__(kTraverseBlock) k_finish(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
-                                                           const __grid_constant__ RenderArgs A) {
+// FF != 0: flat scene, closest hit by the constant-bank list scan of k_trace_flat (no BVH, no stack); else trace_segment<F>.
+template <uint32_t F, uint32_t FF>
+__device__ __forceinline__ void finish_paths(Ctl* __restrict__ ctl, const Queue& q, const DScene& sc, const RenderArgs& A, const FlatList* L) {
   extern __shared__ uint32_t s_stack[];
   __shared__ float s_grad[256 * 3];
   __shared__ uint8_t s_perm[3 * 256];
@@ -698,18 +714,47 @@ __global__ void __launch_bounds__(kTraverseBlock) k_finish(Ctl* __restrict__ ctl
   const NoiseTab T{s_grad, s_perm};
   uint32_t* stack = s_stack + threadIdx.x;
   unsigned int segments = 0;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const float4 o4 = q.o[i], d4 = q.d[i], t4 = q.thr[i];
-    uint2 meta = q.meta[i];
-    RayT ray{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
-    f3 thr = mk3(t4.x, t4.y, t4.z);
-    const uint32_t pixel = __float_as_uint(t4.w);
-    uint32_t origin_geom = __float_as_uint(d4.w);
-    const unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
-    for (;;) {
-      const Hit hit = trace_segment<F>(sc, ray, origin_geom, true, A.key, pixel, sample, meta.y, stack, kTraverseBlock);
+  // Every lane is a path carrier: when its path ends it takes the next unclaimed queue slot instead of waiting for the
+  // longest path of the warp (claims are warp-aggregated: one atomic on ctl->trav_next, which prepare_iteration left at 0).
+  constexpr uint32_t kFull = 0xFFFFFFFFu;
+  const uint32_t lane = threadIdx.x & 31u;
+  bool have = false, more = true;   // more (warp-uniform): the queue may still hold unclaimed paths
+  RayT ray{};
+  f3 thr = mk3(0.f, 0.f, 0.f);
+  uint2 meta = make_uint2(0u, 0u);
+  uint32_t pixel = 0, origin_geom = kNone;
+  unsigned long long sample = 0;
+  for (;;) {
+    if (more) {
+      const unsigned int need = __ballot_sync(kFull, !have);
+      if (__popc(need) >= A.finish_refill || need == kFull) {
+        const int leader = __ffs(need) - 1;
+        uint32_t base = 0;
+        if ((int)lane == leader) base = atomicAdd(&ctl->trav_next, (unsigned int)__popc(need));
+        base = __shfl_sync(kFull, base, leader);
+        if (!have) {
+          const uint32_t i = base + __popc(need & ((1u << lane) - 1u));
+          if (i < n) {
+            const float4 o4 = q.o[i], d4 = q.d[i], t4 = q.thr[i];
+            meta = q.meta[i];
+            ray = RayT{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
+            thr = mk3(t4.x, t4.y, t4.z);
+            pixel = __float_as_uint(t4.w);
+            origin_geom = __float_as_uint(d4.w);
+            sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
+            have = true;
+          }
+        }
+        more = base + (uint32_t)__popc(need) < n;
+      }
+    }
+    if (!__any_sync(kFull, have)) break;
+    if (have) {
+      Hit hit;
+      if (FF) hit = scan_flat<FF ? FF : TF_SPHERE>(sc, *L, ray, origin_geom);
+      else hit = trace_segment<F>(sc, ray, origin_geom, true, A.key, pixel, sample, meta.y, stack, kTraverseBlock);
       segments++;
-      if (!shade_path(sc, A, T, ray, hit, thr, origin_geom, pixel, meta)) break;
+      have = shade_path(sc, A, T, ray, hit, thr, origin_geom, pixel, meta);
     }
   }
   // bookkeeping: segments traced, and (last block) the render is complete
@@ -726,7 +771,27 @@ __global__ void __launch_bounds__(kTraverseBlock) k_finish(Ctl* __restrict__ ctl
     }
   }
 }
+template <uint32_t F>
+__global__ void __launch_bounds__(kTraverseBlock) k_finish(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
+                                                           const __grid_constant__ RenderArgs A) {
+  finish_paths<F, 0>(ctl, q, sc, A, nullptr);
+}
 template <uint32_t F> struct FinishK { static TraverseFn fn() { return k_finish<F>; } };
+
+template <uint32_t FF>
+__global__ void __launch_bounds__(kTraverseBlock, 8) k_finish_flat(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
+                                                                   const __grid_constant__ RenderArgs A, const __grid_constant__ FlatList L) {
+  finish_paths<FF, FF>(ctl, q, sc, A, &L);
+}
+using FinishFlatFn = void (*)(Ctl*, Queue, const DScene, const RenderArgs, const FlatList);
+static FinishFlatFn pick_finish_flat(uint32_t features) {
+  switch (features & (TF_SPHERE | TF_PLANAR)) {
+    case TF_SPHERE: return k_finish_flat<TF_SPHERE>;
+    case TF_PLANAR: return k_finish_flat<TF_PLANAR>;
+    case TF_SPHERE | TF_PLANAR: return k_finish_flat<TF_SPHERE | TF_PLANAR>;
+    default: return nullptr;
+  }
+}
 
 // ---- deterministic primary-ray probe (parity gate: primitive id + t) --------------------------------------
 __global__ void __launch_bounds__(kTraverseBlock) k_probe(const __grid_constant__ DScene sc, const __grid_constant__ DCamera cam, float time,
@@ -1130,8 +1195,19 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   A.hits = ds.hits;
   A.refill = 24;
   A.node_burst = 4;
-  A.finish_max = 1u << 18;
+  // k_finish takes over the tail.  Flat scenes: with the constant-bank scan a lane that carries its path to the end
+  // (and claims the next one when it dies) is faster per ray than a wavefront iteration once no camera rays are left to
+  // generate, so it takes over as soon as every path has started, whatever their number.  BVH scenes: worth it only when
+  // the depth limit leaves dozens of near-empty iterations to replace (demo1 / demo2, depth 50); at depth 20 with
+  // subsurface media (pawn, bunny) the iterations are cheaper.  Sweeps: profiles/r01h_sweep_tail.txt
+  A.finish_max = dev.has_flat ? 0xFFFFFFFFu : (cam.max_depth > 24 ? 1u << 20 : 0u);
   if (const char* e = std::getenv("RT_B200_FINISH")) A.finish_max = (uint32_t)std::strtoul(e, nullptr, 10);
+  A.finish_refill = 4;
+  if (const char* e = std::getenv("RT_B200_FINISH_REFILL")) A.finish_refill = std::min(32, std::max(1, std::atoi(e)));
+  A.tile = dev.has_flat ? 0u : 1u;   // coherence only matters to the BVH kernels; the flat scan is the same for every ray
+  if (const char* e = std::getenv("RT_B200_TILE")) A.tile = std::atoi(e) ? 1u : 0u;
+  int tail_batch = 3;                // iterations (each followed by a k_finish check) per host round trip once all paths have started
+  if (const char* e = std::getenv("RT_B200_TAIL_BATCH")) tail_batch = std::min(64, std::max(1, std::atoi(e)));
   if (const char* e = std::getenv("RT_B200_NODE_BURST")) A.node_burst = std::min(8, std::max(1, std::atoi(e)));
   if (const char* e = std::getenv("RT_B200_REFILL")) A.refill = std::min(32, std::max(1, std::atoi(e)));
   Ctl init{};
@@ -1157,6 +1233,8 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   const FlatFn flat = dev.has_flat ? pick_flat(s.flat.features) : nullptr;
   const TraceFlatFn fused = dev.has_flat ? pick_trace_flat(s.flat.features) : nullptr;
   const TraverseFn finish = pick_by_features<FinishK>(s.flat.features);
+  const FinishFlatFn finish_flat = fused ? pick_finish_flat(s.flat.features) : nullptr;
+  if (dev.has_flat && !finish_flat && !std::getenv("RT_B200_FINISH")) A.finish_max = 1u << 18;   // A/B variants of the flat path: generic k_finish
   int g_trav = dev.sm_count * 8, g_shade = dev.sm_count * 8, g_gen = dev.sm_count * 4;
   if (const char* e = std::getenv("RT_B200_TRAV_BLOCKS")) g_trav = dev.sm_count * std::max(1, std::atoi(e));
   const size_t stack_bytes = (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t);
@@ -1170,6 +1248,11 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   k_begin<<<1, 1, 0, stream>>>(ds.ctl);
   launches++;
   unsigned long long batch = 4, prev_started = 0;
+  // tail mode: every camera path has started (known up front when the whole range fits the pool, e.g. one GPU's share
+  // of a small render).  From then on k_finish is checked after EVERY iteration - a ~2 us no-op until few enough paths
+  // are left - so the takeover never waits for a host round trip, and launches queued past it are empty.
+  bool tail = total <= ds.pool;
+  if (tail && A.finish_max) batch = (unsigned long long)tail_batch;
   for (;;) {
     for (unsigned long long b = 0; b < batch; b++) {
       Queue& q = ds.q[cur];
@@ -1191,10 +1274,11 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
       if (t_this) { cudaEventRecord(ds.events[timed * 4 + 2], stream); timed++; }
       cur ^= 1;
       iter++;
-    }
-    if (A.finish_max) {   // device-side decision: no-op until the work items are exhausted and few paths are left
-      finish<<<dev.sm_count * 4, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, ds.q[cur], dev.d, A);
-      launches++;
+      if (A.finish_max && (tail || b + 1 == batch)) {   // device-side decision: no-op until the work items are exhausted and few paths are left
+        if (finish_flat) finish_flat<<<dev.sm_count * 8, kTraverseBlock, 0, stream>>>(ds.ctl, ds.q[cur], dev.d, A, dev.flat);
+        else finish<<<dev.sm_count * 8, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, ds.q[cur], dev.d, A);
+        launches++;
+      }
     }
     RT_CUDA(cudaMemcpyAsync(ds.h_ctl, ds.ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, stream));
     RT_CUDA(cudaStreamSynchronize(stream));
@@ -1203,7 +1287,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
     const double per_iter = (double)(started - prev_started) / (double)batch;
     prev_started = started;
     if (left > 0 && per_iter >= 1.0) batch = (unsigned long long)std::min(4096.0, std::max(4.0, 0.9 * (double)left / per_iter));
-    else batch = A.finish_max ? 3 : 8;
+    else { tail = true; batch = A.finish_max ? (unsigned long long)tail_batch : 8; }
     if (iter > 100000000u) { set_error("wavefront loop did not terminate"); return RT_ERR_CUDA; }
   }
   if (timing) { RT_CUDA(cudaEventRecord(ev_end, stream)); RT_CUDA(cudaEventSynchronize(ev_end)); }
@@ -1304,6 +1388,67 @@ int32_t rt_render_device(RtScene* sp, int32_t device, const RtCamera* rc, uint64
   return run_wavefront(s, *ds, *lease.w, cam, seed, first_sample, n_samples, d_sum, d_sumsq, stream, stats);
 }
 
+// ---- page-locked host buffers for the caller's image (recycled: cudaMallocHost / cudaFreeHost cost ~0.3 ms each) ----
+static std::mutex g_host_mu;
+static std::map<void*, size_t> g_host_live;                  // handed out: pointer → capacity
+static std::multimap<size_t, void*> g_host_free;             // capacity → buffer, at most kHostFreeMax bytes kept
+static size_t g_host_free_bytes = 0;
+constexpr size_t kHostFreeMax = 256u << 20;
+
+int32_t rt_host_alloc(size_t bytes, void** out) {
+  if (!out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  *out = nullptr;
+  if (bytes == 0) bytes = 1;
+  const size_t cap = (bytes + 4095) / 4096 * 4096;
+  {
+    std::lock_guard<std::mutex> lock(g_host_mu);
+    auto it = g_host_free.lower_bound(cap);
+    if (it != g_host_free.end() && it->first <= cap + cap / 4) {   // close enough in size: reuse
+      *out = it->second;
+      g_host_live[it->second] = it->first;
+      g_host_free_bytes -= it->first;
+      g_host_free.erase(it);
+      return RT_OK;
+    }
+  }
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    set_error("no CUDA device visible: page-locked buffers need the CUDA driver (there is no CPU fallback)");
+    return RT_ERR_NO_DEVICE;
+  }
+  void* p = nullptr;
+  cudaError_t e = cudaHostAlloc(&p, cap, cudaHostAllocPortable);
+  if (e != cudaSuccess) { set_error(std::string("cudaHostAlloc failed: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
+  std::lock_guard<std::mutex> lock(g_host_mu);
+  g_host_live[p] = cap;
+  *out = p;
+  return RT_OK;
+}
+
+int32_t rt_host_free(void* p) {
+  if (!p) return RT_OK;
+  size_t cap = 0;
+  bool keep = false;
+  {
+    std::lock_guard<std::mutex> lock(g_host_mu);
+    auto it = g_host_live.find(p);
+    if (it == g_host_live.end()) { set_error("rt_host_free: not a buffer from rt_host_alloc"); return RT_ERR_INVALID_ARG; }
+    cap = it->second;
+    g_host_live.erase(it);
+    if (g_host_free_bytes + cap <= kHostFreeMax) { g_host_free.emplace(cap, p); g_host_free_bytes += cap; keep = true; }
+  }
+  if (!keep) cudaFreeHost(p);
+  return RT_OK;
+}
+
+// true when [p, p + bytes) is page-locked memory the copy engines can write directly
+static bool is_pinned_host(const void* p, size_t bytes) {
+  cudaPointerAttributes a0{}, a1{};
+  if (cudaPointerGetAttributes(&a0, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  if (cudaPointerGetAttributes(&a1, static_cast<const char*>(p) + bytes - 1) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a0.type == cudaMemoryTypeHost && a1.type == cudaMemoryTypeHost;
+}
+
 int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample,
                   uint64_t n_samples, float* rgb_out, float* rgb_sumsq_out, RtStats* stats) {
   if (!sp || !rc || !rgb_out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
@@ -1335,13 +1480,19 @@ int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed
   RT_CUDA(cudaEventCreate(&c1));
   k_scale<<<ds->sm_count * 4, 256, 0, stream>>>(ws.sum, ws.out, (int)elems, 1.0f / (float)cam.spp);   // Ray.hs:232
   RT_CUDA(cudaEventRecord(c0, stream));
-  // device → pinned staging (full PCIe rate, asynchronous) → caller's pageable buffer
-  RT_CUDA(cudaMemcpyAsync(ws.h_out, ws.out, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
-  if (rgb_sumsq_out) RT_CUDA(cudaMemcpyAsync(ws.h_out + ws.accum_elems, ws.sumsq, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  // page-locked caller buffers (rt_host_alloc, …) are written by the copy engine directly; pageable ones go
+  // device → pinned staging (full PCIe rate, asynchronous) → one host memcpy
+  const bool direct = is_pinned_host(rgb_out, elems * sizeof(float)) && (!rgb_sumsq_out || is_pinned_host(rgb_sumsq_out, elems * sizeof(float)));
+  float* h_rgb = direct ? rgb_out : ws.h_out;
+  float* h_sq = direct ? rgb_sumsq_out : ws.h_out + ws.accum_elems;
+  RT_CUDA(cudaMemcpyAsync(h_rgb, ws.out, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  if (rgb_sumsq_out) RT_CUDA(cudaMemcpyAsync(h_sq, ws.sumsq, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
   RT_CUDA(cudaEventRecord(c1, stream));
   RT_CUDA(cudaStreamSynchronize(stream));
-  std::memcpy(rgb_out, ws.h_out, elems * sizeof(float));
-  if (rgb_sumsq_out) std::memcpy(rgb_sumsq_out, ws.h_out + ws.accum_elems, elems * sizeof(float));
+  if (!direct) {
+    std::memcpy(rgb_out, ws.h_out, elems * sizeof(float));
+    if (rgb_sumsq_out) std::memcpy(rgb_sumsq_out, ws.h_out + ws.accum_elems, elems * sizeof(float));
+  }
   if (stats) {
     float ms = 0;
     cudaEventElapsedTime(&ms, c0, c1);

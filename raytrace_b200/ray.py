@@ -140,6 +140,36 @@ def _classified(fn):
 
 # ---- raytrace -----------------------------------------------------------------------------------
 
+class _PinnedBuffer:
+    """Owner of one page-locked float32 buffer from rt_host_alloc; numpy arrays built over it keep it alive
+    (``__array_interface__``) and it goes back to the library's free list when the last of them is dropped."""
+
+    def __init__(self, n_floats: int):
+        self._lib = _ffi.lib()
+        p = C.c_void_p()
+        _ffi.check(self._lib.rt_host_alloc(max(1, n_floats) * 4, C.byref(p)))
+        self._ptr = p.value
+        self.__array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (self._ptr, False), "version": 3}
+
+    def __del__(self):
+        try:
+            if self._ptr:
+                self._lib.rt_host_free(C.c_void_p(self._ptr))
+                self._ptr = None
+        except Exception:      # interpreter shutdown
+            pass
+
+
+def _image_buffer(h: int, w: int) -> np.ndarray:
+    """H×W×3 float32 result array over page-locked memory: rt_render's copy engine writes it directly (no staging
+    memcpy).  ``RT_B200_PINNED_OUT=0`` falls back to an ordinary pageable numpy array."""
+    import os
+    if os.environ.get("RT_B200_PINNED_OUT", "1") == "0":
+        return np.empty((h, w, 3), dtype=np.float32)
+    return np.asarray(_PinnedBuffer(h * w * 3)).reshape(h, w, 3)
+
+
+
 class CompiledScene:
     """A committed + uploaded scene; reusable across renders (the upload happens once)."""
 
@@ -168,8 +198,8 @@ class CompiledScene:
         cam = self.camera(settings)
         h, w = imageHeight(settings), settings.cs_imageWidth
         n = settings.cs_samplesPerPixel if n_samples is None else int(n_samples)
-        out = np.empty((h, w, 3), dtype=np.float32)
-        sq = np.empty((h, w, 3), dtype=np.float32) if want_sumsq else None
+        out = _image_buffer(h, w)
+        sq = _image_buffer(h, w) if want_sumsq else None
         stats = _ffi.RtStats()
         _ffi.check(L.rt_render(self.handle.handle, self.device, C.byref(cam), C.c_uint64(seed.seed),
                                C.c_uint64(first_sample), C.c_uint64(n),

@@ -214,3 +214,58 @@ def test_aggregated_cuboids(built, tree, monkeypatch):
     assert abs(st["rays"] / st["samples"] - cnt["rays"] / cnt["samples"]) < 0.01 * cnt["rays"] / cnt["samples"]
     z = z_scores(img.astype(np.float64), sq.astype(np.float64), 512, ref, rsq, 512)
     assert (np.abs(z) > 4).mean() < 2e-3
+
+
+TAIL_CASES = [
+    ("cornell", dict(width=37, spp=24)),               # flat scene: k_finish_flat takes the whole tail
+    ("demo1", dict(width=45, spp=8)),                  # BVH, depth 50: generic k_finish below 1 Mi paths
+    ("pawn", dict(width=35, spp=8)),                   # BVH + subsurface medium, depth 20: no tail kernel by default
+]
+
+
+@pytest.mark.parametrize("name,kw", TAIL_CASES, ids=[c[0] for c in TAIL_CASES])
+def test_tail_kernel_and_tiled_start_order_do_not_change_the_samples(built, name, kw, monkeypatch):
+    """The tail kernel (lanes carry a path to its end and claim the next one) and the 8x4-tiled order in which camera
+    paths start only reschedule work: the RNG is keyed by (pixel, sample, bounce), so every variant renders the same
+    sample set and images differ by fp32 summation order alone.  Image sizes are deliberately not multiples of the
+    tile (ragged last band / last tile)."""
+    ctor, seed = scenes.CONFIGS[name]
+    s, w = ctor(**kw)
+    cs = CompiledScene(w)
+    base = cs.render(s, rt.mkStdGen(seed))
+    assert np.isfinite(base).all()
+    variants = [{"RT_B200_FINISH": "0"}, {"RT_B200_FINISH": "4294967295"}, {"RT_B200_FINISH": "300", "RT_B200_TAIL_BATCH": "1"},
+                {"RT_B200_TILE": "0"}, {"RT_B200_TILE": "1"}, {"RT_B200_FINISH_REFILL": "32", "RT_B200_FINISH": "100000"}]
+    for env in variants:
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        img, st = cs.render(s, rt.mkStdGen(seed), want_stats=True)
+        for k in env:
+            monkeypatch.delenv(k)
+        assert st["samples"] == base.shape[0] * base.shape[1] * s.cs_samplesPerPixel
+        assert np.allclose(img, base, rtol=2e-4, atol=2e-5), env
+
+
+def test_page_locked_output_buffers(built, monkeypatch):
+    """rt_render writes page-locked caller buffers (rt_host_alloc) directly and pageable ones through its staging
+    buffer; both hold the same image.  Freed buffers are recycled; foreign pointers are refused."""
+    import ctypes as C
+    from raytrace_b200 import _ffi
+    s, w = scenes.readme_example(width=80, spp=8)
+    cs = CompiledScene(w)
+    pinned, sq = cs.render(s, rt.mkStdGen(5), want_sumsq=True)
+    monkeypatch.setenv("RT_B200_PINNED_OUT", "0")
+    pageable, sq2 = cs.render(s, rt.mkStdGen(5), want_sumsq=True)
+    monkeypatch.delenv("RT_B200_PINNED_OUT")
+    assert np.allclose(pinned, pageable, rtol=2e-4, atol=2e-5) and np.allclose(sq, sq2, rtol=2e-4, atol=2e-5)
+    keep = pinned.copy()
+    del pinned, sq                     # buffers go back to the library's free list ...
+    again = cs.render(s, rt.mkStdGen(5))
+    assert np.allclose(again, keep, rtol=2e-4, atol=2e-5)
+    L = _ffi.lib()
+    p, q = C.c_void_p(), C.c_void_p()
+    assert L.rt_host_alloc(1 << 16, C.byref(p)) == 0 and p.value
+    assert L.rt_host_free(p) == 0
+    assert L.rt_host_alloc(1 << 16, C.byref(q)) == 0 and q.value == p.value      # ... and are handed out again
+    assert L.rt_host_free(q) == 0
+    assert L.rt_host_free(q) == 1      # double free / foreign pointer: RT_ERR_INVALID_ARG, nothing is touched

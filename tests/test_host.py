@@ -40,6 +40,21 @@ def test_no_gpu_is_a_loud_error_not_a_fallback(built):
     assert e.value.status == 7 and "no CPU fallback" in e.value.message
 
 
+def test_page_locked_buffers_need_the_driver(built):
+    """rt_host_alloc without a CUDA device is RT_ERR_NO_DEVICE (never a silent malloc); rt_host_free refuses pointers
+    it did not hand out."""
+    L = _ffi.lib()
+    n = ctypes.c_int32(-1)
+    L.rt_device_count(ctypes.byref(n))
+    p = ctypes.c_void_p()
+    if n.value == 0:
+        assert L.rt_host_alloc(4096, ctypes.byref(p)) == 7 and not p.value
+        assert b"no CPU fallback" in L.rt_last_error()
+    assert L.rt_host_free(ctypes.c_void_p(4096)) == 1
+    assert L.rt_host_free(None) == 0
+    assert L.rt_host_alloc(16, None) == 1
+
+
 def test_product_never_imports_the_oracle():
     for dirpath, _, files in os.walk(os.path.join(ROOT, "raytrace_b200")):
         for f in files:
