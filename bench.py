@@ -256,7 +256,8 @@ def main():
     # ---- e2e: public API with HOST buffers; scene commit + upload + render + image read-back per step ----
     e2e_ms = []
     h2d = 0
-    for k in range(max(1, min(args.steps, 3))):
+    n_e2e_warm = 2                                           # first calls allocate the workspace's image buffers and the page-locked result
+    for k in range(n_e2e_warm + max(1, min(args.steps, 5))):
         barrier()
         t0 = time.perf_counter()
         cs2 = CompiledScene(world, device=local_rank)       # host description -> flatten -> H2D
@@ -274,8 +275,25 @@ def main():
         dt = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
         if distributed:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e_ms.append(float(dt.item()))
+        if k >= n_e2e_warm:
+            e2e_ms.append(float(dt.item()))
         del cs2
+
+    # ---- the collective alone (sample-sharded runs): one reduce(SUM) of the fp32 image to rank 0, device-timed ----
+    reduce_ms = None
+    if distributed:
+        ts = []
+        for k in range(5):
+            dist.barrier()
+            r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            r0.record(stream)
+            dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
+            r1.record(stream)
+            r1.synchronize()
+            ts.append(r0.elapsed_time(r1))
+        t = torch.tensor([statistics.median(ts)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        reduce_ms = float(t.item())
 
     if rank != 0:
         if distributed:
@@ -288,6 +306,11 @@ def main():
     trav_ms = sum(s["ms_traverse"] for s in stats)
     shade_ms = sum(s["ms_shade"] for s in stats)
     iters = sum(s["iterations"] for s in stats)
+    fin_ms = sum(s["ms_finish"] for s in stats)
+    fin_rays = sum(s["rays_finish"] for s in stats)
+    fin_paths = sum(s["paths_finish"] for s in stats)
+    iter_launches = iters - sum(1 for s in stats if s["paths_finish"])   # the tail kernel counts as one iteration
+    iter_rays = rays - fin_rays                                           # segments traced by the iteration kernels
     launches = sum(s["launches"] for s in stats)
 
     # ---- CPU baseline + the oracle's traversal counters (they define the algorithmic bytes per ray) ----
@@ -314,13 +337,15 @@ def main():
     if fused:
         # compulsory HBM traffic of the fused kernel: every segment except a path's first reads its 56-byte record, and
         # every path that continues writes one (new camera paths are generated in registers; no hit buffer)
-        fz_bytes = 112.0 * max(rays - samples_rendered, 0)
+        # (the paths handed to the tail kernel were written by the last iteration and are read by k_finish_flat)
+        fz_bytes = 112.0 * max(iter_rays - samples_rendered, 0) + 56.0 * fin_paths
         ach = fz_bytes / (shade_ms * 1e-3) / 1e9
         kernels["k_trace_flat"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                                   "traffic": (NCU_TRAFFIC[(args.scene, "k_trace_flat")] * rays / max(iters, 1)) if (args.scene, "k_trace_flat") in NCU_TRAFFIC else None,
-                                   "bytes_per_ray_algorithmic": fz_bytes / max(rays, 1),
-                                   "avg_launch_ms": shade_ms / max(iters, 1), "ms_per_step": shade_ms / args.steps,
-                                   "algorithmic_bytes_per_launch": fz_bytes / max(iters, 1),
+                                   "traffic": (NCU_TRAFFIC[(args.scene, "k_trace_flat")] * iter_rays / max(iter_launches, 1)) if (args.scene, "k_trace_flat") in NCU_TRAFFIC else None,
+                                   "bytes_per_ray_algorithmic": fz_bytes / max(iter_rays, 1),
+                                   "avg_launch_ms": shade_ms / max(iter_launches, 1), "ms_per_step": shade_ms / args.steps,
+                                   "algorithmic_bytes_per_launch": fz_bytes / max(iter_launches, 1),
+                                   "rays_per_launch": iter_rays / max(iter_launches, 1),
                                    "note": "queue traffic only: the scene list is constant-bank resident.  The kernel's limiter is "
                                            "instruction issue (ncu: 73 % issue-active, 27 of 32 threads per instruction) - see roofline_fp32"}
         if bytes_per_ray is not None and aux.get("fp32_fma_tflops"):
@@ -328,7 +353,7 @@ def main():
             # each redirect target one planar test + 10)
             f_shade = 40 + 74 * len(settings.cs_redirectTargets)
             fl = flops_per_ray(n_node, n_sph, n_pl) + f_shade
-            ach = rays * fl / (shade_ms * 1e-3) / 1e12
+            ach = iter_rays * fl / (shade_ms * 1e-3) / 1e12
             roof_fp32 = {"kernel": "k_trace_flat", "achieved": ach, "peak": aux["fp32_fma_tflops"], "unit": "TFLOP/s",
                          "frac": ach / aux["fp32_fma_tflops"], "flops_per_ray_algorithmic": fl,
                          "peak_source": "tools/peaks.cu, measured in this run (FFMA chains)",
@@ -337,17 +362,17 @@ def main():
         # k_shade streams the wavefront state (SURVEY 8(d)'s constant term): per ray segment it reads the 56-byte path
         # record + the 8-byte hit, and writes a 56-byte record for every path that continues (rays - samples of them:
         # each sample ends exactly once).  This is compulsory HBM traffic (the queues exceed L2).
-        sh_bytes = 64.0 * rays + 56.0 * max(rays - samples_rendered, 0)
+        sh_bytes = 64.0 * iter_rays + 56.0 * (max(iter_rays - samples_rendered, 0) + fin_paths)
         ach = sh_bytes / (shade_ms * 1e-3) / 1e9
         kernels["k_shade"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                              "traffic": (NCU_TRAFFIC[(args.scene, "k_shade")] * rays / max(iters, 1)) if (args.scene, "k_shade") in NCU_TRAFFIC else None, "bytes_per_ray_algorithmic": sh_bytes / max(rays, 1),
-                              "avg_launch_ms": shade_ms / max(iters, 1), "ms_per_step": shade_ms / args.steps,
-                              "algorithmic_bytes_per_launch": sh_bytes / max(iters, 1)}
+                              "traffic": (NCU_TRAFFIC[(args.scene, "k_shade")] * iter_rays / max(iter_launches, 1)) if (args.scene, "k_shade") in NCU_TRAFFIC else None, "bytes_per_ray_algorithmic": sh_bytes / max(iter_rays, 1),
+                              "avg_launch_ms": shade_ms / max(iter_launches, 1), "ms_per_step": shade_ms / args.steps,
+                              "algorithmic_bytes_per_launch": sh_bytes / max(iter_launches, 1)}
     if bytes_per_ray is not None and trav_ms > 0 and not fused:
-        achieved = rays * bytes_per_ray / (trav_ms * 1e-3) / 1e9
+        achieved = iter_rays * bytes_per_ray / (trav_ms * 1e-3) / 1e9
         kernels["k_traverse"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                                 "traffic": (NCU_TRAFFIC[(args.scene, "k_traverse")] * rays / max(iters, 1)) if (args.scene, "k_traverse") in NCU_TRAFFIC else None, "bytes_per_ray_algorithmic": bytes_per_ray,
-                                 "avg_launch_ms": trav_ms / max(iters, 1), "ms_per_step": trav_ms / args.steps,
+                                 "traffic": (NCU_TRAFFIC[(args.scene, "k_traverse")] * iter_rays / max(iter_launches, 1)) if (args.scene, "k_traverse") in NCU_TRAFFIC else None, "bytes_per_ray_algorithmic": bytes_per_ray,
+                                 "avg_launch_ms": trav_ms / max(iter_launches, 1), "ms_per_step": trav_ms / args.steps,
                                  "frac_of_measured_l2": achieved / aux["l2_read_gbs"] if aux.get("l2_read_gbs") else None,
                                  "note": "SURVEY 8(d) algorithmic bytes (32*N_node + 16*N_sphere + 48*N_planar + 128, the REFERENCE's "
                                          "per-ray test counts from the oracle).  The scene records are cache / constant-bank resident "
@@ -355,16 +380,26 @@ def main():
                                          "kernel's real limiter is instruction issue — see roofline_fp32 and profiles/"}
         if aux.get("fp32_fma_tflops"):
             fl = flops_per_ray(n_node, n_sph, n_pl)
-            ach = rays * fl / (trav_ms * 1e-3) / 1e12
+            ach = iter_rays * fl / (trav_ms * 1e-3) / 1e12
             roof_fp32 = {"kernel": "k_traverse", "achieved": ach, "peak": aux["fp32_fma_tflops"], "unit": "TFLOP/s",
                          "frac": ach / aux["fp32_fma_tflops"], "flops_per_ray_algorithmic": fl,
                          "peak_source": "tools/peaks.cu, measured in this run (FFMA chains)",
                          "l2_read_gbs_measured": aux.get("l2_read_gbs")}
+    if fin_paths and fin_ms > 0:
+        # the tail kernel: each lane carries a path to its end; HBM traffic is one 56-byte record per path it takes over
+        # (plus the accumulator atomics), so it is latency / issue bound by construction - reported for its share of the step
+        kernels["k_finish"] = {"bound": "hbm", "achieved": 56.0 * fin_paths / (fin_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                               "frac": 56.0 * fin_paths / (fin_ms * 1e-3) / 1e9 / peak, "traffic": None,
+                               "bytes_per_ray_algorithmic": 56.0 * fin_paths / max(fin_rays, 1), "avg_launch_ms": fin_ms / args.steps,
+                               "ms_per_step": fin_ms / args.steps, "rays_per_launch": fin_rays / args.steps,
+                               "mrays_per_s": fin_rays / (fin_ms * 1e-3) / 1e6,
+                               "note": "tail kernel (k_finish_flat / k_finish): no queue traffic after the first read; issue / latency bound"}
     if kernels:
         # the dominant kernel = the one with the larger share of the step
         dom = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
         roof = dict(kernels[dom], kernel=dom, peak_source=f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
-                    rays_per_launch=rays / max(iters, 1), other_kernels={k: v for k, v in kernels.items() if k != dom})
+                    other_kernels={k: v for k, v in kernels.items() if k != dom})
+        roof.setdefault("rays_per_launch", iter_rays / max(iter_launches, 1))
     e2e_val = total_samples / (statistics.median(e2e_ms) * 1e-3) / 1e6
     line = {
         "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world_size, "steps": args.steps,
@@ -375,8 +410,8 @@ def main():
                    "l2": "256 MiB flush between timed steps", "pool": stats[-1]["pool"]},
         "mrays_per_s": rays / (total_ms * 1e-3) / 1e6 * (world_size if distributed else 1),
         "rays_per_sample": rays / (count * W * H * args.steps),
-        "kernel_ms_per_step": {"traverse": trav_ms / args.steps, "shade": shade_ms / args.steps,
-                               "iterations": iters / args.steps},
+        "kernel_ms_per_step": {"traverse": trav_ms / args.steps, "shade": shade_ms / args.steps, "finish": fin_ms / args.steps,
+                               "iterations": iters / args.steps, "reduce": reduce_ms},
         "gpu_launches": int(launches),
         "e2e": {"value": e2e_val, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": W * H * 3 * 4,
                 "ms_per_step": statistics.median(e2e_ms)},

@@ -163,6 +163,9 @@ typedef struct RtStats {
   double ms_shade;         /* device time spent in the shading/scatter/compaction kernel          */
   double ms_raygen;        /* device time spent in camera-ray generation                          */
   double ms_copy;          /* host<->device copies done by this call                              */
+  double ms_finish;        /* device time of the tail kernel (k_finish); ms_raygen is what is left of ms_total */
+  uint64_t rays_finish;    /* segments traced by the tail kernel (included in rays)               */
+  uint64_t paths_finish;   /* paths the tail kernel carried to their end                          */
 } RtStats;
 
 typedef struct RtSceneInfo {

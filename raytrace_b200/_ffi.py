@@ -79,7 +79,8 @@ class RtStats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("rays", C.c_uint64), ("launches", C.c_uint64),
                 ("iterations", C.c_uint32), ("pool", C.c_uint32),
                 ("ms_total", C.c_double), ("ms_traverse", C.c_double), ("ms_shade", C.c_double),
-                ("ms_raygen", C.c_double), ("ms_copy", C.c_double)]
+                ("ms_raygen", C.c_double), ("ms_copy", C.c_double), ("ms_finish", C.c_double),
+                ("rays_finish", C.c_uint64), ("paths_finish", C.c_uint64)]
 
     def as_dict(self) -> Dict[str, float]:
         return {n: getattr(self, n) for n, _ in self._fields_}

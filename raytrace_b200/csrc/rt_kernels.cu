@@ -55,6 +55,8 @@ struct Ctl {                      // device-resident control block of one render
   unsigned int iterations, pool;
   unsigned int trav_next;         // next queue slot the persistent traversal warps fetch
   unsigned int blocks_done;       // k_shade blocks finished (the last one prepares the next iteration)
+  unsigned int paths_finish;      // paths the tail kernel took over
+  unsigned long long rays_finish; // segments traced by the tail kernel (also counted in rays)
 };
 
 struct Queue {                    // SoA live-ray queue (56 B per path)
@@ -759,12 +761,13 @@ __device__ __forceinline__ void finish_paths(Ctl* __restrict__ ctl, const Queue&
   }
   // bookkeeping: segments traced, and (last block) the render is complete
   for (int o = 16; o > 0; o >>= 1) segments += __shfl_down_sync(0xFFFFFFFFu, segments, o);
-  if ((threadIdx.x & 31) == 0 && segments) atomicAdd(&ctl->rays, (unsigned long long)segments);
+  if ((threadIdx.x & 31) == 0 && segments) { atomicAdd(&ctl->rays, (unsigned long long)segments); atomicAdd(&ctl->rays_finish, (unsigned long long)segments); }
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
     if (atomicAdd(&ctl->blocks_done, 1u) == gridDim.x - 1) {
       ctl->blocks_done = 0;
+      ctl->paths_finish += n;
       ctl->n_live = 0;
       ctl->n_cur = 0;
       ctl->iterations += 1;
@@ -1159,9 +1162,8 @@ static int32_t ensure_workspace(Workspace& ds, uint32_t pool, size_t accum_elems
       ds.allocs.push_back(p[k]);
     }
     ds.sum = (float*)p[0]; ds.sumsq = (float*)p[1]; ds.out = (float*)p[2];
-    if (ds.h_out) cudaFreeHost(ds.h_out);
+    if (ds.h_out) cudaFreeHost(ds.h_out);   // the staging buffer is re-created on demand (pageable destinations only)
     ds.h_out = nullptr;
-    RT_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ds.h_out), 2 * accum_elems * sizeof(float)));
     ds.accum_elems = accum_elems;
   }
   return RT_OK;
@@ -1240,6 +1242,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   const size_t stack_bytes = (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t);
   uint64_t launches = 0;
   size_t timed = 0;
+  std::vector<char> has_fin(timing ? kMaxTimed : 0, 0);   // iteration k was followed by a (timed) k_finish launch
   uint32_t iter = 0;
   int cur = 0;
   // The loop is device driven: the last k_shade block prepares the next iteration, the host only launches batches
@@ -1278,6 +1281,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
         if (finish_flat) finish_flat<<<dev.sm_count * 8, kTraverseBlock, 0, stream>>>(ds.ctl, ds.q[cur], dev.d, A, dev.flat);
         else finish<<<dev.sm_count * 8, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, ds.q[cur], dev.d, A);
         launches++;
+        if (t_this) { cudaEventRecord(ds.events[(timed - 1) * 4 + 3], stream); has_fin[timed - 1] = 1; }
       }
     }
     RT_CUDA(cudaMemcpyAsync(ds.h_ctl, ds.ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, stream));
@@ -1295,6 +1299,8 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   if (stats) {
     stats->samples = total;
     stats->rays = ds.h_ctl->rays;
+    stats->rays_finish = ds.h_ctl->rays_finish;
+    stats->paths_finish = ds.h_ctl->paths_finish;
     stats->launches = launches;
     stats->iterations = ds.h_ctl->iterations;
     stats->pool = ds.pool;
@@ -1302,20 +1308,23 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
       float ms = 0;
       cudaEventElapsedTime(&ms, ev_begin, ev_end);
       stats->ms_total = ms;
-      double tt = 0, tsd = 0;
+      double tt = 0, tsd = 0, tfin = 0;
       for (size_t k = 0; k < timed; k++) {
-        float a = 0, b = 0;
+        float a = 0, b = 0, c = 0;
         cudaEventElapsedTime(&a, ds.events[k * 4 + 0], ds.events[k * 4 + 1]);
         cudaEventElapsedTime(&b, ds.events[k * 4 + 1], ds.events[k * 4 + 2]);
+        if (has_fin[k]) cudaEventElapsedTime(&c, ds.events[k * 4 + 2], ds.events[k * 4 + 3]);
         tt += a;
         tsd += b;
+        tfin += c;
       }
       // iterations beyond the timed window (very long renders) are extrapolated by iteration count
       double scale = timed ? (double)iter / (double)timed : 0.0;
       if (timed == kMaxTimed && iter > timed) { tt *= scale; tsd *= scale; }
       stats->ms_traverse = tt;
       stats->ms_shade = tsd;
-      stats->ms_raygen = std::max(0.0, (double)ms - tt - tsd);
+      stats->ms_finish = tfin;
+      stats->ms_raygen = std::max(0.0, (double)ms - tt - tsd - tfin);
     }
   }
   return RT_OK;
@@ -1334,7 +1343,7 @@ static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DC
     if (st != RT_OK) return st;
     total.samples += part.samples; total.rays += part.rays; total.launches += part.launches; total.iterations += part.iterations;
     total.pool = part.pool; total.ms_total += part.ms_total; total.ms_traverse += part.ms_traverse; total.ms_shade += part.ms_shade;
-    total.ms_raygen += part.ms_raygen;
+    total.ms_raygen += part.ms_raygen; total.ms_finish += part.ms_finish; total.rays_finish += part.rays_finish; total.paths_finish += part.paths_finish;
     first_sample += n;
     n_samples -= n;
   }
@@ -1483,6 +1492,7 @@ int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed
   // page-locked caller buffers (rt_host_alloc, …) are written by the copy engine directly; pageable ones go
   // device → pinned staging (full PCIe rate, asynchronous) → one host memcpy
   const bool direct = is_pinned_host(rgb_out, elems * sizeof(float)) && (!rgb_sumsq_out || is_pinned_host(rgb_sumsq_out, elems * sizeof(float)));
+  if (!direct && !ws.h_out) RT_CUDA(cudaMallocHost(reinterpret_cast<void**>(&ws.h_out), 2 * ws.accum_elems * sizeof(float)));
   float* h_rgb = direct ? rgb_out : ws.h_out;
   float* h_sq = direct ? rgb_sumsq_out : ws.h_out + ws.accum_elems;
   RT_CUDA(cudaMemcpyAsync(h_rgb, ws.out, elems * sizeof(float), cudaMemcpyDeviceToHost, stream));
