@@ -161,7 +161,11 @@ raytrace CameraSettings{..} world gen = unsafePerformIO $ do
       h = round (fromIntegral w / cs_aspectRatio) :: Int          -- round-half-even (Ray.hs:123)
       targets = [ RedirectTarget p (t3 q) (t3 a) (t3 b) | (p, q, a, b) <- cs_redirectTargets ]
       (seed, _) = genWord64 gen
-  buf <- mallocForeignPtrArray (w * h * 3) :: IO (ForeignPtr CFloat)
+  -- page-locked result buffer from the library's recycling pool: rt_render's copy engine writes it directly
+  -- (a pageable mallocForeignPtrArray works too, through one staging memcpy)
+  buf <- alloca $ \pp -> do
+    c_host_alloc (fromIntegral (w * h * 3 * sizeOf (0 :: CFloat))) pp >>= check
+    peek pp >>= newForeignPtr p_host_free . castPtr :: IO (ForeignPtr CFloat)
   withArrayLen targets $ \nt pt -> allocaBytes cameraSize $ \cam -> withForeignPtr buf $ \o -> do
     pokeCamera cam Camera
       { camCenter = t3 cs_center, camLookAt = t3 cs_lookAt, camUp = t3 cs_up, camVfov = cs_vfov, camAspect = cs_aspectRatio

@@ -148,6 +148,8 @@ foreign import ccall safe   "rt_scene_commit"           c_scene_commit   :: Ptr 
 foreign import ccall safe   "rt_scene_upload"           c_scene_upload   :: Ptr RtScene -> Int32 -> IO Int32
 foreign import ccall safe   "rt_render"                 c_render         :: Ptr RtScene -> Int32 -> Ptr () -> Word64 -> Word64 -> Word64
                                                                          -> Ptr CFloat -> Ptr CFloat -> Ptr () -> IO Int32
+foreign import ccall safe   "rt_host_alloc"             c_host_alloc     :: CSize -> Ptr (Ptr ()) -> IO Int32
+foreign import ccall safe   "&rt_host_free"             p_host_free      :: FunPtr (Ptr CFloat -> IO ())   -- ForeignPtr finaliser (status ignored)
 foreign import ccall safe   "rt_probe_primary"          c_probe_primary  :: Ptr RtScene -> Int32 -> Ptr () -> Double -> Ptr Word32 -> Ptr CFloat -> IO Int32
 foreign import ccall safe   "rt_probe_surface"          c_probe_surface  :: Ptr RtScene -> Int32 -> Ptr () -> Double -> Ptr CFloat -> IO Int32
 foreign import ccall safe   "rt_tonemap_u8"             c_tonemap_u8     :: Int32 -> Ptr CFloat -> Int32 -> Int32 -> Ptr Word8 -> IO Int32
