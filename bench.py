@@ -184,6 +184,7 @@ def main():
     import torch.distributed as dist
     from raytrace_b200 import scenes, mkStdGen
     from raytrace_b200.ray import CompiledScene, imageHeight
+    from raytrace_b200.multigpu import ImageReducer
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback; use --impl reference for the CPU arm)")
@@ -212,14 +213,24 @@ def main():
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def one_step(step_seed):
+    # sample-sharded runs: accumulators in symmetric memory, image reduce by the root's own NVLS / peer-load kernel
+    # (raytrace_b200.multigpu.ImageReducer -> rt_reduce_image); RT_B200_REDUCE=nccl selects dist.reduce instead
+    reducer = ImageReducer(H * W * 3, dev) if distributed else None
+    result = {"img": acc}
+
+    def one_step(step_seed, want_stats=True):
         """device-resident step: render this rank's sample range, reduce to rank 0, normalise."""
+        if distributed:
+            a = reducer.acc()
+            a.zero_()
+            st = cs.render_device(settings, mkStdGen(step_seed), first, count, a.data_ptr(), 0, stream.cuda_stream, want_stats=want_stats)
+            img = reducer.reduce(1.0 / spp)
+            if rank == 0:
+                result["img"] = img
+            return st
         acc.zero_()
         st = cs.render_device(settings, mkStdGen(step_seed), first, count, acc.data_ptr(), 0, stream.cuda_stream)
-        if distributed:
-            dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
-        if rank == 0:
-            acc.mul_(1.0 / spp)
+        acc.mul_(1.0 / spp)
         return st
 
     for k in range(args.warmup):
@@ -238,7 +249,9 @@ def main():
         if distributed:
             dist.barrier()
         e0.record(stream)
-        st = one_step(seed + k)
+        # sharded runs ask for no statistics inside the timed step: nothing is read back, and a share that fits the
+        # pool returns without a host synchronisation, so the reduce queues right behind the render
+        st = one_step(seed + k, want_stats=not distributed)
         e1.record(stream)
         e1.synchronize()
         step_ms.append(e0.elapsed_time(e1))
@@ -246,12 +259,15 @@ def main():
     barrier()
     t_wall = time.perf_counter() - t_wall0
     clocks = sampler.stop() if rank == 0 else None
+    if distributed:   # ray counts and per-kernel times of the same steps, from an instrumented (untimed) re-run
+        stats = [one_step(seed + k, want_stats=True) for k in range(args.steps)]
+        barrier()
 
     total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
     if distributed:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)      # max over ranks
     total_ms = float(total_ms.item())
-    lum = float(acc.mean().item()) if rank == 0 else 0.0
+    lum = float(result["img"].mean().item()) if rank == 0 else 0.0
 
     # ---- e2e: public API with HOST buffers; scene commit + upload + render + image read-back per step ----
     e2e_ms = []
@@ -265,12 +281,12 @@ def main():
         if not distributed:
             img = cs2.render(settings, mkStdGen(seed + 77 + k))   # rt_render: D2H of the normalised image inside
         else:
-            acc.zero_()
-            cs2.render_device(settings, mkStdGen(seed + 77 + k), first, count, acc.data_ptr(), 0, stream.cuda_stream)
-            dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
+            a = reducer.acc()
+            a.zero_()
+            cs2.render_device(settings, mkStdGen(seed + 77 + k), first, count, a.data_ptr(), 0, stream.cuda_stream, want_stats=False)
+            img = reducer.reduce(1.0 / spp)
             if rank == 0:
-                acc.mul_(1.0 / spp)
-                out_host.copy_(acc, non_blocking=True)
+                out_host.copy_(img, non_blocking=True)
             torch.cuda.synchronize(dev)
         dt = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
         if distributed:
@@ -280,20 +296,23 @@ def main():
         del cs2
 
     # ---- the collective alone (sample-sharded runs): one reduce(SUM) of the fp32 image to rank 0, device-timed ----
-    reduce_ms = None
+    reduce_ms = reduce_nccl_ms = None
     if distributed:
-        ts = []
-        for k in range(5):
-            dist.barrier()
-            r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            r0.record(stream)
-            dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
-            r1.record(stream)
-            r1.synchronize()
-            ts.append(r0.elapsed_time(r1))
-        t = torch.tensor([statistics.median(ts)], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        reduce_ms = float(t.item())
+        def timed(fn):
+            ts = []
+            for k in range(7):
+                dist.barrier()
+                r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                r0.record(stream)
+                fn()
+                r1.record(stream)
+                r1.synchronize()
+                ts.append(r0.elapsed_time(r1))
+            t = torch.tensor([statistics.median(ts[2:])], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        reduce_ms = timed(lambda: reducer.reduce(1.0 / spp))                       # barrier + rt_reduce_image (or dist.reduce)
+        reduce_nccl_ms = timed(lambda: dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM))  # the ncclReduce it replaces
 
     if rank != 0:
         if distributed:
@@ -411,7 +430,8 @@ def main():
         "mrays_per_s": rays / (total_ms * 1e-3) / 1e6 * (world_size if distributed else 1),
         "rays_per_sample": rays / (count * W * H * args.steps),
         "kernel_ms_per_step": {"traverse": trav_ms / args.steps, "shade": shade_ms / args.steps, "finish": fin_ms / args.steps,
-                               "iterations": iters / args.steps, "reduce": reduce_ms},
+                               "iterations": iters / args.steps, "reduce": reduce_ms, "reduce_nccl": reduce_nccl_ms,
+                               "reduce_mode": (reducer.mode + (" (" + reducer.why + ")" if reducer.why else "")) if reducer else None},
         "gpu_launches": int(launches),
         "e2e": {"value": e2e_val, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": W * H * 3 * 4,
                 "ms_per_step": statistics.median(e2e_ms)},

@@ -226,6 +226,9 @@ int32_t rt_render(RtScene* scene, int32_t device, const RtCamera* cam, uint64_t 
  * Same, accumulating UN-normalised sums into DEVICE buffers owned by the caller (e.g. a torch
  * tensor), on the caller's stream; used by the one-process-per-GPU sample-sharded path where
  * an NCCL reduce follows.  d_sum / d_sumsq must be zero-initialised by the caller.
+ * Completion is ordered on the stream: operations the caller queues on it afterwards see the finished sums.  With
+ * stats == NULL nothing is read back, and when the launch sequence is known up front (flat scene whose sample range fits
+ * the path pool - one GPU's share of a small render) the call returns without synchronising the host.
  */
 int32_t rt_render_device(RtScene* scene, int32_t device, const RtCamera* cam, uint64_t seed,
                          uint64_t first_sample, uint64_t n_samples, float* d_sum,
@@ -241,6 +244,18 @@ int32_t rt_probe_primary(RtScene* scene, int32_t device, const RtCamera* cam, do
  * (Texture.hs:15: tex point uv; zero for pitchBlack / dielectric) and the material kind; zeros on a miss or a medium.
  * HOST buffer H*W*10. */
 int32_t rt_probe_surface(RtScene* scene, int32_t device, const RtCamera* cam, double time, float* out);
+
+/* The one collective of the sample-sharded path (one reduce of the fp32 image to the root), done over NVLink
+ * peer memory by the root's own kernel instead of ncclReduce.  Every rank keeps its un-normalised sum buffer in symmetric
+ * memory (mapped by all peers; torch.distributed._symmetric_memory or cuMem + cuMulticast in a C host); after a barrier
+ * across ranks the ROOT calls this on its stream:
+ *   multicast_ptr != NULL: one pass of multimem.ld_reduce over the NVSwitch multicast mapping - the switch sums the G
+ *                          buffers in the fabric (NVLS) and the root ingests the image once;
+ *   else:                  the root sums peer_ptrs[0 .. n_peers) (its own buffer included) with peer loads.
+ * d_out[k] = scale * sum_r buffer_r[k] (scale = 1/spp, Ray.hs:232), d_out a root-local device buffer that is NOT one
+ * of the summed buffers.  n_floats must be a multiple of 4 and all pointers 16-byte aligned (pad the image). */
+int32_t rt_reduce_image(int32_t device, const void* multicast_ptr, const void* const* peer_ptrs, int32_t n_peers,
+                        float* d_out, uint64_t n_floats, float scale, void* cuda_stream);
 
 /* Optional page-locked host buffers for rt_render's outputs.  rt_render accepts ANY host pointer; when rgb_out (and
  * rgb_sumsq_out) point into page-locked memory - from rt_host_alloc, cudaMallocHost or cudaHostRegister - the image is

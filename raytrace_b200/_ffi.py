@@ -103,7 +103,7 @@ EXPORTS = [
     "rt_scene_add_node", "rt_scene_set_noise_tables", "rt_scene_commit", "rt_scene_info", "rt_scene_get_eval_order",
     "rt_scene_get_bvh", "rt_scene_upload", "rt_image_height", "rt_render", "rt_render_device",
     "rt_probe_primary", "rt_probe_surface", "rt_set_pool_size", "rt_tonemap_u8",
-    "rt_obj_parse", "rt_mesh_sizes", "rt_mesh_data", "rt_mesh_destroy", "rt_host_alloc", "rt_host_free",
+    "rt_obj_parse", "rt_mesh_sizes", "rt_mesh_data", "rt_mesh_destroy", "rt_host_alloc", "rt_host_free", "rt_reduce_image",
 ]
 
 _lib: Optional[C.CDLL] = None
@@ -154,6 +154,7 @@ def lib() -> C.CDLL:
     L.rt_mesh_destroy.argtypes = [vp]
     L.rt_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
     L.rt_host_free.argtypes = [vp]
+    L.rt_reduce_image.argtypes = [C.c_int32, vp, C.POINTER(vp), C.c_int32, vp, C.c_uint64, C.c_float, vp]
     for name in EXPORTS:
         fn = getattr(L, name)
         if name not in ("rt_version", "rt_last_error"):

@@ -692,7 +692,15 @@ static TraceFlatFn pick_trace_flat(uint32_t features) {
   }
 }
 
-__global__ void k_begin(Ctl* ctl) { prepare_iteration(ctl, true); }
+// Initialises the control block ON the device (no host-to-device copy whose pinned source a later, still queued render
+// of the same workspace could overwrite) and prepares iteration 0.
+__global__ void k_begin(Ctl* ctl, unsigned long long total_items, unsigned int pool) {
+  Ctl c{};
+  c.total_items = total_items;
+  c.pool = pool;
+  *ctl = c;
+  prepare_iteration(ctl, true);
+}
 
 // ---- tail kernel ------------------------------------------------------------------------------------------------
 // Once every camera path has been started and only a few long paths survive (depth up to 50: dozens of nearly empty
@@ -859,6 +867,37 @@ __global__ void k_tonemap(const float* __restrict__ rgb, int n, int mode, uint8_
   }
 }
 
+// ---- image reduction over NVLink peer memory (sample-sharded renders) -------------------------------------
+// Every rank's un-normalised sum buffer lives in symmetric memory.  With NVSwitch multicast the root reads the image ONCE
+// through the multicast address: multimem.ld_reduce makes the switch fetch the element from every GPU and add them in the
+// fabric (NVLS), so the root ingests W*H*3 floats instead of (G-1) times that, and the 1/spp normalisation (Ray.hs:232)
+// is fused into the same pass.  Without multicast the root sums the peers' buffers with plain peer loads.
+__device__ __forceinline__ float4 multimem_sum4(const float4* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__global__ void __launch_bounds__(256) k_reduce_multimem(const float4* mc, float4* __restrict__ out, size_t n4, float scale) {
+  for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n4; k += (size_t)gridDim.x * blockDim.x) {
+    const float4 v = multimem_sum4(mc + k);
+    out[k] = make_float4(v.x * scale, v.y * scale, v.z * scale, v.w * scale);
+  }
+}
+constexpr int kMaxPeers = 16;
+struct PeerPtrs { const float4* p[kMaxPeers]; };
+__global__ void __launch_bounds__(256) k_reduce_peers(const __grid_constant__ PeerPtrs peers, int n_peers, float4* __restrict__ out, size_t n4, float scale) {
+  for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n4; k += (size_t)gridDim.x * blockDim.x) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+    for (int r = 0; r < n_peers; r++) {
+      const float4 v = __ldcv(peers.p[r] + k);     // volatile-cached load: peer memory written by another GPU
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    out[k] = make_float4(a.x * scale, a.y * scale, a.z * scale, a.w * scale);
+  }
+}
+
 __global__ void k_scale(const float* __restrict__ in, float* __restrict__ out, int n, float s) {
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) out[k] = in[k] * s;
 }
@@ -893,6 +932,8 @@ struct Workspace {
   std::vector<void*> allocs;
   std::vector<cudaEvent_t> events;
   cudaStream_t stream = nullptr;
+  cudaEvent_t last_done = nullptr;   // recorded when a render returned with work still queued (single-shot renders)
+  bool pending = false;              // ... the next user of the workspace orders its stream behind it
 };
 
 static std::mutex g_ws_mutex;
@@ -904,6 +945,7 @@ static void destroy_workspace(Workspace* w) {
   for (auto e : w->events) cudaEventDestroy(e);
   if (w->h_ctl) cudaFreeHost(w->h_ctl);
   if (w->h_out) cudaFreeHost(w->h_out);
+  if (w->last_done) cudaEventDestroy(w->last_done);
   if (w->stream) cudaStreamDestroy(w->stream);
   delete w;
 }
@@ -918,6 +960,7 @@ static int32_t acquire_workspace(int device, Workspace** out) {
   w->device = device;
   cudaError_t e = cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&w->h_ctl), sizeof(Ctl));
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&w->last_done, cudaEventDisableTiming);
   if (e != cudaSuccess) {
     set_error(std::string("workspace creation failed: ") + cudaGetErrorString(e));
     destroy_workspace(w);
@@ -1212,12 +1255,6 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   if (const char* e = std::getenv("RT_B200_TAIL_BATCH")) tail_batch = std::min(64, std::max(1, std::atoi(e)));
   if (const char* e = std::getenv("RT_B200_NODE_BURST")) A.node_burst = std::min(8, std::max(1, std::atoi(e)));
   if (const char* e = std::getenv("RT_B200_REFILL")) A.refill = std::min(32, std::max(1, std::atoi(e)));
-  Ctl init{};
-  init.total_items = total;
-  init.pool = ds.pool;
-  *ds.h_ctl = init;
-  RT_CUDA(cudaMemcpyAsync(ds.ctl, ds.h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, stream));
-
   const bool timing = stats != nullptr && std::getenv("RT_B200_NOTIMING") == nullptr;
   const size_t kMaxTimed = 4096;            // iterations with per-kernel events
   if (timing && ds.events.size() < kMaxTimed * 4 + 2) {
@@ -1248,14 +1285,18 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   // The loop is device driven: the last k_shade block prepares the next iteration, the host only launches batches
   // and reads the 80-byte control block back between them.  Batch length follows the measured consumption of work
   // items (iterations past the end are empty launches, so the estimate stays a little short).
-  k_begin<<<1, 1, 0, stream>>>(ds.ctl);
+  k_begin<<<1, 1, 0, stream>>>(ds.ctl, total, ds.pool);
   launches++;
   unsigned long long batch = 4, prev_started = 0;
   // tail mode: every camera path has started (known up front when the whole range fits the pool, e.g. one GPU's share
   // of a small render).  From then on k_finish is checked after EVERY iteration - a ~2 us no-op until few enough paths
   // are left - so the takeover never waits for a host round trip, and launches queued past it are empty.
   bool tail = total <= ds.pool;
-  if (tail && A.finish_max) batch = (unsigned long long)tail_batch;
+  // flat scenes, unbounded tail kernel: once every path has started, ONE more iteration + k_finish_flat completes the
+  // render, so the launch sequence is known without reading the control block back
+  const bool finish_all = finish_flat != nullptr && A.finish_max == 0xFFFFFFFFu;
+  if (tail && A.finish_max) batch = finish_all ? 1ull : (unsigned long long)tail_batch;
+  const bool single_shot = tail && finish_all;   // the whole sample range fits the pool: k_begin, one iteration, tail
   for (;;) {
     for (unsigned long long b = 0; b < batch; b++) {
       Queue& q = ds.q[cur];
@@ -1284,6 +1325,14 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
         if (t_this) { cudaEventRecord(ds.events[(timed - 1) * 4 + 3], stream); has_fin[timed - 1] = 1; }
       }
     }
+    if (single_shot && !stats) {
+      // nothing to read back: return with the work queued (stream-ordered completion, like any device-buffer API);
+      // whoever borrows this workspace next orders its stream behind last_done
+      RT_CUDA(cudaEventRecord(ds.last_done, stream));
+      ds.pending = true;
+      RT_CUDA(cudaGetLastError());
+      return RT_OK;
+    }
     RT_CUDA(cudaMemcpyAsync(ds.h_ctl, ds.ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, stream));
     RT_CUDA(cudaStreamSynchronize(stream));
     if (ds.h_ctl->n_live == 0) break;
@@ -1291,7 +1340,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
     const double per_iter = (double)(started - prev_started) / (double)batch;
     prev_started = started;
     if (left > 0 && per_iter >= 1.0) batch = (unsigned long long)std::min(4096.0, std::max(4.0, 0.9 * (double)left / per_iter));
-    else { tail = true; batch = A.finish_max ? (unsigned long long)tail_batch : 8; }
+    else { tail = true; batch = finish_all ? 1ull : (A.finish_max ? (unsigned long long)tail_batch : 8); }
     if (iter > 100000000u) { set_error("wavefront loop did not terminate"); return RT_ERR_CUDA; }
   }
   if (timing) { RT_CUDA(cudaEventRecord(ev_end, stream)); RT_CUDA(cudaEventSynchronize(ev_end)); }
@@ -1394,6 +1443,7 @@ int32_t rt_render_device(RtScene* sp, int32_t device, const RtCamera* rc, uint64
   st = ensure_workspace(*lease.w, choose_pool(s, total), 0);
   if (st != RT_OK) return st;
   cudaStream_t stream = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : lease.w->stream;
+  if (lease.w->pending) { RT_CUDA(cudaStreamWaitEvent(stream, lease.w->last_done, 0)); lease.w->pending = false; }
   return run_wavefront(s, *ds, *lease.w, cam, seed, first_sample, n_samples, d_sum, d_sumsq, stream, stats);
 }
 
@@ -1478,6 +1528,7 @@ int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed
   st = ensure_workspace(ws, choose_pool(s, std::max<unsigned long long>(total, 1)), elems);
   if (st != RT_OK) return st;
   cudaStream_t stream = ws.stream;
+  if (ws.pending) { RT_CUDA(cudaStreamWaitEvent(stream, ws.last_done, 0)); ws.pending = false; }
   RT_CUDA(cudaMemsetAsync(ws.sum, 0, elems * sizeof(float), stream));
   if (rgb_sumsq_out) RT_CUDA(cudaMemsetAsync(ws.sumsq, 0, elems * sizeof(float), stream));
   if (n_samples) {
@@ -1564,6 +1615,37 @@ int32_t rt_probe_surface(RtScene* sp, int32_t device, const RtCamera* rc, double
   if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
   cudaFree(d_out);
   RT_CUDA(e);
+  return RT_OK;
+}
+
+int32_t rt_reduce_image(int32_t device, const void* multicast_ptr, const void* const* peer_ptrs, int32_t n_peers,
+                        float* d_out, uint64_t n_floats, float scale, void* cuda_stream) {
+  if (!d_out || (!multicast_ptr && (!peer_ptrs || n_peers <= 0))) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  if (n_peers > kMaxPeers) { set_error("rt_reduce_image: at most 16 peers"); return RT_ERR_INVALID_ARG; }
+  if (n_floats % 4 != 0 || (reinterpret_cast<uintptr_t>(d_out) & 15u) || (reinterpret_cast<uintptr_t>(multicast_ptr) & 15u)) {
+    set_error("rt_reduce_image: buffers must be 16-byte aligned and hold a multiple of 4 floats (pad the image)");
+    return RT_ERR_INVALID_ARG;
+  }
+  int32_t st = check_device(device);
+  if (st != RT_OK) return st;
+  RT_CUDA(cudaSetDevice(device));
+  if (n_floats == 0) return RT_OK;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(cuda_stream);
+  const size_t n4 = n_floats / 4;
+  int sm = 0;
+  cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, device);
+  const int grid = (int)std::min<size_t>((n4 + 255) / 256, (size_t)sm * 8);
+  if (multicast_ptr) {
+    k_reduce_multimem<<<grid, 256, 0, stream>>>(static_cast<const float4*>(multicast_ptr), reinterpret_cast<float4*>(d_out), n4, scale);
+  } else {
+    PeerPtrs pp{};
+    for (int r = 0; r < n_peers; r++) {
+      if (!peer_ptrs[r] || (reinterpret_cast<uintptr_t>(peer_ptrs[r]) & 15u)) { set_error("rt_reduce_image: bad peer pointer"); return RT_ERR_INVALID_ARG; }
+      pp.p[r] = static_cast<const float4*>(peer_ptrs[r]);
+    }
+    k_reduce_peers<<<grid, 256, 0, stream>>>(pp, n_peers, reinterpret_cast<float4*>(d_out), n4, scale);
+  }
+  RT_CUDA(cudaGetLastError());
   return RT_OK;
 }
 

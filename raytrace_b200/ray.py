@@ -214,16 +214,19 @@ class CompiledScene:
         return res[0] if len(res) == 1 else tuple(res)
 
     def render_device(self, settings: CameraSettings, seed: StdGen, first_sample: int, n_samples: int,
-                      d_sum_ptr: int, d_sumsq_ptr: int = 0, stream_ptr: int = 0):
-        """Accumulate un-normalised sums into caller-owned DEVICE buffers (torch tensors)."""
+                      d_sum_ptr: int, d_sumsq_ptr: int = 0, stream_ptr: int = 0, want_stats: bool = True):
+        """Accumulate un-normalised sums into caller-owned DEVICE buffers (torch tensors).  Completion is ordered on
+        the stream.  With ``want_stats=False`` nothing is read back, and a render whose launch sequence is known up
+        front (flat scene, sample range within the pool: one GPU's share of a small render) returns without a host
+        synchronisation, so the caller's next stream operation (the reduce) queues behind it with no idle gap."""
         L = _ffi.lib()
         cam = self.camera(settings)
-        stats = _ffi.RtStats()
+        stats = _ffi.RtStats() if want_stats else None
         _ffi.check(L.rt_render_device(self.handle.handle, self.device, C.byref(cam), C.c_uint64(seed.seed),
                                       C.c_uint64(first_sample), C.c_uint64(n_samples),
                                       C.c_void_p(d_sum_ptr), C.c_void_p(d_sumsq_ptr or None),
-                                      C.c_void_p(stream_ptr or None), C.byref(stats)))
-        return stats.as_dict()
+                                      C.c_void_p(stream_ptr or None), C.byref(stats) if want_stats else None))
+        return stats.as_dict() if want_stats else None
 
     def probe_primary(self, settings: CameraSettings, time: float = 0.5):
         L = _ffi.lib()

@@ -71,3 +71,36 @@ def test_reduce_image_without_group_just_normalises():
     a = torch.full((12,), 6.0)
     reduce_image(a, 3)
     assert torch.allclose(a, torch.full((12,), 2.0))
+
+
+def _reducer_worker(rank, world, port, spp, n_px, out_dir):
+    from raytrace_b200.multigpu import ImageReducer
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    red = ImageReducer(n_px * 3, "cpu")               # no CUDA: the reducer must pick the dist.reduce path
+    assert red.mode == "nccl" and red.handles is None
+    for step in range(3):                             # reused across images like bench.py does
+        acc = red.acc()
+        acc.zero_()
+        first, count = split_samples(spp, world, rank)
+        _fake_range(n_px)(first + step, count, acc[: n_px * 3])
+        img = red.reduce(1.0 / spp)
+        assert (img is None) == (rank != 0)
+        if rank == 0:
+            np.save(os.path.join(out_dir, f"img{step}.npy"), img.numpy().copy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_image_reducer_gloo_world_size_2(tmp_path):
+    """ImageReducer without CUDA / symmetric memory: dist.reduce + scale, image padded to a multiple of 4 floats
+    (n_px * 3 = 771 is not one) and the padding never leaks into the result."""
+    n_px, world, spp = 257, 2, 10
+    mp.spawn(_reducer_worker, args=(world, _free_port(), spp, n_px, str(tmp_path)), nprocs=world, join=True)
+    for step in range(3):
+        single = torch.zeros(n_px * 3, dtype=torch.float32)
+        _fake_range(n_px)(step, spp, single)
+        got = np.load(tmp_path / f"img{step}.npy")
+        assert got.shape == (n_px * 3,)
+        assert np.allclose(got, single.numpy() / spp, rtol=1e-5, atol=1e-6)
