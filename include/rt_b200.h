@@ -226,6 +226,7 @@ int32_t rt_render(RtScene* scene, int32_t device, const RtCamera* cam, uint64_t 
  * Same, accumulating UN-normalised sums into DEVICE buffers owned by the caller (e.g. a torch
  * tensor), on the caller's stream; used by the one-process-per-GPU sample-sharded path where
  * an NCCL reduce follows.  d_sum / d_sumsq must be zero-initialised by the caller.
+ * cuda_stream is a cudaStream_t (NULL = the default stream).
  * Completion is ordered on the stream: operations the caller queues on it afterwards see the finished sums.  With
  * stats == NULL nothing is read back, and when the launch sequence is known up front (flat scene whose sample range fits
  * the path pool - one GPU's share of a small render) the call returns without synchronising the host.

@@ -1442,7 +1442,8 @@ int32_t rt_render_device(RtScene* sp, int32_t device, const RtCamera* rc, uint64
   if (st != RT_OK) return st;
   st = ensure_workspace(*lease.w, choose_pool(s, total), 0);
   if (st != RT_OK) return st;
-  cudaStream_t stream = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : lease.w->stream;
+  // the caller's stream, NULL = the default stream (CUDA convention): what the caller queues next is ordered behind the render
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(cuda_stream);
   if (lease.w->pending) { RT_CUDA(cudaStreamWaitEvent(stream, lease.w->last_done, 0)); lease.w->pending = false; }
   return run_wavefront(s, *ds, *lease.w, cam, seed, first_sample, n_samples, d_sum, d_sumsq, stream, stats);
 }

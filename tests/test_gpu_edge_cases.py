@@ -269,3 +269,32 @@ def test_page_locked_output_buffers(built, monkeypatch):
     assert L.rt_host_alloc(7654000, C.byref(q)) == 0 and q.value == p.value      # ... and are handed out again
     assert L.rt_host_free(q) == 0
     assert L.rt_host_free(q) == 1      # double free / foreign pointer: RT_ERR_INVALID_ARG, nothing is touched
+
+
+@pytest.mark.parametrize("name,kw", [("cornell", dict(width=64, spp=16)), ("demo1", dict(width=64, spp=8))], ids=["flat", "bvh"])
+def test_render_device_is_stream_ordered(built, name, kw):
+    """rt_render_device accumulates into a caller-owned device buffer on the caller's stream (NULL = default stream).
+    Without statistics a flat-scene render returns before the GPU has finished (single-shot launch sequence), so
+    whatever the caller queues next on that stream - here the scale and the copy - must still see the finished sums;
+    back-to-back renders reuse one workspace and must not disturb each other."""
+    import torch
+    ctor, seed = scenes.CONFIGS[name]
+    s, w = ctor(**kw)
+    cs = CompiledScene(w)
+    want = cs.render(s, rt.mkStdGen(seed)).astype(np.float64)
+    spp = s.cs_samplesPerPixel
+    dev = torch.device("cuda", 0)
+    n = want.size
+    side = torch.cuda.Stream(dev)
+    for stream in (torch.cuda.current_stream(dev), side):
+        with torch.cuda.stream(stream):
+            accs = [torch.zeros(n, dtype=torch.float32, device=dev) for _ in range(3)]
+            for a in accs:                                   # three renders queued back to back, nothing read back
+                assert cs.render_device(s, rt.mkStdGen(seed), 0, spp, a.data_ptr(), 0, stream.cuda_stream, want_stats=False) is None
+            imgs = [(a * (1.0 / spp)).cpu().numpy() for a in accs]
+        for img in imgs:
+            assert np.allclose(img.reshape(want.shape), want, rtol=2e-4, atol=2e-5)
+    a = torch.zeros(n, dtype=torch.float32, device=dev)
+    st = cs.render_device(s, rt.mkStdGen(seed), 0, spp, a.data_ptr(), 0, 0)           # with statistics: synchronous
+    assert st["samples"] == want.shape[0] * want.shape[1] * spp and st["rays"] >= st["samples"]
+    assert np.allclose((a / spp).cpu().numpy().reshape(want.shape), want, rtol=2e-4, atol=2e-5)
