@@ -923,7 +923,8 @@ struct Workspace {
   Queue q[2]{};
   float2* hits = nullptr;
   Ctl* ctl = nullptr;
-  Ctl* h_ctl = nullptr;   // pinned
+  Ctl* h_ctl = nullptr;   // pinned, two snapshot slots
+  cudaEvent_t snap_ev[2] = {nullptr, nullptr};
   float* sum = nullptr;
   float* sumsq = nullptr;
   float* out = nullptr;
@@ -946,6 +947,7 @@ static void destroy_workspace(Workspace* w) {
   if (w->h_ctl) cudaFreeHost(w->h_ctl);
   if (w->h_out) cudaFreeHost(w->h_out);
   if (w->last_done) cudaEventDestroy(w->last_done);
+  for (cudaEvent_t ev : w->snap_ev) if (ev) cudaEventDestroy(ev);
   if (w->stream) cudaStreamDestroy(w->stream);
   delete w;
 }
@@ -959,7 +961,8 @@ static int32_t acquire_workspace(int device, Workspace** out) {
   auto* w = new Workspace();
   w->device = device;
   cudaError_t e = cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking);
-  if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&w->h_ctl), sizeof(Ctl));
+  if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&w->h_ctl), 2 * sizeof(Ctl));
+  for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaEventCreateWithFlags(&w->snap_ev[k], cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&w->last_done, cudaEventDisableTiming);
   if (e != cudaSuccess) {
     set_error(std::string("workspace creation failed: ") + cudaGetErrorString(e));
@@ -1287,7 +1290,6 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   // items (iterations past the end are empty launches, so the estimate stays a little short).
   k_begin<<<1, 1, 0, stream>>>(ds.ctl, total, ds.pool);
   launches++;
-  unsigned long long batch = 4, prev_started = 0;
   // tail mode: every camera path has started (known up front when the whole range fits the pool, e.g. one GPU's share
   // of a small render).  From then on k_finish is checked after EVERY iteration - a ~2 us no-op until few enough paths
   // are left - so the takeover never waits for a host round trip, and launches queued past it are empty.
@@ -1295,63 +1297,100 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   // flat scenes, unbounded tail kernel: once every path has started, ONE more iteration + k_finish_flat completes the
   // render, so the launch sequence is known without reading the control block back
   const bool finish_all = finish_flat != nullptr && A.finish_max == 0xFFFFFFFFu;
-  if (tail && A.finish_max) batch = finish_all ? 1ull : (unsigned long long)tail_batch;
   const bool single_shot = tail && finish_all;   // the whole sample range fits the pool: k_begin, one iteration, tail
+  const unsigned long long tail_chunk = finish_all ? 1ull : (A.finish_max ? (unsigned long long)tail_batch : 8ull);
+
+  auto launch_iteration = [&](bool fin_check) {
+    Queue& q = ds.q[cur];
+    Queue& qn = ds.q[cur ^ 1];
+    const bool t_this = timing && timed < kMaxTimed;
+    if (fused) {   // one launch per iteration; reported as shade time (ms_traverse = ms_raygen = 0)
+      if (t_this) { cudaEventRecord(ds.events[timed * 4 + 0], stream); cudaEventRecord(ds.events[timed * 4 + 1], stream); }
+      fused<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A, dev.flat);
+      launches += 1;
+    } else {
+      k_raygen<<<g_gen, kRaygenBlock, 0, stream>>>(ds.ctl, q, A);
+      if (t_this) cudaEventRecord(ds.events[timed * 4 + 0], stream);
+      if (flat) flat<<<dev.sm_count * 8, kFlatBlock, 0, stream>>>(ds.ctl, q, dev.d, dev.flat, ds.hits);
+      else traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, dev.d, A);
+      if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
+      k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
+      launches += 3;
+    }
+    if (t_this) { cudaEventRecord(ds.events[timed * 4 + 2], stream); timed++; }
+    cur ^= 1;
+    iter++;
+    if (A.finish_max && fin_check) {   // device-side decision: no-op until the work items are exhausted and few paths are left
+      if (finish_flat) finish_flat<<<dev.sm_count * 8, kTraverseBlock, 0, stream>>>(ds.ctl, ds.q[cur], dev.d, A, dev.flat);
+      else finish<<<dev.sm_count * 8, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, ds.q[cur], dev.d, A);
+      launches++;
+      if (t_this) { cudaEventRecord(ds.events[(timed - 1) * 4 + 3], stream); has_fin[timed - 1] = 1; }
+    }
+  };
+  // A chunk = some iterations, then a snapshot of the control block into one of two pinned slots + an event; the host
+  // waits for the snapshot, plans the next chunk from the measured consumption of work items (iterations past the end
+  // are empty launches, so the estimate stays a little short) and launches it.  RT_B200_PIPELINE=1 keeps one more chunk
+  // queued behind the one waited for, so the GPU never idles during a read-back; measured (profiles/r01h_sweep_tail.txt):
+  // no gain - the ~5 round trips of a render cost less than the staler plans (one more iteration before the tail kernel
+  // takes over, one chunk of empty launches at the end): Cornell 10.3 -> 10.4 ms, pawn 35.4 -> 35.7.  Off.
+  struct Flight { int slot; unsigned long long iters; };
+  int slot = 0;
+  auto launch_chunk = [&](unsigned long long n) -> Flight {
+    for (unsigned long long b2 = 0; b2 < n; b2++) launch_iteration(tail || b2 + 1 == n);
+    cudaMemcpyAsync(&ds.h_ctl[slot], ds.ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, stream);
+    cudaEventRecord(ds.snap_ev[slot], stream);
+    Flight f{slot, (unsigned long long)iter};
+    slot ^= 1;
+    return f;
+  };
+  bool pipeline = false;
+  if (const char* e = std::getenv("RT_B200_PIPELINE")) pipeline = std::atoi(e) != 0;
+  unsigned long long chunk_next = tail ? tail_chunk : 2ull;
+  unsigned long long prev_started = 0, prev_iters = 0;
+  Flight cur_f = launch_chunk(tail ? tail_chunk : (pipeline ? 2ull : 4ull));
+  if (single_shot && !stats) {
+    // nothing to read back: return with the work queued (stream-ordered completion, like any device-buffer API);
+    // whoever borrows this workspace next orders its stream behind last_done
+    RT_CUDA(cudaEventRecord(ds.last_done, stream));
+    ds.pending = true;
+    RT_CUDA(cudaGetLastError());
+    return RT_OK;
+  }
+  const Ctl* final_ctl = nullptr;
   for (;;) {
-    for (unsigned long long b = 0; b < batch; b++) {
-      Queue& q = ds.q[cur];
-      Queue& qn = ds.q[cur ^ 1];
-      const bool t_this = timing && timed < kMaxTimed;
-      if (fused) {   // one launch per iteration; reported as shade time (ms_traverse = ms_raygen = 0)
-        if (t_this) { cudaEventRecord(ds.events[timed * 4 + 0], stream); cudaEventRecord(ds.events[timed * 4 + 1], stream); }
-        fused<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A, dev.flat);
-        launches += 1;
-      } else {
-        k_raygen<<<g_gen, kRaygenBlock, 0, stream>>>(ds.ctl, q, A);
-        if (t_this) cudaEventRecord(ds.events[timed * 4 + 0], stream);
-        if (flat) flat<<<dev.sm_count * 8, kFlatBlock, 0, stream>>>(ds.ctl, q, dev.d, dev.flat, ds.hits);
-        else traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, dev.d, A);
-        if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
-        k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
-        launches += 3;
-      }
-      if (t_this) { cudaEventRecord(ds.events[timed * 4 + 2], stream); timed++; }
-      cur ^= 1;
-      iter++;
-      if (A.finish_max && (tail || b + 1 == batch)) {   // device-side decision: no-op until the work items are exhausted and few paths are left
-        if (finish_flat) finish_flat<<<dev.sm_count * 8, kTraverseBlock, 0, stream>>>(ds.ctl, ds.q[cur], dev.d, A, dev.flat);
-        else finish<<<dev.sm_count * 8, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, ds.q[cur], dev.d, A);
-        launches++;
-        if (t_this) { cudaEventRecord(ds.events[(timed - 1) * 4 + 3], stream); has_fin[timed - 1] = 1; }
-      }
+    Flight next_f{};
+    const bool have_next = pipeline;
+    if (have_next) next_f = launch_chunk(chunk_next);
+    RT_CUDA(cudaEventSynchronize(ds.snap_ev[cur_f.slot]));
+    const Ctl& c = ds.h_ctl[cur_f.slot];
+    if (c.n_live == 0) {   // the render was complete at this snapshot; what was queued behind it is empty
+      if (have_next) { RT_CUDA(cudaEventSynchronize(ds.snap_ev[next_f.slot])); final_ctl = &ds.h_ctl[next_f.slot]; }
+      else final_ctl = &c;
+      break;
     }
-    if (single_shot && !stats) {
-      // nothing to read back: return with the work queued (stream-ordered completion, like any device-buffer API);
-      // whoever borrows this workspace next orders its stream behind last_done
-      RT_CUDA(cudaEventRecord(ds.last_done, stream));
-      ds.pending = true;
-      RT_CUDA(cudaGetLastError());
-      return RT_OK;
-    }
-    RT_CUDA(cudaMemcpyAsync(ds.h_ctl, ds.ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, stream));
-    RT_CUDA(cudaStreamSynchronize(stream));
-    if (ds.h_ctl->n_live == 0) break;
-    const unsigned long long started = ds.h_ctl->next_item, left = total - started;
-    const double per_iter = (double)(started - prev_started) / (double)batch;
+    const unsigned long long started = c.next_item;
+    const double per_iter = cur_f.iters > prev_iters ? (double)(started - prev_started) / (double)(cur_f.iters - prev_iters) : 0.0;
     prev_started = started;
-    if (left > 0 && per_iter >= 1.0) batch = (unsigned long long)std::min(4096.0, std::max(4.0, 0.9 * (double)left / per_iter));
-    else { tail = true; batch = finish_all ? 1ull : (A.finish_max ? (unsigned long long)tail_batch : 8); }
+    prev_iters = cur_f.iters;
+    const double inflight = have_next ? (double)(next_f.iters - cur_f.iters) : 0.0;
+    if (started >= total) { tail = true; chunk_next = tail_chunk; }
+    else if (per_iter >= 1.0) {
+      const double est_left = std::max(0.0, (double)(total - started) - per_iter * inflight);
+      chunk_next = (unsigned long long)std::min(4096.0, std::max(2.0, (pipeline ? 0.45 : 0.9) * est_left / per_iter));
+    } else chunk_next = 2;
+    if (!have_next) next_f = launch_chunk(chunk_next);
+    cur_f = next_f;
     if (iter > 100000000u) { set_error("wavefront loop did not terminate"); return RT_ERR_CUDA; }
   }
   if (timing) { RT_CUDA(cudaEventRecord(ev_end, stream)); RT_CUDA(cudaEventSynchronize(ev_end)); }
   RT_CUDA(cudaGetLastError());
   if (stats) {
     stats->samples = total;
-    stats->rays = ds.h_ctl->rays;
-    stats->rays_finish = ds.h_ctl->rays_finish;
-    stats->paths_finish = ds.h_ctl->paths_finish;
+    stats->rays = final_ctl->rays;
+    stats->rays_finish = final_ctl->rays_finish;
+    stats->paths_finish = final_ctl->paths_finish;
     stats->launches = launches;
-    stats->iterations = ds.h_ctl->iterations;
+    stats->iterations = final_ctl->iterations;
     stats->pool = ds.pool;
     if (timing) {
       float ms = 0;
