@@ -72,15 +72,13 @@ def flops_per_ray(n_node, n_sph, n_pl):
 # DRAM bytes per k_traverse launch from the committed `ncu --set full` captures (profiles/, per workload; None = not captured)
 NCU_TRAFFIC = {
     # (workload, kernel): DRAM bytes PER RAY = (dram__bytes_read.sum + dram__bytes_write.sum) / rays of the captured launch
-    # (ncu --set full, full 4 Mi-path launches; profiles/r01c_ncu_full_summary.txt).  The bench line reports
-    # traffic = this x the measured mean rays per launch of the run, so it stays "per launch like achieved".
-    ("cornell", "k_shade"): 400.5e6 / 4194304, ("cornell", "k_traverse"): 153.6e6 / 4194304,
-    ("pawn", "k_shade"): 415.8e6 / 4194304,
-    # k_traverse_p on the SAH tree, full 16 Mi-ray launch (profiles/r01g_ncu_full_summary_pawn.txt): 633.9 MB + 106.8 MB
-    ("pawn", "k_traverse"): (633.9e6 + 106.8e6) / 16777216,
-    # fused flat-scene kernel (raygen + closest hit + shading + compaction in one launch), full 16 Mi-path launch,
-    # profiles/r01f_ncu_full_summary.txt: 660.0 MB read + 608.6 MB written
-    ("cornell", "k_trace_flat"): (660.0e6 + 608.6e6) / 16777216,
+    # (ncu --set full, full 16 Mi-path launches; profiles/r01h_kernel_table.md, r01h_ncu_full_summary.txt).  The bench line
+    # reports traffic = this x the measured mean rays per launch of the run, so it stays "per launch like achieved".
+    ("pawn", "k_shade"): (1146.6e6 + 342.0e6) / 16777216, ("pawn", "k_traverse"): (633.9e6 + 106.5e6) / 16777216,
+    ("demo1", "k_shade"): (1114.9e6 + 547.8e6) / 16777216, ("demo1", "k_traverse"): (536.9e6 + 107.9e6) / 16777216,
+    ("demo2", "k_shade"): (1131.2e6 + 590.7e6) / 16777216, ("demo2", "k_traverse"): (940.2e6 + 112.2e6) / 16777216,
+    # fused flat-scene kernel (raygen + closest hit + shading + compaction in one launch): 660.9 MB read + 609.6 MB written
+    ("cornell", "k_trace_flat"): (660.9e6 + 609.6e6) / 16777216,
 }
 
 
