@@ -175,6 +175,9 @@ typedef struct RtSceneInfo {
   uint32_t surface_root;
   uint32_t max_depth;         /* deepest root→leaf path in the device tree */
   uint64_t device_bytes;      /* scene bytes resident in HBM */
+  uint32_t n_closed_media;    /* media whose boundary is a shared, closed, outward-oriented surface (interior queries
+                               * are then bounded by the free-flight distance) */
+  uint32_t reserved;
 } RtSceneInfo;
 
 typedef struct RtScene RtScene;

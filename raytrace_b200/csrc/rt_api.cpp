@@ -270,6 +270,9 @@ int32_t rt_scene_info(const RtScene* sp, RtSceneInfo* info) {
   info->surface_root = f.surface_root;
   info->max_depth = f.max_depth;
   info->device_bytes = f.bytes();
+  info->n_closed_media = 0;
+  for (uint32_t k = 0; k < f.n_media; k++) info->n_closed_media += f.media[k].closed ? 1u : 0u;
+  info->reserved = 0;
   return RT_OK;
 }
 

@@ -89,6 +89,11 @@ struct DMedium {    // constantMedium, Geometry.hs:298-330
   // surface tree (e.g. `dielectric <$ mesh` + `constantMedium rho mesh`): the surface closest hit then answers the first
   // boundary query (closest over a subset = closest over the set when it lies in the subset).  shared = 0 otherwise.
   uint32_t geom_lo, geom_hi, shared;
+  // shared boundary that is a CLOSED, outward-oriented surface (a watertight triangle mesh: every directed edge once and
+  // its reverse once, positive volume; or one sphere): from a point inside, every ray leaves through a back face, so a
+  // path that has just scattered in this medium is known to be inside it (rt_trace.cuh::starts_inside_only_medium).
+  // The Stanford bunny has holes -> 0; the pawn is watertight -> 1.
+  uint32_t closed;
 };
 
 struct DTarget {    // RedirectTarget, Ray.hs:112-118 (+ its parallelogram record for the pdf probe)

@@ -17,6 +17,7 @@
 //   * primitives are numbered in the reference's evaluation order so that "lower index wins an
 //     exact tie" equals the reference's tie rules (earlier child / left child wins).
 #include <algorithm>
+#include <array>
 #include <chrono>
 #include <cstdio>
 #include <cmath>
@@ -105,6 +106,8 @@ struct HPrim {            // one primitive instance (double precision, final spa
   BoxD box;               // world-space box (swept over the shutter for moving instances)
   uint32_t ref_index = kNone;   // position in the reference's evaluation order (decides exact ties)
   uint32_t index = kNone;       // device (storage) index: leaf order of the device tree
+  D3 corner[3];           // triangles: the three vertices as given (local space) - watertightness test of medium boundaries
+  bool has_corners = false;
   D3 box_c, box_e[3];     // PRIM_FLAG_BOXHEAD: centre and unit axes of the aggregated cuboid (same space as c / n)
   double box_h[3] = {0, 0, 0};   // ... and its half extents
 };
@@ -292,6 +295,7 @@ struct Builder {
     if (xf.moving) { p.c = q; p.n = n; p.wa = wa; p.wb = wb; }
     else { p.c = xf.fwd.pt(q, 0); p.n = xf.fwd.lin(n); p.wa = xf.fwd.lin(wa); p.wb = xf.fwd.lin(wb); }
     if (uv) std::memcpy(p.uv, uv, sizeof p.uv);
+    if (corners && tri) { p.corner[0] = corners[0]; p.corner[1] = corners[1]; p.corner[2] = corners[2]; p.has_corners = true; }
     finish_prim(p, xf, node, sub, material, hull);
     return leaf_for(std::move(p), ref);
   }
@@ -775,6 +779,51 @@ struct Builder {
     return median_build(std::move(hs));  // GROUP → BVH (results identical to the linear scan)
   }
 
+  void collect_prims(int r, std::vector<uint32_t>& out) const {
+    const RNode& n = rnodes[r];
+    if (n.kind == RNode::LEAF) { out.push_back(n.prim); return; }
+    for (int c : n.children) collect_prims(c, out);
+  }
+  // Is the boundary under RNode r a closed, outward-oriented surface?  Conservative: true only for one static sphere of
+  // positive radius, or a set of static triangles under ONE transform in which every directed edge (keyed by the exact
+  // vertex coordinates, so duplicated obj vertices still match) occurs once and its reverse once, with positive volume.
+  bool boundary_is_closed(int r) const {
+    std::vector<uint32_t> ps;
+    collect_prims(r, ps);
+    if (ps.empty()) return false;
+    if (ps.size() == 1) {
+      const HPrim& p = prims[ps[0]];
+      return p.type == PRIM_SPHERE && p.r > 0 && !(p.flags & PRIM_FLAG_MOVING);
+    }
+    std::map<std::array<double, 3>, uint32_t> vid;
+    std::map<std::pair<uint32_t, uint32_t>, int> edges;
+    double vol6 = 0;
+    const uint32_t xf0 = prims[ps[0]].xform;
+    for (uint32_t pi : ps) {
+      const HPrim& p = prims[pi];
+      if (p.type != PRIM_TRI || !p.has_corners || p.xform != xf0 || (p.flags & PRIM_FLAG_MOVING)) return false;
+      uint32_t id[3];
+      for (int k = 0; k < 3; k++) {
+        const std::array<double, 3> key{p.corner[k].x, p.corner[k].y, p.corner[k].z};
+        auto it = vid.find(key);
+        if (it == vid.end()) it = vid.emplace(key, (uint32_t)vid.size()).first;
+        id[k] = it->second;
+      }
+      if (id[0] == id[1] || id[1] == id[2] || id[0] == id[2]) return false;   // degenerate triangle
+      for (int k = 0; k < 3; k++) edges[{id[k], id[(k + 1) % 3]}]++;
+      vol6 += dot(p.corner[0], cross(p.corner[1], p.corner[2]));
+    }
+    for (const auto& e : edges) {
+      if (e.second != 1) return false;
+      auto rev = edges.find({e.first.second, e.first.first});
+      if (rev == edges.end() || rev->second != 1) return false;
+    }
+    // orientation in WORLD space: a reflecting instance transform (det < 0) turns the surface inside out
+    const double* M = xforms[xf0].fwd.M;
+    const double det = M[0] * (M[4] * M[8] - M[5] * M[7]) - M[1] * (M[3] * M[8] - M[5] * M[6]) + M[2] * (M[3] * M[7] - M[4] * M[6]);
+    return std::isfinite(vol6) && std::isfinite(det) && vol6 * det > 0;
+  }
+
   void collect_geoms(int r, std::vector<uint32_t>& out) const {
     const RNode& n = rnodes[r];
     if (n.kind == RNode::LEAF) { out.push_back(prims[n.prim].geom); return; }
@@ -979,7 +1028,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
       dm.neg_inv_density = (float)(-(1.0 / b.media[i].density));
       dm.root = b.emit_ref(fs, h, 0, max_depth);
       dm.material = b.media[i].material;
-      dm.geom_lo = dm.geom_hi = dm.shared = 0;
+      dm.geom_lo = dm.geom_hi = dm.shared = dm.closed = 0;
       // shared-boundary shortcut: dense geometry-id range, every id also present in the surface tree
       std::vector<uint32_t> g;
       b.collect_geoms(b.media[i].rtree, g);
@@ -988,6 +1037,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
       if (!g.empty() && g.back() - g.front() + 1 == g.size() && std::getenv("RT_B200_NO_SHARED") == nullptr &&
           std::includes(surf_geoms.begin(), surf_geoms.end(), g.begin(), g.end())) {
         dm.geom_lo = g.front(); dm.geom_hi = g.back(); dm.shared = 1;
+        if (std::getenv("RT_B200_NO_INTERIOR_BOUND") == nullptr && b.boundary_is_closed(b.media[i].rtree)) dm.closed = 1;
       }
     }
     fs.n_media = (uint32_t)b.media.size();

@@ -290,7 +290,22 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
         for (;;) {
           if (have_h) {
             float s1 = 0.f, s2 = -1.f;   // free-flight segment (s1, s2); empty when s2 < s1
-            if (m == 0) { best = h; }
+            if (m == 0) {
+              if (tmin == 0.f && h.prim != kNone && !(h.t > tmin0)) {
+                // bounded interior query (fetch, below) met the boundary within tmin of the scatter point: the reference
+                // skips that crossing (open interval (1e-4, inf)) and sees the ray as already outside - redo the segment
+                // as an ordinary one (once per ~1e4 interior segments)
+                origin_geom = kNone;
+                tmin = tmin0;
+                h = Hit{inf, kNone, false};
+                cur = sc.surface_root;
+                break;
+              }
+              tmin = tmin0;
+              best = h;
+              // the bounded query found nothing before the free-flight distance: the scatter event
+              if (h.prim == kNone && h.t < inf) { best.prim = kMediumBase; best.front = true; m = sc.n_media; }
+            }
             else if (pass == 0) {
               if (h.prim != kNone) {
                 if (!h.front) { s1 = tmin0; s2 = fminf(best.t, h.t); }           // we are inside (Geometry.hs:313)
@@ -380,6 +395,16 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
             skip_b = kNone;
             h = Hit{inf, kNone, false};
             m = 0;
+            if constexpr (kMedia) {
+              // interior segment of a subsurface-scattering mesh: the free-flight distance bounds the surface query
+              // (rt_trace.cuh::starts_inside_only_medium)
+              if (starts_inside_only_medium(sc, origin_geom)) {
+                const uint32_t pixel = __float_as_uint(__ldcs(q.thr + i).w);
+                const uint2 meta = __ldcs(q.meta + i);
+                h.t = free_flight_bound(sc, tmin0, A.key, pixel, (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x, meta.y);
+                if (h.t < inf) tmin = 0.f;   // the scatter point lies on no surface: look at (0, bound] so that a boundary crossing inside (0, tmin0] is noticed
+              }
+            }
           }
         }
       }

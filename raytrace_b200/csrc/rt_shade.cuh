@@ -27,7 +27,7 @@ __device__ __forceinline__ Surf reconstruct(const DScene& sc, const RayT& ray, c
     s.sphere_uv = false;
     s.uvn = mk3(0.f, 0.f, 0.f);
     s.material = sc.media[hit.prim - kMediumBase].material;
-    s.geom = kNone;
+    s.geom = hit.prim;   // kMediumBase + k: the next segment starts at a scatter point INSIDE medium k (no surface geometry has such an id)
     s.prim = kNone;
     s.tf = 0;
     return s;

@@ -373,6 +373,22 @@ __device__ __forceinline__ void closest_hit(const DScene& sc, uint32_t root, con
   }
 }
 
+// A segment that starts at a scatter point of the scene's ONLY medium, whose boundary is part of the surfaces
+// (`dielectric <$ mesh` + `constantMedium rho mesh`: subsurface scattering) and a closed surface (DMedium::closed: the
+// first boundary hit from an interior point is then always a back face), is inside that medium from tmin on, so the
+// reference's outcome (Geometry.hs:313-327) is: the closest surface hit if it comes before tmin + d, else a scatter event
+// at tmin + d, with d = -ln(rand)/density drawn from the counter RNG - the same number whether it is drawn before or
+// after the traversal.  Drawing it first turns the unbounded surface query of an interior ray (which crosses the whole
+// mesh to find where it would leave) into one bounded by the free-flight distance: a mean free path of 0.2 in a pawn four
+// units tall culls nearly every node.  Returns the bound (inf: not applicable / rand = 0).
+__device__ __forceinline__ bool starts_inside_only_medium(const DScene& sc, uint32_t origin_geom) {
+  return origin_geom == kMediumBase && sc.n_media == 1u && sc.media[0].closed != 0u;   // closed implies shared
+}
+__device__ __forceinline__ float free_flight_bound(const DScene& sc, float tmin, uint2 key, uint32_t pixel, uint64_t sample, uint32_t bounce) {
+  const uint4 rnd = rng4(key, pixel, sample, bounce, RNG_MEDIA);
+  return tmin + sc.media[0].neg_inv_density * logf(u01(rnd.x));   // rand = 0 -> +inf -> unbounded, no scatter (as in the reference)
+}
+
 // ---- full closest-hit query of a path segment: surfaces, then every medium (Geometry.hs:298-330) ---
 template <uint32_t F>
 __device__ __forceinline__ Hit trace_segment(const DScene& sc, const RayT& ray, uint32_t origin_geom, bool with_media,
@@ -381,8 +397,22 @@ __device__ __forceinline__ Hit trace_segment(const DScene& sc, const RayT& ray, 
   const float tmin = 1e-4f;  // Ray.hs:178
   const float inf = __int_as_float(0x7f800000);
   Hit best{inf, kNone, false};
-  closest_hit<F>(sc, sc.surface_root, ray, tmin, origin_geom, kNone, stack, stride, best);
   if constexpr ((F & TF_MEDIA) != 0) {
+    if (with_media && starts_inside_only_medium(sc, origin_geom)) best.t = free_flight_bound(sc, tmin, key, pixel, sample, bounce);
+  }
+  // the bounded query looks at (0, bound]: a scatter point lies on no surface, and a boundary crossing inside (0, tmin] -
+  // which the reference's open interval skips, so that it sees the ray as already outside - must be noticed
+  closest_hit<F>(sc, sc.surface_root, ray, best.t < inf ? 0.f : tmin, origin_geom, kNone, stack, stride, best);
+  if constexpr ((F & TF_MEDIA) != 0) {
+    if (best.prim == kNone && best.t < inf) {   // nothing before the free-flight distance: the scatter event
+      best.prim = kMediumBase;
+      best.front = true;
+      return best;
+    }
+    if (best.prim != kNone && !(best.t > tmin)) {   // crossing within tmin: an ordinary segment after all (~1e-4 of them)
+      best = Hit{inf, kNone, false};
+      closest_hit<F>(sc, sc.surface_root, ray, tmin, origin_geom, kNone, stack, stride, best);
+    }
     if (with_media) {
       uint4 rnd = make_uint4(0, 0, 0, 0);
       for (uint32_t m = 0; m < sc.n_media; m++) {

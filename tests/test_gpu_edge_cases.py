@@ -298,3 +298,35 @@ def test_render_device_is_stream_ordered(built, name, kw):
     st = cs.render_device(s, rt.mkStdGen(seed), 0, spp, a.data_ptr(), 0, 0)           # with statistics: synchronous
     assert st["samples"] == want.shape[0] * want.shape[1] * spp and st["rays"] >= st["samples"]
     assert np.allclose((a / spp).cpu().numpy().reshape(want.shape), want, rtol=2e-4, atol=2e-5)
+
+
+def test_interior_queries_bounded_by_free_flight_distance(built, monkeypatch):
+    """A path that has just scattered inside the scene's only medium, whose boundary is a closed surface shared with the
+    surfaces (pawn; a glass ball filled with fog), draws its free-flight distance BEFORE the traversal and bounds the
+    surface query with it.  The counter RNG hands out the same number either way, so the event sequence - and the image
+    at equal seeds - is that of the unbounded queries (RT_B200_NO_INTERIOR_BOUND=1 at commit), up to summation order."""
+    from raytrace_b200 import V3, constantTexture, dielectric, isotropic, group, pureGeometry, constantMedium, sphere, lambertian
+    ball = sphere((0, 0, -3), 1.5)
+    fog_ball = group([pureGeometry(dielectric(1.5) << ball), isotropic(constantTexture(V3(0.9, 0.6, 0.3))) << constantMedium(3.0, ball),
+                      pureGeometry(lambertian(constantTexture(V3(0.5, 0.5, 0.5))) << sphere((0, -101.5, -3), 100))])
+    s_ball = rt.defaultCameraSettings.replace(cs_imageWidth=72, cs_samplesPerPixel=32, cs_maxRecursionDepth=30, cs_background=scenes.sky)
+    s_pawn, w_pawn = scenes.pawn(width=56, spp=24)
+    for s, w, seed in ((s_ball, fog_ball, 7), (s_pawn, w_pawn, 55)):
+        cs = CompiledScene(w)
+        assert cs.info()["n_closed_media"] == 1
+        monkeypatch.setenv("RT_B200_NO_INTERIOR_BOUND", "1")
+        cs_ref = CompiledScene(w)
+        monkeypatch.delenv("RT_B200_NO_INTERIOR_BOUND")
+        assert cs_ref.info()["n_closed_media"] == 0
+        a, st_a = cs.render(s, rt.mkStdGen(seed), want_stats=True)
+        b, st_b = cs_ref.render(s, rt.mkStdGen(seed), want_stats=True)
+        # identical event sequences: same ray count (a knife-edge tie may flip a handful of paths), same image
+        assert abs(int(st_a["rays"]) - int(st_b["rays"])) <= 1e-4 * st_b["rays"]
+        close = np.isclose(a, b, rtol=2e-4, atol=2e-5).all(axis=2)
+        assert close.mean() >= 0.999, close.mean()
+        assert abs(a.mean() - b.mean()) <= 1e-3 * b.mean()
+    # the tail kernel (trace_segment) takes the same shortcut
+    monkeypatch.setenv("RT_B200_FINISH", "4294967295")
+    c = CompiledScene(w_pawn).render(s_pawn, rt.mkStdGen(55))
+    monkeypatch.delenv("RT_B200_FINISH")
+    assert np.isclose(c, a, rtol=2e-4, atol=2e-5).all(axis=2).mean() >= 0.999

@@ -281,3 +281,32 @@ def test_sah_builder_pathological_inputs(built, case):
             assert not seen[first:first + c].any()
             seen[first:first + c] = True
     assert seen.all()
+
+
+def _volume(mesh_geom, density=5.0):
+    from raytrace_b200 import V3, constantTexture, dielectric, isotropic, group, pureGeometry, constantMedium
+    return group([pureGeometry(dielectric(1.5) << mesh_geom),
+                  isotropic(constantTexture(V3(1, 0, 0))) << constantMedium(density, mesh_geom)])
+
+
+def test_closed_boundary_detection(built):
+    """Interior queries are bounded by the free-flight distance only when the medium's boundary is part of the surfaces
+    AND provably closed and outward oriented (DMedium::closed): every directed edge once, its reverse once, positive
+    volume in world space - or one sphere.  Anything else keeps the reference's unbounded boundary queries."""
+    from raytrace_b200 import Mesh, triangleMesh, sphere, transform, scale, rotateY
+    closed = lambda g: CompiledScene(_volume(g), upload=False).info()["n_closed_media"]   # noqa: E731
+    assert CompiledScene(scenes.pawn(width=8, spp=1)[1], upload=False).info()["n_closed_media"] == 1      # watertight
+    assert CompiledScene(scenes.bunny_volume(width=8, spp=1)[1], upload=False).info()["n_closed_media"] == 0  # holes
+    v = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1]], dtype=np.float64)
+    tet = [(0, 2, 1), (0, 1, 3), (0, 3, 2), (1, 2, 3)]                  # outward-oriented tetrahedron
+    faces = lambda tris: np.array([[a, -1, b, -1, c, -1] for a, b, c in tris], dtype=np.int32)   # noqa: E731
+    assert closed(triangleMesh(Mesh(v, np.zeros((0, 2)), faces(tet)))) == 1
+    assert closed(triangleMesh(Mesh(v, np.zeros((0, 2)), faces(tet[:3])))) == 0                       # one face missing
+    assert closed(triangleMesh(Mesh(v, np.zeros((0, 2)), faces([(a, c, b) for a, b, c in tet])))) == 0  # inside out
+    assert closed(triangleMesh(Mesh(v, np.zeros((0, 2)), faces(tet[:3] + [(1, 3, 2)])))) == 0          # one face flipped
+    dup = np.vstack([v, v[1:2]])                                        # an obj-style duplicated vertex still matches
+    assert closed(triangleMesh(Mesh(dup, np.zeros((0, 2)), faces([(0, 2, 4), (0, 1, 3), (0, 3, 2), (1, 2, 3)])))) == 1
+    assert closed(transform(rotateY(0.3), triangleMesh(Mesh(v, np.zeros((0, 2)), faces(tet))))) == 1  # rotated instance
+    assert closed(sphere((0, 0, 0), 1.0)) == 1
+    assert closed(sphere((0, 0, 0), -1.0)) == 0                         # the hollow-sphere trick: normals point inwards
+    assert CompiledScene(scenes.demo2(width=8, spp=1)[1], upload=False).info()["n_media"] == 2        # two media: hint unused
