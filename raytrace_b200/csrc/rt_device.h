@@ -132,6 +132,11 @@ struct DScene {     // device pointers of one uploaded scene
   uint32_t surface_root;       // node reference or kNone
   uint32_t has_noise;
   uint32_t n_prims;
+  // conservative world-space box of everything a ray can meet (all surface primitives and medium boundaries, swept over
+  // the shutter, rounded outward); has_world_box = 0 when it is not finite.  Camera rays that miss it end on the
+  // background inside k_raygen and never enter the queue (rt_kernels.cu::k_raygen).
+  float world_lo[3], world_hi[3];
+  uint32_t has_world_box;
 };
 
 }  // namespace rtb

@@ -1042,6 +1042,19 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
     }
     fs.n_media = (uint32_t)b.media.size();
     fs.max_depth = max_depth;
+    {   // world box: every primitive instance (surface or medium boundary), padded like the node boxes
+      BoxD wb;
+      for (const HPrim& p : b.prims) wb.join(p.box);
+      bool finite = !b.prims.empty();
+      for (int k = 0; k < 3; k++) finite = finite && std::isfinite(wb.lo[k]) && std::isfinite(wb.hi[k]) && wb.lo[k] <= wb.hi[k];
+      if (finite && std::getenv("RT_B200_NO_PRIMARY_CULL") == nullptr) {
+        double mx = 0;
+        for (int k = 0; k < 3; k++) mx = std::max(mx, std::max(std::fabs(wb.lo[k]), std::fabs(wb.hi[k])));
+        const double pad = 1e-5 * mx + 1e-6;
+        for (int k = 0; k < 3; k++) { fs.world_lo[k] = Builder::round_down(wb.lo[k] - pad); fs.world_hi[k] = Builder::round_up(wb.hi[k] + pad); }
+        fs.has_world_box = 1;
+      }
+    }
     if (max_depth + 1 > (uint32_t)kStackDepth)
       b.fail(RT_ERR_UNSUPPORTED, "flattened BVH is deeper than the shared-memory traversal stack (32 levels)");
     lap("media trees to device");

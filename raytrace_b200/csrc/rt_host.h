@@ -53,6 +53,8 @@ struct FlatScene {
   uint32_t n_spheres = 0, n_planars = 0;
   uint32_t max_depth = 0;
   uint32_t features = 0;       // TF_* bits: selects the kernel specialisation
+  float world_lo[3] = {0, 0, 0}, world_hi[3] = {0, 0, 0};   // box of all primitives (outward rounded)
+  uint32_t has_world_box = 0;
   uint64_t bytes() const;
 };
 

@@ -56,6 +56,8 @@ struct Ctl {                      // device-resident control block of one render
   unsigned int trav_next;         // next queue slot the persistent traversal warps fetch
   unsigned int blocks_done;       // k_shade blocks finished (the last one prepares the next iteration)
   unsigned int paths_finish;      // paths the tail kernel took over
+  unsigned int n_gen, gen_done;   // k_raygen with primary-ray culling: camera paths queued so far / blocks finished
+  unsigned int culled;            // ... camera rays of this iteration that missed the world box (ended on the background)
   unsigned long long rays_finish; // segments traced by the tail kernel (also counted in rays)
 };
 
@@ -79,6 +81,8 @@ struct RenderArgs {
   uint32_t finish_max;            // k_finish takes over when at most this many paths are left (0 = never)
   int finish_refill;              // k_finish: idle lanes per warp that trigger a claim of new paths
   uint32_t tile;                  // camera paths start in 8x4 pixel tiles (1) or in row-major pixel order (0)
+  uint32_t cull;                  // k_raygen: camera rays that miss the world box end there (never queued)
+  float world_lo[3], world_hi[3];
 };
 
 // Closes iteration k and prepares iteration k+1 (single thread: the last k_shade block, or k_begin for k = 0).
@@ -150,16 +154,95 @@ __device__ __forceinline__ NewPath new_camera_path(const RenderArgs& A, unsigned
   return NewPath{camera_ray(A.cam, pixel, u01(r0.x), lu, lv, u01(r0.y), u01(r0.z)), pixel, (uint32_t)sample};
 }
 
-__global__ void __launch_bounds__(kRaygenBlock) k_raygen(const Ctl* __restrict__ ctl, Queue q, const __grid_constant__ RenderArgs A) {
+// Camera rays of the refilled queue tail.  With A.cull (the scene has a finite world box) a camera ray that misses the box
+// cannot hit anything: its path ends on the background right here (Ray.hs:179: miss -> cs_background) and is never
+// queued - no 56-byte record, no traversal fetch, no hit record, no shading pass for the large part of the frame an
+// object in front of a backdrop leaves empty (pawn, bunny: ~80 % of the camera rays).  Survivors are compacted into
+// [fill_lo, fill_lo + n_gen) (warp ballot ranks, one atomic per 256-item tile); the last block publishes n_live.
+__global__ void __launch_bounds__(kRaygenBlock) k_raygen(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ RenderArgs A) {
   const uint32_t lo = ctl->fill_lo, n = ctl->n_live;
   const unsigned long long item0 = ctl->fill_item0;
-  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; lo + t < n; t += gridDim.x * blockDim.x) {
-    const NewPath np = new_camera_path(A, item0 + t);
-    const uint32_t slot = lo + t;
-    q.o[slot] = make_float4(np.ray.o.x, np.ray.o.y, np.ray.o.z, np.ray.time);
-    q.d[slot] = make_float4(np.ray.d.x, np.ray.d.y, np.ray.d.z, __uint_as_float(kNone));
-    q.thr[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(np.pixel));
-    q.meta[slot] = make_uint2(np.sample_lo, 0u);
+  if (!A.cull) {
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; lo + t < n; t += gridDim.x * blockDim.x) {
+      const NewPath np = new_camera_path(A, item0 + t);
+      const uint32_t slot = lo + t;
+      q.o[slot] = make_float4(np.ray.o.x, np.ray.o.y, np.ray.o.z, np.ray.time);
+      q.d[slot] = make_float4(np.ray.d.x, np.ray.d.y, np.ray.d.z, __uint_as_float(kNone));
+      q.thr[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(np.pixel));
+      q.meta[slot] = make_uint2(np.sample_lo, 0u);
+    }
+    return;
+  }
+  __shared__ uint32_t s_cnt[kRaygenBlock / 32];
+  __shared__ uint32_t s_base;
+  // nothing to generate: n_live == fill_lo, or k_finish has just ended the render (n_live = 0 with a stale fill_lo)
+  const uint32_t fill = n > lo ? n - lo : 0u, lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const float4 wlo = make_float4(A.world_lo[0], A.world_lo[1], A.world_lo[2], 0.f), whi = make_float4(A.world_hi[0], A.world_hi[1], A.world_hi[2], 0.f);
+  unsigned int culled = 0;
+  for (uint32_t base = blockIdx.x * blockDim.x; base < fill; base += gridDim.x * blockDim.x) {   // uniform per block
+    const uint32_t t = base + threadIdx.x;
+    bool keep = false;
+    NewPath np{};
+    if (t < fill) {
+      np = new_camera_path(A, item0 + t);
+      f3 inv;
+      inv.x = fabsf(np.ray.d.x) > 1e-30f ? __frcp_rn(np.ray.d.x) : copysignf(1e30f, np.ray.d.x);
+      inv.y = fabsf(np.ray.d.y) > 1e-30f ? __frcp_rn(np.ray.d.y) : copysignf(1e30f, np.ray.d.y);
+      inv.z = fabsf(np.ray.d.z) > 1e-30f ? __frcp_rn(np.ray.d.z) : copysignf(1e30f, np.ray.d.z);
+      float tn;
+      keep = box_hit(wlo, whi, inv, np.ray.o * inv, 1e-4f, __int_as_float(0x7f800000), tn);
+      if (!keep) {   // miss: emitted = background, path ends (throughput is still 1)
+        const f3 c = background(A.cam, np.ray.d);
+        culled++;
+        if (c.x != 0.f || c.y != 0.f || c.z != 0.f) {
+          float* s = A.sum + 3 * (size_t)np.pixel;
+          atomicAdd(s, c.x);
+          atomicAdd(s + 1, c.y);
+          atomicAdd(s + 2, c.z);
+          if (A.sumsq) {
+            float* s2 = A.sumsq + 3 * (size_t)np.pixel;
+            atomicAdd(s2, c.x * c.x);
+            atomicAdd(s2 + 1, c.y * c.y);
+            atomicAdd(s2 + 2, c.z * c.z);
+          }
+        }
+      }
+    }
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
+    if (lane == 0) s_cnt[warp] = __popc(mask);
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kRaygenBlock / 32; w++) {
+      const uint32_t c = s_cnt[w];
+      before += (w < (int)warp) ? c : 0u;
+      total += c;
+    }
+    if (threadIdx.x == 0 && total) s_base = atomicAdd(&ctl->n_gen, total);
+    __syncthreads();
+    if (keep) {
+      const uint32_t slot = lo + s_base + before + __popc(mask & ((1u << lane) - 1u));
+      q.o[slot] = make_float4(np.ray.o.x, np.ray.o.y, np.ray.o.z, np.ray.time);
+      q.d[slot] = make_float4(np.ray.d.x, np.ray.d.y, np.ray.d.z, __uint_as_float(kNone));
+      q.thr[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(np.pixel));
+      q.meta[slot] = make_uint2(np.sample_lo, 0u);
+    }
+    __syncthreads();   // s_cnt / s_base are reused by the next tile
+  }
+  for (int o = 16; o > 0; o >>= 1) culled += __shfl_down_sync(0xFFFFFFFFu, culled, o);
+  if (lane == 0 && culled) atomicAdd(&ctl->culled, culled);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&ctl->gen_done, 1u) == gridDim.x - 1) {   // last block: publish what this iteration really holds
+      __threadfence();
+      volatile Ctl* c = ctl;
+      c->gen_done = 0;
+      if (fill) c->n_live = lo + c->n_gen;
+      c->n_gen = 0;
+      c->rays += c->culled;          // a culled camera ray is a path segment like any other (Ray.hs:178)
+      c->culled = 0;
+    }
   }
 }
 
@@ -1114,6 +1197,8 @@ static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
   d.n_media = f.n_media;
   d.surface_root = f.surface_root;
   d.has_noise = f.has_noise;
+  for (int k = 0; k < 3; k++) { d.world_lo[k] = f.world_lo[k]; d.world_hi[k] = f.world_hi[k]; }
+  d.has_world_box = f.has_world_box;
   d.n_prims = (uint32_t)f.canonical.size();
   s.devices[device] = ds;
   *out = ds;
@@ -1279,6 +1364,20 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   if (const char* e = std::getenv("RT_B200_FINISH_REFILL")) A.finish_refill = std::min(32, std::max(1, std::atoi(e)));
   A.tile = dev.has_flat ? 0u : 1u;   // coherence only matters to the BVH kernels; the flat scan is the same for every ray
   if (const char* e = std::getenv("RT_B200_TILE")) A.tile = std::atoi(e) ? 1u : 0u;
+  // Camera rays that miss the world box end inside k_raygen.  Worth the test (and the compaction it brings) only when the
+  // lens lies OUTSIDE the box - from inside it every ray passes (demo1 / demo2: +1 ms for nothing).  Flat scenes: the fused
+  // kernel generates its own camera rays.
+  A.cull = 0u;
+  if (dev.d.has_world_box && !dev.has_flat) {
+    float lens = 0.f;
+    if (cam.has_defocus)
+      lens = std::max(std::sqrt(cam.defocus_u[0] * cam.defocus_u[0] + cam.defocus_u[1] * cam.defocus_u[1] + cam.defocus_u[2] * cam.defocus_u[2]),
+                      std::sqrt(cam.defocus_v[0] * cam.defocus_v[0] + cam.defocus_v[1] * cam.defocus_v[1] + cam.defocus_v[2] * cam.defocus_v[2]));
+    for (int k = 0; k < 3; k++)
+      if (cam.center[k] + lens < dev.d.world_lo[k] || cam.center[k] - lens > dev.d.world_hi[k]) A.cull = 1u;
+  }
+  if (const char* e = std::getenv("RT_B200_PRIMARY_CULL")) A.cull = (std::atoi(e) && dev.d.has_world_box) ? 1u : 0u;
+  for (int k = 0; k < 3; k++) { A.world_lo[k] = dev.d.world_lo[k]; A.world_hi[k] = dev.d.world_hi[k]; }
   int tail_batch = 3;                // iterations (each followed by a k_finish check) per host round trip once all paths have started
   if (const char* e = std::getenv("RT_B200_TAIL_BATCH")) tail_batch = std::min(64, std::max(1, std::atoi(e)));
   if (const char* e = std::getenv("RT_B200_NODE_BURST")) A.node_burst = std::min(8, std::max(1, std::atoi(e)));
@@ -1325,6 +1424,13 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   const bool single_shot = tail && finish_all;   // the whole sample range fits the pool: k_begin, one iteration, tail
   const unsigned long long tail_chunk = finish_all ? 1ull : (A.finish_max ? (unsigned long long)tail_batch : 8ull);
 
+  // RT_B200_DEBUG_SYNC=1: synchronise after every launch and name the kernel that faulted (stderr)
+  const bool debug_sync = std::getenv("RT_B200_DEBUG_SYNC") != nullptr;
+  auto dbg = [&](const char* what) {
+    if (!debug_sync) return;
+    cudaError_t e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) std::fprintf(stderr, "[rt_b200] %s (iteration %u): %s\n", what, iter, cudaGetErrorString(e));
+  };
   auto launch_iteration = [&](bool fin_check) {
     Queue& q = ds.q[cur];
     Queue& qn = ds.q[cur ^ 1];
@@ -1335,11 +1441,14 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
       launches += 1;
     } else {
       k_raygen<<<g_gen, kRaygenBlock, 0, stream>>>(ds.ctl, q, A);
+      dbg("k_raygen");
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 0], stream);
       if (flat) flat<<<dev.sm_count * 8, kFlatBlock, 0, stream>>>(ds.ctl, q, dev.d, dev.flat, ds.hits);
       else traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, dev.d, A);
+      dbg("traverse");
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
       k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
+      dbg("k_shade");
       launches += 3;
     }
     if (t_this) { cudaEventRecord(ds.events[timed * 4 + 2], stream); timed++; }
@@ -1349,6 +1458,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
       if (finish_flat) finish_flat<<<dev.sm_count * 8, kTraverseBlock, 0, stream>>>(ds.ctl, ds.q[cur], dev.d, A, dev.flat);
       else finish<<<dev.sm_count * 8, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, ds.q[cur], dev.d, A);
       launches++;
+      dbg("k_finish");
       if (t_this) { cudaEventRecord(ds.events[(timed - 1) * 4 + 3], stream); has_fin[timed - 1] = 1; }
     }
   };

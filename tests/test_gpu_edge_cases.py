@@ -232,10 +232,13 @@ def test_tail_kernel_and_tiled_start_order_do_not_change_the_samples(built, name
     ctor, seed = scenes.CONFIGS[name]
     s, w = ctor(**kw)
     cs = CompiledScene(w)
-    base = cs.render(s, rt.mkStdGen(seed))
+    base, st0 = cs.render(s, rt.mkStdGen(seed), want_stats=True)
     assert np.isfinite(base).all()
+    # RT_B200_PRIMARY_CULL: camera rays that miss the world box end on the background inside k_raygen (pawn: the camera
+    # looks at the object from outside) or go through the queue like every other ray - the same paths either way
     variants = [{"RT_B200_FINISH": "0"}, {"RT_B200_FINISH": "4294967295"}, {"RT_B200_FINISH": "300", "RT_B200_TAIL_BATCH": "1"},
-                {"RT_B200_TILE": "0"}, {"RT_B200_TILE": "1"}, {"RT_B200_FINISH_REFILL": "32", "RT_B200_FINISH": "100000"}]
+                {"RT_B200_TILE": "0"}, {"RT_B200_TILE": "1"}, {"RT_B200_FINISH_REFILL": "32", "RT_B200_FINISH": "100000"},
+                {"RT_B200_PRIMARY_CULL": "0"}, {"RT_B200_PRIMARY_CULL": "1"}, {"RT_B200_PRIMARY_CULL": "1", "RT_B200_FINISH": "4294967295"}]
     for env in variants:
         for k, v in env.items():
             monkeypatch.setenv(k, v)
@@ -243,6 +246,7 @@ def test_tail_kernel_and_tiled_start_order_do_not_change_the_samples(built, name
         for k in env:
             monkeypatch.delenv(k)
         assert st["samples"] == base.shape[0] * base.shape[1] * s.cs_samplesPerPixel
+        assert st["rays"] == st0["rays"], env          # the same path segments, however they are scheduled
         assert np.allclose(img, base, rtol=2e-4, atol=2e-5), env
 
 
@@ -330,3 +334,26 @@ def test_interior_queries_bounded_by_free_flight_distance(built, monkeypatch):
     c = CompiledScene(w_pawn).render(s_pawn, rt.mkStdGen(55))
     monkeypatch.delenv("RT_B200_FINISH")
     assert np.isclose(c, a, rtol=2e-4, atol=2e-5).all(axis=2).mean() >= 0.999
+
+
+def test_primary_ray_culling_with_a_lens(built, monkeypatch):
+    """Culling is on only when the whole lens lies outside the world box; a thin-lens camera outside the box (defocus
+    blur, pool smaller than one sample pass so that compacted tiles cross iteration boundaries) renders the same
+    image as with the camera rays sent through the queue, and statistics count the culled rays as path segments."""
+    from raytrace_b200 import V3, constantTexture, lambertian, dielectric, group, sphere, bvhTree
+    balls = [sphere((x * 0.8, y * 0.8, -6 - 0.2 * x), 0.35) for x in range(-4, 5) for y in range(-2, 3)]      # 45: a real BVH, not a flat list
+    world = group([lambertian(constantTexture(V3(0.8, 0.3, 0.3))) << bvhTree(balls[:25]), dielectric(1.5) << bvhTree(balls[25:])])
+    s = rt.defaultCameraSettings.replace(cs_imageWidth=90, cs_aspectRatio=1.5, cs_samplesPerPixel=12, cs_maxRecursionDepth=8,
+                                         cs_background=scenes.sky, cs_defocusAngle=0.02, cs_focusDist=6.0, cs_vfov=1.2)
+    cs = CompiledScene(world)
+    assert cs.info()["n_bvh_nodes"] > 0
+    cs.handle.set_pool_size(3072)
+    a, sa = cs.render(s, rt.mkStdGen(11), want_stats=True)
+    monkeypatch.setenv("RT_B200_PRIMARY_CULL", "0")
+    b, sb = cs.render(s, rt.mkStdGen(11), want_stats=True)
+    monkeypatch.delenv("RT_B200_PRIMARY_CULL")
+    assert sa["rays"] == sb["rays"] and sa["samples"] == sb["samples"]
+    assert np.allclose(a, b, rtol=2e-4, atol=2e-5)
+    assert sa["iterations"] <= sb["iterations"]         # culled paths never occupy pool slots
+    ref, _ = OracleScene(world).render(s, 11)
+    assert abs(luminance(a.astype(np.float64)).mean() - luminance(ref).mean()) < 0.03 * luminance(ref).mean()
