@@ -795,29 +795,36 @@ struct Builder {
       const HPrim& p = prims[ps[0]];
       return p.type == PRIM_SPHERE && p.r > 0 && !(p.flags & PRIM_FLAG_MOVING);
     }
-    std::map<std::array<double, 3>, uint32_t> vid;
-    std::map<std::pair<uint32_t, uint32_t>, int> edges;
-    double vol6 = 0;
+    // vertices are identified by their exact coordinates (sort + unique: O(n log n), a million triangles in a fraction
+    // of a second), directed edges by the pair of vertex ids packed into 64 bits
     const uint32_t xf0 = prims[ps[0]].xform;
+    std::vector<std::array<double, 3>> pts;
+    pts.reserve(3 * ps.size());
+    double vol6 = 0;
     for (uint32_t pi : ps) {
       const HPrim& p = prims[pi];
       if (p.type != PRIM_TRI || !p.has_corners || p.xform != xf0 || (p.flags & PRIM_FLAG_MOVING)) return false;
-      uint32_t id[3];
       for (int k = 0; k < 3; k++) {
-        const std::array<double, 3> key{p.corner[k].x, p.corner[k].y, p.corner[k].z};
-        auto it = vid.find(key);
-        if (it == vid.end()) it = vid.emplace(key, (uint32_t)vid.size()).first;
-        id[k] = it->second;
+        if (!(std::isfinite(p.corner[k].x) && std::isfinite(p.corner[k].y) && std::isfinite(p.corner[k].z))) return false;
+        pts.push_back({p.corner[k].x + 0.0, p.corner[k].y + 0.0, p.corner[k].z + 0.0});   // + 0.0: -0 and +0 are one vertex
       }
-      if (id[0] == id[1] || id[1] == id[2] || id[0] == id[2]) return false;   // degenerate triangle
-      for (int k = 0; k < 3; k++) edges[{id[k], id[(k + 1) % 3]}]++;
       vol6 += dot(p.corner[0], cross(p.corner[1], p.corner[2]));
     }
-    for (const auto& e : edges) {
-      if (e.second != 1) return false;
-      auto rev = edges.find({e.first.second, e.first.first});
-      if (rev == edges.end() || rev->second != 1) return false;
+    std::vector<std::array<double, 3>> uniq(pts);
+    std::sort(uniq.begin(), uniq.end());
+    uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+    std::vector<uint64_t> edges;
+    edges.reserve(pts.size());
+    for (size_t t = 0; t < pts.size(); t += 3) {
+      uint64_t id[3];
+      for (int k = 0; k < 3; k++) id[k] = (uint64_t)(std::lower_bound(uniq.begin(), uniq.end(), pts[t + k]) - uniq.begin());
+      if (id[0] == id[1] || id[1] == id[2] || id[0] == id[2]) return false;   // degenerate triangle
+      for (int k = 0; k < 3; k++) edges.push_back(id[k] << 32 | id[(k + 1) % 3]);
     }
+    std::sort(edges.begin(), edges.end());
+    if (std::adjacent_find(edges.begin(), edges.end()) != edges.end()) return false;       // a directed edge used twice
+    for (uint64_t e : edges)                                                                // ... and its reverse exactly once
+      if (!std::binary_search(edges.begin(), edges.end(), (e << 32) | (e >> 32))) return false;
     // orientation in WORLD space: a reflecting instance transform (det < 0) turns the surface inside out
     const double* M = xforms[xf0].fwd.M;
     const double det = M[0] * (M[4] * M[8] - M[5] * M[7]) - M[1] * (M[3] * M[8] - M[5] * M[6]) + M[2] * (M[3] * M[7] - M[4] * M[6]);
