@@ -33,6 +33,12 @@ constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr uint32_t kLeafBit = 0x80000000u;
 constexpr uint32_t kLeafShift = 5u, kLeafCountMask = 31u, kLeafCap = 32u;   // leaf ref = kLeafBit | first << 5 | (count - 1)
 constexpr uint32_t kMediumBase = 0xFFFF0000u;  // hit.prim >= kMediumBase: medium (prim - base)
+// origin-geometry word of a queued path (Queue::d.w): the geometry id of the surface the ray starts on (< 2^26), kNone,
+// or kMediumBase + k after a scatter event in medium k.  kInsideFlag on a surface id: the surface is the closed boundary
+// of the scene's only medium and the ray leaves it INWARDS (refracted into the solid, or reflected back from inside), so
+// the segment starts inside the medium like one that starts at a scatter point (rt_trace.cuh::starts_inside_only_medium).
+// Traversal strips the flag before the id is compared with anything.
+constexpr uint32_t kInsideFlag = 0x80000000u;
 constexpr int kStackDepth = 32;                // shared-memory short stack entries per thread
 constexpr int kMaxTargets = 8;                 // cs_redirectTargets entries supported on device
 constexpr int kMaxMedia = 16;

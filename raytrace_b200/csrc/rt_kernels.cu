@@ -378,7 +378,6 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
                 // bounded interior query (fetch, below) met the boundary within tmin of the scatter point: the reference
                 // skips that crossing (open interval (1e-4, inf)) and sees the ray as already outside - redo the segment
                 // as an ordinary one (once per ~1e4 interior segments)
-                origin_geom = kNone;
                 tmin = tmin0;
                 h = Hit{inf, kNone, false};
                 cur = sc.surface_root;
@@ -481,11 +480,15 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
             if constexpr (kMedia) {
               // interior segment of a subsurface-scattering mesh: the free-flight distance bounds the surface query
               // (rt_trace.cuh::starts_inside_only_medium)
-              if (starts_inside_only_medium(sc, origin_geom)) {
+              const bool inside = starts_inside_only_medium(sc, origin_geom);
+              origin_geom = strip_inside_flag(origin_geom);
+              if (inside) {
                 const uint32_t pixel = __float_as_uint(__ldcs(q.thr + i).w);
                 const uint2 meta = __ldcs(q.meta + i);
                 h.t = free_flight_bound(sc, tmin0, A.key, pixel, (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x, meta.y);
-                if (h.t < inf) tmin = 0.f;   // the scatter point lies on no surface: look at (0, bound] so that a boundary crossing inside (0, tmin0] is noticed
+                // the origin is a scatter point or a surface the ray never re-hits (skip_a): look at (0, bound] so that a
+                // boundary crossing inside (0, tmin0] is noticed
+                if (h.t < inf) tmin = 0.f;
               }
             }
           }

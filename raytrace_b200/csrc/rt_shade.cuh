@@ -288,6 +288,12 @@ __device__ __forceinline__ bool shade_bounce(const DScene& sc, const DCamera& ca
   ray.o = s.p;
   ray.d = dir;
   origin_geom = s.geom;
+  if (sc.n_media == 1u && sc.media[0].closed != 0u && s.geom >= sc.media[0].geom_lo && s.geom <= sc.media[0].geom_hi) {
+    // leaving the closed boundary of the only medium: s.n faces the incoming ray, so the outward normal is s.n on a
+    // front-side hit and -s.n otherwise; a new direction against it goes into the solid
+    const float side = dot3(dir, s.n);
+    if (s.front ? side < 0.f : side > 0.f) origin_geom |= kInsideFlag;
+  }
   return true;
 }
 

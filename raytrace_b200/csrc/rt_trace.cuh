@@ -382,7 +382,12 @@ __device__ __forceinline__ void closest_hit(const DScene& sc, uint32_t root, con
 // mesh to find where it would leave) into one bounded by the free-flight distance: a mean free path of 0.2 in a pawn four
 // units tall culls nearly every node.  Returns the bound (inf: not applicable / rand = 0).
 __device__ __forceinline__ bool starts_inside_only_medium(const DScene& sc, uint32_t origin_geom) {
-  return origin_geom == kMediumBase && sc.n_media == 1u && sc.media[0].closed != 0u;   // closed implies shared
+  const bool scattered = origin_geom == kMediumBase;                                         // starts at a scatter point
+  const bool inwards = (origin_geom & kInsideFlag) != 0u && origin_geom < kMediumBase;       // leaves the boundary into the solid
+  return (scattered || inwards) && sc.n_media == 1u && sc.media[0].closed != 0u;             // closed implies shared
+}
+__device__ __forceinline__ uint32_t strip_inside_flag(uint32_t origin_geom) {
+  return origin_geom < kMediumBase ? origin_geom & ~kInsideFlag : origin_geom;
 }
 __device__ __forceinline__ float free_flight_bound(const DScene& sc, float tmin, uint2 key, uint32_t pixel, uint64_t sample, uint32_t bounce) {
   const uint4 rnd = rng4(key, pixel, sample, bounce, RNG_MEDIA);
@@ -399,6 +404,7 @@ __device__ __forceinline__ Hit trace_segment(const DScene& sc, const RayT& ray, 
   Hit best{inf, kNone, false};
   if constexpr ((F & TF_MEDIA) != 0) {
     if (with_media && starts_inside_only_medium(sc, origin_geom)) best.t = free_flight_bound(sc, tmin, key, pixel, sample, bounce);
+    origin_geom = strip_inside_flag(origin_geom);
   }
   // the bounded query looks at (0, bound]: a scatter point lies on no surface, and a boundary crossing inside (0, tmin] -
   // which the reference's open interval skips, so that it sees the ray as already outside - must be noticed
