@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define RT_B200_VERSION 0x00010000u
+#define RT_B200_VERSION 0x00020000u
 
 typedef enum RtStatus {
   RT_OK = 0,
@@ -166,6 +166,14 @@ typedef struct RtStats {
   double ms_finish;        /* device time of the tail kernel (k_finish); ms_raygen is what is left of ms_total */
   uint64_t rays_finish;    /* segments traced by the tail kernel (included in rays)               */
   uint64_t paths_finish;   /* paths the tail kernel carried to their end                          */
+  /* Work EXECUTED by the GPU traversal (k_traverse_p), counted on the device when RtOptions.count_work = 1 (an
+   * instrumented variant of the kernel; zeros otherwise).  These - not the reference's test counts - are what the
+   * traversal roofline is computed from: bytes = 64 per node pair, 64 per primitive record, 64 per box record. */
+  uint64_t node_pairs;     /* 64-byte child-pair fetches (two slab tests each)                    */
+  uint64_t sphere_tests;   /* sphere records fetched and tested                                   */
+  uint64_t planar_tests;   /* parallelogram / triangle records fetched and tested                 */
+  uint64_t box_tests;      /* aggregated-cuboid slab tests (one 64-byte box record each)          */
+  uint64_t rays_counted;   /* path segments covered by the four counters above                    */
 } RtStats;
 
 typedef struct RtSceneInfo {
@@ -181,6 +189,41 @@ typedef struct RtSceneInfo {
 } RtSceneInfo;
 
 typedef struct RtScene RtScene;
+
+/*
+ * Tuning / A-B options of one scene.  Every field: negative = library default (rt_options_init sets them all to -1).
+ * Commit-time fields are read by rt_scene_commit, render-time fields by every render of the scene.  Every combination
+ * renders the SAME samples (equal-seed images equal up to fp32 summation order; tests/test_gpu_edge_cases.py) - these are
+ * performance knobs and parity switches, not quality settings.  The library reads no environment variables.
+ */
+typedef struct RtOptions {
+  /* ---- commit time ---- */
+  int32_t bvh_reference;     /* 1: device tree = the reference's object-median tree (Geometry.hs:369-377); 0: binned SAH (default) */
+  int32_t leaf_max;          /* a `group` of at most this many primitives is one scanned leaf (default 24, <= 32) */
+  int32_t collapse;          /* subtrees of at most this many primitives become one leaf (default 4) */
+  int32_t aggregate_boxes;   /* 1 (default): a cuboid's six faces are answered by one slab test; 0: six planar tests */
+  int32_t shared_boundary;   /* 1 (default): a medium boundary that is also a surface is answered from the surface hit */
+  int32_t interior_bound;    /* 1 (default): interior segments of a closed shared boundary are bounded by the free-flight distance */
+  int32_t world_box;         /* 1 (default): keep the world box (camera rays that miss it end in k_raygen) */
+  int32_t split_moving;      /* 1 (default): moving instances get a tree of their own so that static primitives run the kernel without the per-primitive transform */
+  int32_t trace_commit;      /* 1: print the phases of the host scene pipeline to stderr */
+  double sah_node_cost;      /* cost of a node step in primitive tests (default 1.0) */
+  /* ---- render time ---- */
+  int64_t pool;              /* live-path pool size (default 2^24; rounded up to 1024) */
+  int64_t finish_max;        /* tail kernel takes over at <= this many live paths (0 = never, >= 2^32-1 = as soon as all paths started) */
+  int32_t finish_refill;     /* tail kernel: idle lanes per warp that trigger a claim (default 4) */
+  int32_t tail_batch;        /* iterations per host round trip once all paths have started (default 3) */
+  int32_t node_burst;        /* k_traverse_p: node steps per vote (default 4) */
+  int32_t refill;            /* k_traverse_p: idle lanes per warp that trigger a fetch (default 24) */
+  int32_t trav_blocks;       /* k_traverse_p: resident blocks per SM (default 8) */
+  int32_t tile;              /* 1: camera paths start in 8x4 pixel tiles (default for BVH scenes) */
+  int32_t primary_cull;      /* 1/0: force camera-ray culling against the world box on/off (default: on when the lens is outside it) */
+  int32_t shade_sort;        /* 1: k_shade handles paths grouped by material class (default: on when the scene mixes Perlin / image textures with plain ones) */
+  int32_t timing;            /* 0: no per-kernel events even when stats are requested (default 1) */
+  int32_t count_work;        /* 1: run the instrumented traversal kernel and fill RtStats.node_pairs ... (default 0) */
+  int32_t debug_sync;        /* 1: synchronise after every launch and name a faulting kernel on stderr */
+  int32_t reserved[8];
+} RtOptions;
 
 /* library */
 uint32_t rt_version(void);
@@ -270,8 +313,11 @@ int32_t rt_reduce_image(int32_t device, const void* multicast_ptr, const void* c
 int32_t rt_host_alloc(size_t bytes, void** out);
 int32_t rt_host_free(void* p);
 
-/* tuning knobs (0 = default) */
-int32_t rt_set_pool_size(RtScene* scene, uint32_t n_paths);
+/* tuning knobs */
+int32_t rt_options_init(RtOptions* opts);                              /* every field = -1 (library default) */
+int32_t rt_scene_set_options(RtScene* scene, const RtOptions* opts);   /* commit-time fields: call before rt_scene_commit */
+int32_t rt_scene_get_options(const RtScene* scene, RtOptions* opts);
+int32_t rt_set_pool_size(RtScene* scene, uint32_t n_paths);            /* = options.pool (0 = default) */
 
 /* image output step after the path (writeImage / writeImageSqrt, Ray.hs:248-260):
  * linear RGB float → 8-bit with the sRGB OETF (mode 0) or sqrt gamma (mode 1), clamped. */

@@ -229,23 +229,33 @@ class OracleScene:
         self._check(self.L.orc_probe_surface(self.h, C.byref(cam), float(time), out.ctypes.data_as(C.POINTER(C.c_double))))
         return out
 
-    def probe_stable(self, settings: CameraSettings, time: float = 0.5, delta: float = None, t_tol: float = 1e-4,
-                     eps_rad: float = 2e-6):
-        """Centre probe plus the mask of WELL-CONDITIONED pixels: the oracle's own answer (primitive id, and t
-        within t_tol relative) does not change when the probe ray is tilted by ±eps_rad (2e-6 rad ~ 16 fp32 ulps of
-        a direction component; `delta` overrides it in pixel units).  A pixel that passes has a condition number
-        (dt/t)/dtheta < t_tol/eps_rad = 50, so fp32 input rounding alone (~1.2e-7 rad) cannot move t by 1e-5.
-        Pixels whose centre ray runs through a primitive edge or grazes a silhouette fail this; their reference
-        answer is fp64 rounding noise (README scene column 46: a = 2.2e-16 on the mirror's edge)."""
+    def probe_tilted(self, settings: CameraSettings, time: float = 0.5, delta: float = None, eps_rad: float = 2e-6):
+        """The pixel-centre probe and the same probe tilted by ±eps_rad in x and y (2e-6 rad ~ 16 fp32 ulps of a
+        direction component; `delta` overrides it in pixel units): ids (5, H, W) uint32 and ts (5, H, W) float64,
+        index 0 = the centre ray."""
         import math
         if delta is None:
             h = imageHeight(settings)
             pixel_angle = 2.0 * math.tan(settings.cs_vfov / 2.0) / h
             delta = eps_rad / pixel_angle
-        ids, ts = self.probe_primary(settings, time)
-        stable = np.ones(ids.shape, bool)
-        for ox, oy in ((-delta, 0.0), (delta, 0.0), (0.0, -delta), (0.0, delta)):
+        out_i, out_t = [], []
+        for ox, oy in ((0.0, 0.0), (-delta, 0.0), (delta, 0.0), (0.0, -delta), (0.0, delta)):
             i2, t2 = self.probe_primary(settings, time, 0.5 + ox, 0.5 + oy)
+            out_i.append(i2)
+            out_t.append(t2)
+        return np.stack(out_i), np.stack(out_t)
+
+    def probe_stable(self, settings: CameraSettings, time: float = 0.5, delta: float = None, t_tol: float = 1e-4,
+                     eps_rad: float = 2e-6, tilted=None):
+        """Centre probe plus the mask of WELL-CONDITIONED pixels: the oracle's own answer (primitive id, and t
+        within t_tol relative) does not change when the probe ray is tilted by ±eps_rad.  A pixel that passes has a
+        condition number (dt/t)/dtheta < t_tol/eps_rad = 50, so fp32 input rounding alone (~1.2e-7 rad) cannot move t by
+        1e-5.  Pixels whose centre ray runs through a primitive edge or grazes a silhouette fail this; their reference
+        answer is fp64 rounding noise (README scene column 46: a = 2.2e-16 on the mirror's edge)."""
+        ids5, ts5 = tilted if tilted is not None else self.probe_tilted(settings, time, delta, eps_rad)
+        ids, ts = ids5[0], ts5[0]
+        stable = np.ones(ids.shape, bool)
+        for i2, t2 in zip(ids5[1:], ts5[1:]):
             stable &= i2 == ids
             hit = (ids != 0xFFFFFFFF) & (i2 == ids)
             with np.errstate(invalid="ignore", divide="ignore"):
@@ -276,3 +286,36 @@ class OracleScene:
         if not r:
             return None
         return dict(t=t.value, p=tuple(p), n=tuple(n), front=bool(front.value), uv=tuple(uv), prim=prim.value)
+
+
+def primary_gate(gpu_ids: np.ndarray, gpu_ts: np.ndarray, ids5: np.ndarray, ts5: np.ndarray, t_tol: float = 1e-5) -> dict:
+    """north_star gates 1 + 2 over ALL pixels of a primary-ray probe (no pixel is masked out).
+
+    A pixel PASSES when the GPU's primitive id is one the oracle itself returns for that pixel - at the centre ray or at
+    one of the four ±2e-6 rad tilts (`OracleScene.probe_tilted`) - AND the GPU's hit distance is within t_tol relative
+    of the oracle's t for THAT id (a miss must be a miss: t = inf).  Pixels whose id equals the centre answer are `raw`
+    matches; pixels that only match a tilted answer are `tie_explained` (the centre ray runs through a primitive edge:
+    which side wins is fp64 rounding noise in the reference itself, Geometry.hs:340-345,356-361 + Core.hs:83-84); every
+    other pixel is `unexplained`.  The gate is pass_frac >= 0.9999."""
+    MISS = 0xFFFFFFFF
+    gi = np.asarray(gpu_ids)
+    gt = np.asarray(gpu_ts, dtype=np.float64)
+    same = ids5 == gi[None]                                   # (5, H, W): the oracle returns the GPU's id here
+    with np.errstate(invalid="ignore", divide="ignore"):
+        rel = np.abs(gt[None] - ts5) / np.abs(ts5)
+    t_ok = np.where(gi[None] == MISS, np.isinf(gt)[None], rel <= t_tol)
+    ok5 = same & t_ok
+    raw = same[0]
+    passed = ok5.any(axis=0)
+    id_ok = same.any(axis=0)
+    rel_centre = np.where(raw & (gi != MISS), rel[0], 0.0)
+    n = gi.size
+    return {
+        "pixels": int(n), "raw_match": int(raw.sum()), "raw_frac": float(raw.mean()),
+        "tie_explained": int((passed & ~raw).sum()),          # id differs at the centre, equals a tilted answer, t agrees
+        "id_unexplained": int((~id_ok).sum()),                # id the oracle never returns around this pixel
+        "t_failed": int((id_ok & ~passed).sum()),             # id fine, distance off by more than t_tol
+        "unexplained": int((~passed).sum()), "pass_frac": float(passed.mean()),
+        "max_rel_dt_raw": float(np.nanmax(rel_centre)) if n else 0.0,
+        "passed_mask": passed,
+    }

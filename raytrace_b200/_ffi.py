@@ -80,7 +80,9 @@ class RtStats(C.Structure):
                 ("iterations", C.c_uint32), ("pool", C.c_uint32),
                 ("ms_total", C.c_double), ("ms_traverse", C.c_double), ("ms_shade", C.c_double),
                 ("ms_raygen", C.c_double), ("ms_copy", C.c_double), ("ms_finish", C.c_double),
-                ("rays_finish", C.c_uint64), ("paths_finish", C.c_uint64)]
+                ("rays_finish", C.c_uint64), ("paths_finish", C.c_uint64),
+                ("node_pairs", C.c_uint64), ("sphere_tests", C.c_uint64), ("planar_tests", C.c_uint64),
+                ("box_tests", C.c_uint64), ("rays_counted", C.c_uint64)]
 
     def as_dict(self) -> Dict[str, float]:
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -97,6 +99,23 @@ class RtSceneInfo(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class RtOptions(C.Structure):
+    """include/rt_b200.h RtOptions: negative = library default."""
+    _fields_ = [("bvh_reference", C.c_int32), ("leaf_max", C.c_int32), ("collapse", C.c_int32),
+                ("aggregate_boxes", C.c_int32), ("shared_boundary", C.c_int32), ("interior_bound", C.c_int32),
+                ("world_box", C.c_int32), ("split_moving", C.c_int32), ("trace_commit", C.c_int32),
+                ("sah_node_cost", C.c_double),
+                ("pool", C.c_int64), ("finish_max", C.c_int64),
+                ("finish_refill", C.c_int32), ("tail_batch", C.c_int32), ("node_burst", C.c_int32),
+                ("refill", C.c_int32), ("trav_blocks", C.c_int32), ("tile", C.c_int32),
+                ("primary_cull", C.c_int32), ("shade_sort", C.c_int32), ("timing", C.c_int32),
+                ("count_work", C.c_int32), ("debug_sync", C.c_int32), ("reserved", C.c_int32 * 8)]
+
+    NAMES = ("bvh_reference", "leaf_max", "collapse", "aggregate_boxes", "shared_boundary", "interior_bound", "world_box",
+             "split_moving", "trace_commit", "sah_node_cost", "pool", "finish_max", "finish_refill", "tail_batch",
+             "node_burst", "refill", "trav_blocks", "tile", "primary_cull", "shade_sort", "timing", "count_work", "debug_sync")
+
+
 # every symbol include/rt_b200.h declares (tests check that the .so exports all of them)
 EXPORTS = [
     "rt_version", "rt_last_error", "rt_device_count",
@@ -105,6 +124,7 @@ EXPORTS = [
     "rt_scene_get_bvh", "rt_scene_upload", "rt_image_height", "rt_render", "rt_render_device",
     "rt_probe_primary", "rt_probe_surface", "rt_set_pool_size", "rt_tonemap_u8",
     "rt_obj_parse", "rt_mesh_sizes", "rt_mesh_data", "rt_mesh_destroy", "rt_host_alloc", "rt_host_free", "rt_reduce_image",
+    "rt_options_init", "rt_scene_set_options", "rt_scene_get_options",
 ]
 
 _lib: Optional[C.CDLL] = None
@@ -146,6 +166,9 @@ def lib() -> C.CDLL:
                                    C.POINTER(C.c_float)]
     L.rt_probe_surface.argtypes = [vp, C.c_int32, C.POINTER(RtCamera), C.c_double, C.POINTER(C.c_float)]
     L.rt_set_pool_size.argtypes = [vp, C.c_uint32]
+    L.rt_options_init.argtypes = [C.POINTER(RtOptions)]
+    L.rt_scene_set_options.argtypes = [vp, C.POINTER(RtOptions)]
+    L.rt_scene_get_options.argtypes = [vp, C.POINTER(RtOptions)]
     L.rt_tonemap_u8.argtypes = [C.c_int32, C.POINTER(C.c_float), C.c_int32, C.c_int32,
                                 C.POINTER(C.c_uint8)]
     L.rt_obj_parse.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(vp)]
@@ -342,6 +365,23 @@ class SceneHandle:
 
     def set_pool_size(self, n: int):
         check(self._L.rt_set_pool_size(self._h, int(n)))
+
+    def set_options(self, **kw):
+        """Update RtOptions fields by name (None / negative = library default).  Commit-time fields (bvh_reference,
+        leaf_max, collapse, aggregate_boxes, shared_boundary, interior_bound, world_box, split_moving, sah_node_cost)
+        must be set before ``commit``."""
+        o = RtOptions()
+        check(self._L.rt_scene_get_options(self._h, C.byref(o)))
+        for k, v in kw.items():
+            if k not in RtOptions.NAMES:
+                raise KeyError(f"unknown option {k!r}")
+            setattr(o, k, -1 if v is None else (float(v) if k == "sah_node_cost" else int(v)))
+        check(self._L.rt_scene_set_options(self._h, C.byref(o)))
+
+    def get_options(self) -> dict:
+        o = RtOptions()
+        check(self._L.rt_scene_get_options(self._h, C.byref(o)))
+        return {k: getattr(o, k) for k in RtOptions.NAMES}
 
     @property
     def handle(self):

@@ -12,7 +12,11 @@ namespace rtb {
 static thread_local std::string g_error;
 void set_error(const std::string& msg) { g_error = msg; }
 
-Scene::Scene() { default_noise_tables(perm, grad); }
+void options_init(RtOptions& o) {
+  std::memset(&o, 0xFF, sizeof o);   // every integer field = -1
+  o.sah_node_cost = -1.0;
+}
+Scene::Scene() { default_noise_tables(perm, grad); options_init(opts); }
 Scene::~Scene() {
   for (auto& kv : devices) destroy_device_scene(kv.second);
 }
@@ -248,9 +252,28 @@ int32_t rt_scene_set_noise_tables(RtScene* sp, const int32_t* px, const int32_t*
 int32_t rt_scene_commit(RtScene* sp, uint32_t root) {
   if (!sp) { set_error("null scene"); return RT_ERR_INVALID_ARG; }
   Scene& s = *reinterpret_cast<Scene*>(sp);
-  for (auto& kv : s.devices) destroy_device_scene(kv.second);
-  s.devices.clear();
+  {
+    std::lock_guard<std::mutex> lock(s.devices_mu);   // get_device_scene takes the same lock
+    for (auto& kv : s.devices) destroy_device_scene(kv.second);
+    s.devices.clear();
+  }
   return flatten_scene(s, root);
+}
+
+int32_t rt_options_init(RtOptions* o) {
+  if (!o) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  options_init(*o);
+  return RT_OK;
+}
+int32_t rt_scene_set_options(RtScene* sp, const RtOptions* o) {
+  if (!sp || !o) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  reinterpret_cast<Scene*>(sp)->opts = *o;
+  return RT_OK;
+}
+int32_t rt_scene_get_options(const RtScene* sp, RtOptions* o) {
+  if (!sp || !o) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  *o = reinterpret_cast<const Scene*>(sp)->opts;
+  return RT_OK;
 }
 
 int32_t rt_scene_info(const RtScene* sp, RtSceneInfo* info) {
@@ -302,7 +325,7 @@ int32_t rt_image_height(const RtCamera* cam, int32_t* height) {
 
 int32_t rt_set_pool_size(RtScene* sp, uint32_t n) {
   if (!sp) { set_error("null scene"); return RT_ERR_INVALID_ARG; }
-  reinterpret_cast<Scene*>(sp)->pool_size = n;
+  reinterpret_cast<Scene*>(sp)->opts.pool = n ? (int64_t)n : -1;
   return RT_OK;
 }
 

@@ -994,7 +994,8 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
   try {
     Builder b(sc);
     // RT_B200_TRACE_COMMIT=1: phase times of the host scene pipeline on stderr (tuning aid)
-    const bool trace = std::getenv("RT_B200_TRACE_COMMIT") != nullptr;
+    const RtOptions& O = sc.opts;
+    const bool trace = O.trace_commit > 0;
     auto t_last = std::chrono::steady_clock::now();
     auto lap = [&](const char* what) {
       if (!trace) return;
@@ -1002,11 +1003,11 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
       std::fprintf(stderr, "[rt_b200 commit] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
       t_last = now;
     };
-    if (const char* e = std::getenv("RT_B200_LEAF")) b.kLeafMax = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
-    if (const char* e = std::getenv("RT_B200_BVH")) b.sah = std::strcmp(e, "reference") != 0;
-    if (const char* e = std::getenv("RT_B200_SAH_NODE_COST")) b.sah_node_cost = std::max(0.0, std::atof(e));
-    if (const char* e = std::getenv("RT_B200_NO_BOXES")) b.aggregate_boxes = std::atoi(e) == 0;
-    if (const char* e = std::getenv("RT_B200_COLLAPSE")) b.kCollapse = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)std::atoi(e)));
+    if (O.leaf_max >= 0) b.kLeafMax = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)O.leaf_max));
+    if (O.bvh_reference >= 0) b.sah = O.bvh_reference == 0;
+    if (O.sah_node_cost >= 0) b.sah_node_cost = O.sah_node_cost;
+    if (O.aggregate_boxes >= 0) b.aggregate_boxes = O.aggregate_boxes != 0;
+    if (O.collapse >= 0) b.kCollapse = std::min<uint32_t>(kLeafCap, std::max<uint32_t>(1, (uint32_t)O.collapse));
     b.mat_used.assign(sc.materials.size(), 0);
     b.tex_used.assign(sc.textures.size(), 0);
     XfState id;
@@ -1041,10 +1042,10 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
       b.collect_geoms(b.media[i].rtree, g);
       std::sort(g.begin(), g.end());
       g.erase(std::unique(g.begin(), g.end()), g.end());
-      if (!g.empty() && g.back() - g.front() + 1 == g.size() && std::getenv("RT_B200_NO_SHARED") == nullptr &&
+      if (!g.empty() && g.back() - g.front() + 1 == g.size() && O.shared_boundary != 0 &&
           std::includes(surf_geoms.begin(), surf_geoms.end(), g.begin(), g.end())) {
         dm.geom_lo = g.front(); dm.geom_hi = g.back(); dm.shared = 1;
-        if (std::getenv("RT_B200_NO_INTERIOR_BOUND") == nullptr && b.boundary_is_closed(b.media[i].rtree)) dm.closed = 1;
+        if (O.interior_bound != 0 && b.boundary_is_closed(b.media[i].rtree)) dm.closed = 1;
       }
     }
     fs.n_media = (uint32_t)b.media.size();
@@ -1054,7 +1055,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
       for (const HPrim& p : b.prims) wb.join(p.box);
       bool finite = !b.prims.empty();
       for (int k = 0; k < 3; k++) finite = finite && std::isfinite(wb.lo[k]) && std::isfinite(wb.hi[k]) && wb.lo[k] <= wb.hi[k];
-      if (finite && std::getenv("RT_B200_NO_PRIMARY_CULL") == nullptr) {
+      if (finite && O.world_box != 0) {
         double mx = 0;
         for (int k = 0; k < 3; k++) mx = std::max(mx, std::max(std::fabs(wb.lo[k]), std::fabs(wb.hi[k])));
         const double pad = 1e-5 * mx + 1e-6;

@@ -68,7 +68,7 @@ struct Scene {
   double grad[256][3];
   bool committed = false;
   FlatScene flat;
-  uint32_t pool_size = 0;  // 0 = default
+  RtOptions opts;          // tuning / A-B options (negative field = default); the library reads no environment variables
   std::map<int, DeviceScene*> devices;
   std::mutex devices_mu;   // uploads may race: renders of one committed scene can come from several OS threads
   Scene();
@@ -78,6 +78,7 @@ struct Scene {
 // rt_flatten.cpp
 int32_t flatten_scene(Scene& scene, uint32_t root);
 void default_noise_tables(int32_t perm[3][256], double grad[256][3]);
+void options_init(RtOptions& o);
 
 // rt_kernels.cu
 void destroy_device_scene(DeviceScene* d);

@@ -38,6 +38,18 @@ namespace rtb {
     }                                                                                            \
   } while (0)
 
+// Every ABI entry that selects a device restores the caller's current device on the way out (a torch process must not find
+// torch.cuda.current_device() changed behind its back).
+struct DeviceGuard {
+  int prev = -1;
+  DeviceGuard() { if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; cudaGetLastError(); } }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+struct DevBuf {                   // cudaMalloc'ed scratch freed on every exit path
+  void* p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+};
+
 constexpr int kTraverseBlock = 128;
 constexpr int kShadeBlock = 256;
 #ifndef RT_SHADE_MINB
@@ -59,6 +71,7 @@ struct Ctl {                      // device-resident control block of one render
   unsigned int n_gen, gen_done;   // k_raygen with primary-ray culling: camera paths queued so far / blocks finished
   unsigned int culled;            // ... camera rays of this iteration that missed the world box (ended on the background)
   unsigned long long rays_finish; // segments traced by the tail kernel (also counted in rays)
+  unsigned long long work[5];     // instrumented traversal (RtOptions.count_work): node pairs, sphere / planar / box tests, rays
 };
 
 struct Queue {                    // SoA live-ray queue (56 B per path)
@@ -249,28 +262,6 @@ __global__ void __launch_bounds__(kRaygenBlock) k_raygen(Ctl* __restrict__ ctl, 
 // ---- traversal / closest hit ---------------------------------------------------------------------------
 // F = scene feature bits (TF_*): one specialisation per combination that occurs (sphere-only, planar-only,
 // mixed; with / without media; a catch-all with moving instances), chosen at launch from FlatScene::features.
-template <uint32_t F>
-__global__ void __launch_bounds__(kTraverseBlock) k_traverse(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
-                                                             const __grid_constant__ RenderArgs A) {
-  extern __shared__ uint32_t s_stack[];   // (scene BVH depth + 1) x kTraverseBlock words: a deeper static stack would only eat L1
-  const uint32_t n = ctl->n_live;
-  uint32_t* stack = s_stack + threadIdx.x;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const float4 o4 = q.o[i], d4 = q.d[i];
-    RayT ray{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
-    uint32_t pixel = 0;
-    uint2 meta = make_uint2(0, 0);
-    if constexpr ((F & TF_MEDIA) != 0) {
-      pixel = __float_as_uint(q.thr[i].w);
-      meta = q.meta[i];
-    }
-    unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
-    Hit h = trace_segment<F>(sc, ray, __float_as_uint(d4.w), true, A.key, pixel, sample, meta.y, stack, kTraverseBlock);
-    // front flag travels in the sign of t (t > 0 always): negative = back side
-    A.hits[i] = make_float2(h.front ? h.t : -h.t, __uint_as_float(h.prim));
-  }
-}
-
 
 // ---- persistent traversal with dynamic ray fetch ----------------------------------------------------------------
 // Per-ray work varies by two orders of magnitude (a background ray leaves after the root pair; a ray through a mesh
@@ -286,10 +277,22 @@ constexpr int kPrimBurst = 8;   // primitives tested per PRIMITIVE step
 #ifndef RT_TRAV_MINB
 #define RT_TRAV_MINB 8   // resident-block floor of k_traverse_p: caps it at 64 registers (profiles/r01g_sweep_sah.txt)
 #endif
-template <uint32_t F>
+// kCount: instrumented variant (RtOptions.count_work) - counts the node pairs and primitive records this traversal really
+// fetches (per lane, warp-reduced once at the end) so that the roofline is computed from EXECUTED work.
+template <uint32_t F, bool kCount>
 __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
                                                                const __grid_constant__ RenderArgs A) {
-  extern __shared__ uint32_t s_stack[];   // (scene BVH depth + 1) x kTraverseBlock words: a deeper static stack would only eat L1
+  extern __shared__ uint32_t s_stack[];
+  uint32_t w_pairs = 0, w_sph = 0, w_pl = 0, w_box = 0, w_rays = 0;
+  auto count_prim = [&](uint32_t i) {   // classify primitive i the way intersect_rec does
+    if constexpr (kCount) {
+      const uint32_t tf = __float_as_uint(__ldg(sc.prims + 4 * (size_t)i + 3).x);
+      if (tf & PRIM_FLAG_BOXHEAD) w_box++;
+      else if (tf & PRIM_FLAG_BOXTAIL) {}
+      else if ((tf & PRIM_TYPE_MASK) == PRIM_SPHERE) w_sph++;
+      else w_pl++;
+    }
+  };   // (scene BVH depth + 1) x kTraverseBlock words: a deeper static stack would only eat L1
   uint32_t* const stack = s_stack + threadIdx.x;
   constexpr uint32_t stride = kTraverseBlock;
   constexpr bool kMedia = (F & TF_MEDIA) != 0;
@@ -342,6 +345,7 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
           const float4* N = sc.nodes + 2 * (size_t)cur;
           const F8 c0 = ldg256(N), c1 = ldg256(N + 2);
           const float4 l0 = c0.a, h0 = c0.b, l1 = c1.a, h1 = c1.b;
+          if constexpr (kCount) w_pairs++;
           float tn0, tn1;
           const bool hit0 = box_hit(l0, h0, inv, oinv, tmin, h.t, tn0);
           const bool hit1 = box_hit(l1, h1, inv, oinv, tmin, h.t, tn1);
@@ -358,7 +362,7 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
         }
       } else if (want_p) {
         const uint32_t stop = min(pe, pc + (uint32_t)kPrimBurst);
-        while (pc < stop) pc += intersect_prim<F>(sc, pc, ray, tmin, origin_geom, skip_b, h);   // a cuboid head answers 6 (never past pe)
+        while (pc < stop) { count_prim(pc); pc += intersect_prim<F>(sc, pc, ray, tmin, origin_geom, skip_b, h); }   // a cuboid head answers 6 (never past pe)
       }
       continue;
     }
@@ -400,7 +404,7 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
                   const uint32_t root = sc.media[m - 1].root;
                   if (root & kLeafBit) {    // boundary is a short primitive list: answer the query right here
                     const uint32_t first = (root & ~kLeafBit) >> kLeafShift, count = (root & kLeafCountMask) + 1u;
-                    for (uint32_t k = 0; k < count;) k += intersect_prim<F>(sc, first + k, ray, tmin, origin_geom, skip_b, h);
+                    for (uint32_t k = 0; k < count;) { count_prim(first + k); k += intersect_prim<F>(sc, first + k, ray, tmin, origin_geom, skip_b, h); }
                     continue;
                   }
                   cur = root;
@@ -441,7 +445,7 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
           h = Hit{inf, kNone, false};
           if (md.root & kLeafBit) {
             const uint32_t first = (md.root & ~kLeafBit) >> kLeafShift, count = (md.root & kLeafCountMask) + 1u;
-            for (uint32_t k = 0; k < count;) k += intersect_prim<F>(sc, first + k, ray, tmin, origin_geom, skip_b, h);
+            for (uint32_t k = 0; k < count;) { count_prim(first + k); k += intersect_prim<F>(sc, first + k, ray, tmin, origin_geom, skip_b, h); }
             continue;
           }
           cur = md.root;
@@ -471,6 +475,7 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
             oinv = ray.o * inv;
             slot = i;
             active = true;
+            if constexpr (kCount) w_rays++;
             cur = sc.surface_root;
             sp = 0;
             tmin = tmin0;
@@ -496,6 +501,17 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
       }
     }
     if (__ballot_sync(kFull, active) == 0u) break;
+  }
+  if constexpr (kCount) {
+    for (int o = 16; o > 0; o >>= 1) {
+      w_pairs += __shfl_down_sync(kFull, w_pairs, o); w_sph += __shfl_down_sync(kFull, w_sph, o);
+      w_pl += __shfl_down_sync(kFull, w_pl, o); w_box += __shfl_down_sync(kFull, w_box, o); w_rays += __shfl_down_sync(kFull, w_rays, o);
+    }
+    if (lane == 0) {
+      atomicAdd(&ctl->work[0], (unsigned long long)w_pairs); atomicAdd(&ctl->work[1], (unsigned long long)w_sph);
+      atomicAdd(&ctl->work[2], (unsigned long long)w_pl); atomicAdd(&ctl->work[3], (unsigned long long)w_box);
+      atomicAdd(&ctl->work[4], (unsigned long long)w_rays);
+    }
   }
 }
 
@@ -536,33 +552,6 @@ __device__ __forceinline__ Hit scan_flat(const DScene& sc, const FlatList& L, co
   }
   return h;
 }
-constexpr int kFlatBlock = 256;
-
-template <uint32_t F>
-__global__ void __launch_bounds__(kFlatBlock) k_traverse_flat(const Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
-                                                              const __grid_constant__ FlatList L, float2* __restrict__ hits) {
-  const uint32_t n = ctl->n_live;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const float4 o4 = q.o[i], d4 = q.d[i];
-    const RayT ray{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
-    const uint32_t origin_geom = __float_as_uint(d4.w);
-    const Hit h = scan_flat<F>(sc, L, ray, origin_geom);
-    hits[i] = make_float2(h.front ? h.t : -h.t, __uint_as_float(h.prim));
-  }
-}
-
-using FlatFn = void (*)(const Ctl*, Queue, const DScene, const FlatList, float2*);
-static FlatFn pick_flat(uint32_t features) {
-  if (features & (TF_MOVING | TF_MEDIA)) return nullptr;
-  if (const char* e = std::getenv("RT_B200_TRAVERSE")) if (std::strcmp(e, "flat") != 0) return nullptr;
-  switch (features & (TF_SPHERE | TF_PLANAR)) {
-    case TF_SPHERE: return k_traverse_flat<TF_SPHERE>;
-    case TF_PLANAR: return k_traverse_flat<TF_PLANAR>;
-    case TF_SPHERE | TF_PLANAR: return k_traverse_flat<TF_SPHERE | TF_PLANAR>;
-    default: return nullptr;
-  }
-}
-
 using TraverseFn = void (*)(Ctl*, Queue, const DScene, const RenderArgs);
 template <template <uint32_t> class K, uint32_t B>   // B = TF_BOX or 0
 static TraverseFn pick_planar_variant(uint32_t features) {
@@ -584,14 +573,8 @@ static TraverseFn pick_by_features(uint32_t features) {
   }
   return pick_planar_variant<K, 0u>(features);
 }
-template <uint32_t F> struct StaticK { static TraverseFn fn() { return k_traverse<F>; } };
-template <uint32_t F> struct PersistentK { static TraverseFn fn() { return k_traverse_p<F>; } };
-// default: persistent warps with dynamic fetch; RT_B200_TRAVERSE=static selects the one-ray-per-thread kernel (A/B runs)
-static TraverseFn pick_traverse(uint32_t features) {
-  const char* e = std::getenv("RT_B200_TRAVERSE");
-  if (e && std::strcmp(e, "static") == 0) return pick_by_features<StaticK>(features);
-  return pick_by_features<PersistentK>(features);
-}
+template <uint32_t F> struct PersistentK { static TraverseFn fn() { return k_traverse_p<F, false>; } };
+template <uint32_t F> struct CountedK { static TraverseFn fn() { return k_traverse_p<F, true>; } };   // RtOptions.count_work
 
 // ---- shading, accumulation, compaction -------------------------------------------------------------------
 // ---- TMA (bulk async copy) + mbarrier helpers: the shading kernel prefetches its next tile of queue records into
@@ -627,6 +610,10 @@ __device__ __forceinline__ bool shade_path(const DScene& sc, const RenderArgs& A
   const uint4 rnd = rng4(A.key, pixel, sample, meta.y, RNG_SHADE);
   f3 contrib;
   bool alive = shade_bounce(sc, A.cam, T, ray, hit, thr, origin_geom, rnd, contrib);
+  // a non-finite weight (pdf underflow at a grazing light direction) must not reach the accumulators: one NaN would own
+  // the pixel for the whole render
+  if (!(fabsf(thr.x + thr.y + thr.z) < 3.0e38f)) { alive = false; thr = mk3(0.f, 0.f, 0.f); }
+  if (!(fabsf(contrib.x + contrib.y + contrib.z) < 3.0e38f)) contrib = mk3(0.f, 0.f, 0.f);
   if (contrib.x != 0.f || contrib.y != 0.f || contrib.z != 0.f) {
     float* s = A.sum + 3 * (size_t)pixel;
     atomicAdd(s, contrib.x);
@@ -700,13 +687,13 @@ __device__ __forceinline__ void shade_tiles(Ctl* __restrict__ ctl, const Queue& 
   const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   int par = 0;
   const uint32_t stride = gridDim.x * kShadeBlock;
-  if (threadIdx.x == 0 && blockIdx.x * kShadeBlock < n_stored) issue_tile(0, blockIdx.x * kShadeBlock);
+  if (threadIdx.x == 0 && blockIdx.x * kShadeBlock < n_stored && blockIdx.x * kShadeBlock < n) issue_tile(0, blockIdx.x * kShadeBlock);
   uint32_t tile = 0;
   for (uint32_t base = blockIdx.x * kShadeBlock; base < n; base += stride, par ^= 1, tile++) {
     const uint32_t i = base + threadIdx.x;
     // prefetch the NEXT tile (tiles never run past the allocation: the pool is a multiple of 1024 slots); the stage it
     // lands in was last read one iteration ago, before that iteration's __syncthreads
-    if (threadIdx.x == 0 && base + stride < n_stored) {
+    if (threadIdx.x == 0 && base + stride < n_stored && base + stride < n) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       issue_tile(par ^ 1, base + stride);
     }
@@ -794,7 +781,6 @@ __global__ void __launch_bounds__(kShadeBlock, RT_TRACE_FLAT_MINB) k_trace_flat(
 using TraceFlatFn = void (*)(Ctl*, Queue, Queue, const DScene, const RenderArgs, const FlatList);
 static TraceFlatFn pick_trace_flat(uint32_t features) {
   if (features & (TF_MOVING | TF_MEDIA)) return nullptr;
-  if (const char* e = std::getenv("RT_B200_TRAVERSE")) if (std::strcmp(e, "fused") != 0) return nullptr;
   switch (features & (TF_SPHERE | TF_PLANAR)) {
     case TF_SPHERE: return k_trace_flat<TF_SPHERE>;
     case TF_PLANAR: return k_trace_flat<TF_PLANAR>;
@@ -889,6 +875,8 @@ __device__ __forceinline__ void finish_paths(Ctl* __restrict__ ctl, const Queue&
       ctl->paths_finish += n;
       ctl->n_live = 0;
       ctl->n_cur = 0;
+      ctl->fill_lo = 0;          // a launch queued behind the end of the render must see an EMPTY iteration (no stale tail range)
+      ctl->fill_item0 = ctl->next_item;
       ctl->iterations += 1;
     }
   }
@@ -1030,12 +1018,14 @@ struct DeviceScene {              // one committed scene resident on one device:
 // does not re-allocate half a gigabyte, and concurrent renders (GHC safe calls from several OS threads) never share one.
 struct Workspace {
   int device = 0;
-  uint32_t pool = 0;
+  uint32_t pool = 0;        // capacity of the queues (only ever grows: cudaFree synchronises the whole device)
+  uint32_t pool_used = 0;   // logical pool of the current render (<= pool)
   Queue q[2]{};
   float2* hits = nullptr;
   Ctl* ctl = nullptr;
   Ctl* h_ctl = nullptr;   // pinned, two snapshot slots
   cudaEvent_t snap_ev[2] = {nullptr, nullptr};
+  cudaEvent_t copy_ev[2] = {nullptr, nullptr};   // brackets the image read-back of rt_render (RtStats.ms_copy)
   float* sum = nullptr;
   float* sumsq = nullptr;
   float* out = nullptr;
@@ -1059,6 +1049,7 @@ static void destroy_workspace(Workspace* w) {
   if (w->h_out) cudaFreeHost(w->h_out);
   if (w->last_done) cudaEventDestroy(w->last_done);
   for (cudaEvent_t ev : w->snap_ev) if (ev) cudaEventDestroy(ev);
+  for (cudaEvent_t ev : w->copy_ev) if (ev) cudaEventDestroy(ev);
   if (w->stream) cudaStreamDestroy(w->stream);
   delete w;
 }
@@ -1074,6 +1065,7 @@ static int32_t acquire_workspace(int device, Workspace** out) {
   cudaError_t e = cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&w->h_ctl), 2 * sizeof(Ctl));
   for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaEventCreateWithFlags(&w->snap_ev[k], cudaEventDisableTiming);
+  for (int k = 0; k < 2 && e == cudaSuccess; k++) e = cudaEventCreate(&w->copy_ev[k]);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&w->last_done, cudaEventDisableTiming);
   if (e != cudaSuccess) {
     set_error(std::string("workspace creation failed: ") + cudaGetErrorString(e));
@@ -1098,6 +1090,7 @@ struct WorkspaceLease {           // RAII: returns the workspace on every exit p
 
 void destroy_device_scene(DeviceScene* d) {
   if (!d) return;
+  DeviceGuard guard;
   cudaSetDevice(d->device);
   if (d->arena) cudaFree(d->arena);
   delete d;
@@ -1283,7 +1276,8 @@ static int32_t make_camera(const RtCamera& c, DCamera* out) {
 }
 
 static int32_t ensure_workspace(Workspace& ds, uint32_t pool, size_t accum_elems) {
-  if (ds.pool != pool) {
+  ds.pool_used = pool;
+  if (ds.pool < pool) {
     auto drop = [&](void* p) {
       if (!p) return;
       cudaFree(p);
@@ -1329,8 +1323,7 @@ static int32_t ensure_workspace(Workspace& ds, uint32_t pool, size_t accum_elems
 }
 
 static uint32_t choose_pool(const Scene& s, unsigned long long total_items) {
-  uint32_t pool = s.pool_size;
-  if (const char* e = std::getenv("RT_B200_POOL")) pool = (uint32_t)std::strtoul(e, nullptr, 10);
+  uint32_t pool = s.opts.pool > 0 ? (uint32_t)std::min<int64_t>(s.opts.pool, 1ll << 30) : 0u;
   if (pool == 0) pool = 1u << 24;   // fewer, larger iterations: launch gaps and kernel tails amortise (sweeps in profiles/); 1.9 GB
   pool = (std::max<uint32_t>(pool, 1024) + 1023u) / 1024u * 1024u;   // whole 256-slot tiles for the TMA prefetch in k_shade
   if (total_items < pool) pool = (uint32_t)std::max<unsigned long long>(1024, (total_items + 1023) / 1024 * 1024);
@@ -1343,7 +1336,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   const uint32_t n_pixels = (uint32_t)cam.W * (uint32_t)cam.H;
   const unsigned long long total = (unsigned long long)n_pixels * n_samples;
   if (cam.max_depth <= 0) {   // rayColor 0 _ _ = zero (Ray.hs:176): every path is black before its first segment
-    if (stats) { stats->samples = total; stats->pool = ds.pool; }
+    if (stats) { stats->samples = total; stats->pool = ds.pool_used; }
     return RT_OK;
   }
   RenderArgs A{};
@@ -1361,12 +1354,13 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   // generate, so it takes over as soon as every path has started, whatever their number.  BVH scenes: worth it only when
   // the depth limit leaves dozens of near-empty iterations to replace (demo1 / demo2, depth 50); at depth 20 with
   // subsurface media (pawn, bunny) the iterations are cheaper.  Sweeps: profiles/r01h_sweep_tail.txt
+  const RtOptions& O = s.opts;
   A.finish_max = dev.has_flat ? 0xFFFFFFFFu : (cam.max_depth > 24 ? 1u << 20 : 0u);
-  if (const char* e = std::getenv("RT_B200_FINISH")) A.finish_max = (uint32_t)std::strtoul(e, nullptr, 10);
+  if (O.finish_max >= 0) A.finish_max = (uint32_t)std::min<int64_t>(O.finish_max, 0xFFFFFFFFll);
   A.finish_refill = 4;
-  if (const char* e = std::getenv("RT_B200_FINISH_REFILL")) A.finish_refill = std::min(32, std::max(1, std::atoi(e)));
+  if (O.finish_refill >= 0) A.finish_refill = std::min(32, std::max(1, (int)O.finish_refill));
   A.tile = dev.has_flat ? 0u : 1u;   // coherence only matters to the BVH kernels; the flat scan is the same for every ray
-  if (const char* e = std::getenv("RT_B200_TILE")) A.tile = std::atoi(e) ? 1u : 0u;
+  if (O.tile >= 0) A.tile = O.tile ? 1u : 0u;
   // Camera rays that miss the world box end inside k_raygen.  Worth the test (and the compaction it brings) only when the
   // lens lies OUTSIDE the box - from inside it every ray passes (demo1 / demo2: +1 ms for nothing).  Flat scenes: the fused
   // kernel generates its own camera rays.
@@ -1379,13 +1373,13 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
     for (int k = 0; k < 3; k++)
       if (cam.center[k] + lens < dev.d.world_lo[k] || cam.center[k] - lens > dev.d.world_hi[k]) A.cull = 1u;
   }
-  if (const char* e = std::getenv("RT_B200_PRIMARY_CULL")) A.cull = (std::atoi(e) && dev.d.has_world_box) ? 1u : 0u;
+  if (O.primary_cull >= 0) A.cull = (O.primary_cull && dev.d.has_world_box && !dev.has_flat) ? 1u : 0u;
   for (int k = 0; k < 3; k++) { A.world_lo[k] = dev.d.world_lo[k]; A.world_hi[k] = dev.d.world_hi[k]; }
   int tail_batch = 3;                // iterations (each followed by a k_finish check) per host round trip once all paths have started
-  if (const char* e = std::getenv("RT_B200_TAIL_BATCH")) tail_batch = std::min(64, std::max(1, std::atoi(e)));
-  if (const char* e = std::getenv("RT_B200_NODE_BURST")) A.node_burst = std::min(8, std::max(1, std::atoi(e)));
-  if (const char* e = std::getenv("RT_B200_REFILL")) A.refill = std::min(32, std::max(1, std::atoi(e)));
-  const bool timing = stats != nullptr && std::getenv("RT_B200_NOTIMING") == nullptr;
+  if (O.tail_batch >= 0) tail_batch = std::min(64, std::max(1, (int)O.tail_batch));
+  if (O.node_burst >= 0) A.node_burst = std::min(8, std::max(1, (int)O.node_burst));
+  if (O.refill >= 0) A.refill = std::min(32, std::max(1, (int)O.refill));
+  const bool timing = stats != nullptr && O.timing != 0;
   const size_t kMaxTimed = 4096;            // iterations with per-kernel events
   if (timing && ds.events.size() < kMaxTimed * 4 + 2) {
     size_t want = kMaxTimed * 4 + 2;
@@ -1398,14 +1392,13 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
   if (timing) { ev_begin = ds.events[kMaxTimed * 4]; ev_end = ds.events[kMaxTimed * 4 + 1]; RT_CUDA(cudaEventRecord(ev_begin, stream)); }
 
-  const TraverseFn traverse = pick_traverse(s.flat.features);
-  const FlatFn flat = dev.has_flat ? pick_flat(s.flat.features) : nullptr;
+  const bool count_work = stats != nullptr && O.count_work > 0;
+  const TraverseFn traverse = count_work ? pick_by_features<CountedK>(s.flat.features) : pick_by_features<PersistentK>(s.flat.features);
   const TraceFlatFn fused = dev.has_flat ? pick_trace_flat(s.flat.features) : nullptr;
   const TraverseFn finish = pick_by_features<FinishK>(s.flat.features);
   const FinishFlatFn finish_flat = fused ? pick_finish_flat(s.flat.features) : nullptr;
-  if (dev.has_flat && !finish_flat && !std::getenv("RT_B200_FINISH")) A.finish_max = 1u << 18;   // A/B variants of the flat path: generic k_finish
   int g_trav = dev.sm_count * 8, g_shade = dev.sm_count * 8, g_gen = dev.sm_count * 4;
-  if (const char* e = std::getenv("RT_B200_TRAV_BLOCKS")) g_trav = dev.sm_count * std::max(1, std::atoi(e));
+  if (O.trav_blocks >= 0) g_trav = dev.sm_count * std::max(1, (int)O.trav_blocks);
   const size_t stack_bytes = (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t);
   uint64_t launches = 0;
   size_t timed = 0;
@@ -1415,12 +1408,12 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   // The loop is device driven: the last k_shade block prepares the next iteration, the host only launches batches
   // and reads the 80-byte control block back between them.  Batch length follows the measured consumption of work
   // items (iterations past the end are empty launches, so the estimate stays a little short).
-  k_begin<<<1, 1, 0, stream>>>(ds.ctl, total, ds.pool);
+  k_begin<<<1, 1, 0, stream>>>(ds.ctl, total, ds.pool_used);
   launches++;
   // tail mode: every camera path has started (known up front when the whole range fits the pool, e.g. one GPU's share
   // of a small render).  From then on k_finish is checked after EVERY iteration - a ~2 us no-op until few enough paths
   // are left - so the takeover never waits for a host round trip, and launches queued past it are empty.
-  bool tail = total <= ds.pool;
+  bool tail = total <= ds.pool_used;
   // flat scenes, unbounded tail kernel: once every path has started, ONE more iteration + k_finish_flat completes the
   // render, so the launch sequence is known without reading the control block back
   const bool finish_all = finish_flat != nullptr && A.finish_max == 0xFFFFFFFFu;
@@ -1428,7 +1421,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   const unsigned long long tail_chunk = finish_all ? 1ull : (A.finish_max ? (unsigned long long)tail_batch : 8ull);
 
   // RT_B200_DEBUG_SYNC=1: synchronise after every launch and name the kernel that faulted (stderr)
-  const bool debug_sync = std::getenv("RT_B200_DEBUG_SYNC") != nullptr;
+  const bool debug_sync = O.debug_sync > 0;
   auto dbg = [&](const char* what) {
     if (!debug_sync) return;
     cudaError_t e = cudaStreamSynchronize(stream);
@@ -1446,8 +1439,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
       k_raygen<<<g_gen, kRaygenBlock, 0, stream>>>(ds.ctl, q, A);
       dbg("k_raygen");
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 0], stream);
-      if (flat) flat<<<dev.sm_count * 8, kFlatBlock, 0, stream>>>(ds.ctl, q, dev.d, dev.flat, ds.hits);
-      else traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, dev.d, A);
+      traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, dev.d, A);
       dbg("traverse");
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
       k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
@@ -1465,12 +1457,10 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
       if (t_this) { cudaEventRecord(ds.events[(timed - 1) * 4 + 3], stream); has_fin[timed - 1] = 1; }
     }
   };
-  // A chunk = some iterations, then a snapshot of the control block into one of two pinned slots + an event; the host
-  // waits for the snapshot, plans the next chunk from the measured consumption of work items (iterations past the end
-  // are empty launches, so the estimate stays a little short) and launches it.  RT_B200_PIPELINE=1 keeps one more chunk
-  // queued behind the one waited for, so the GPU never idles during a read-back; measured (profiles/r01h_sweep_tail.txt):
-  // no gain - the ~5 round trips of a render cost less than the staler plans (one more iteration before the tail kernel
-  // takes over, one chunk of empty launches at the end): Cornell 10.3 -> 10.4 ms, pawn 35.4 -> 35.7.  Off.
+  // A chunk = some iterations, then a snapshot of the control block into a pinned slot + an event; the host waits for
+  // the snapshot, plans the next chunk from the measured consumption of work items (iterations past the end are empty
+  // launches, so the estimate stays a little short) and launches it.  (Keeping one more chunk queued behind the one
+  // waited for was measured in round 1 and dropped: the ~5 round trips of a render cost less than the staler plans.)
   struct Flight { int slot; unsigned long long iters; };
   int slot = 0;
   auto launch_chunk = [&](unsigned long long n) -> Flight {
@@ -1481,11 +1471,9 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
     slot ^= 1;
     return f;
   };
-  bool pipeline = false;
-  if (const char* e = std::getenv("RT_B200_PIPELINE")) pipeline = std::atoi(e) != 0;
   unsigned long long chunk_next = tail ? tail_chunk : 2ull;
   unsigned long long prev_started = 0, prev_iters = 0;
-  Flight cur_f = launch_chunk(tail ? tail_chunk : (pipeline ? 2ull : 4ull));
+  Flight cur_f = launch_chunk(tail ? tail_chunk : 4ull);
   if (single_shot && !stats) {
     // nothing to read back: return with the work queued (stream-ordered completion, like any device-buffer API);
     // whoever borrows this workspace next orders its stream behind last_done
@@ -1496,28 +1484,17 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   }
   const Ctl* final_ctl = nullptr;
   for (;;) {
-    Flight next_f{};
-    const bool have_next = pipeline;
-    if (have_next) next_f = launch_chunk(chunk_next);
     RT_CUDA(cudaEventSynchronize(ds.snap_ev[cur_f.slot]));
     const Ctl& c = ds.h_ctl[cur_f.slot];
-    if (c.n_live == 0) {   // the render was complete at this snapshot; what was queued behind it is empty
-      if (have_next) { RT_CUDA(cudaEventSynchronize(ds.snap_ev[next_f.slot])); final_ctl = &ds.h_ctl[next_f.slot]; }
-      else final_ctl = &c;
-      break;
-    }
+    if (c.n_live == 0) { final_ctl = &c; break; }   // the render was complete at this snapshot
     const unsigned long long started = c.next_item;
     const double per_iter = cur_f.iters > prev_iters ? (double)(started - prev_started) / (double)(cur_f.iters - prev_iters) : 0.0;
     prev_started = started;
     prev_iters = cur_f.iters;
-    const double inflight = have_next ? (double)(next_f.iters - cur_f.iters) : 0.0;
     if (started >= total) { tail = true; chunk_next = tail_chunk; }
-    else if (per_iter >= 1.0) {
-      const double est_left = std::max(0.0, (double)(total - started) - per_iter * inflight);
-      chunk_next = (unsigned long long)std::min(4096.0, std::max(2.0, (pipeline ? 0.45 : 0.9) * est_left / per_iter));
-    } else chunk_next = 2;
-    if (!have_next) next_f = launch_chunk(chunk_next);
-    cur_f = next_f;
+    else if (per_iter >= 1.0) chunk_next = (unsigned long long)std::min(4096.0, std::max(2.0, 0.9 * (double)(total - started) / per_iter));
+    else chunk_next = 2;
+    cur_f = launch_chunk(chunk_next);
     if (iter > 100000000u) { set_error("wavefront loop did not terminate"); return RT_ERR_CUDA; }
   }
   if (timing) { RT_CUDA(cudaEventRecord(ev_end, stream)); RT_CUDA(cudaEventSynchronize(ev_end)); }
@@ -1529,7 +1506,9 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
     stats->paths_finish = final_ctl->paths_finish;
     stats->launches = launches;
     stats->iterations = final_ctl->iterations;
-    stats->pool = ds.pool;
+    stats->pool = ds.pool_used;
+    stats->node_pairs = final_ctl->work[0]; stats->sphere_tests = final_ctl->work[1]; stats->planar_tests = final_ctl->work[2];
+    stats->box_tests = final_ctl->work[3]; stats->rays_counted = final_ctl->work[4];
     if (timing) {
       float ms = 0;
       cudaEventElapsedTime(&ms, ev_begin, ev_end);
@@ -1570,6 +1549,8 @@ static int32_t run_wavefront(Scene& s, DeviceScene& dev, Workspace& ds, const DC
     total.samples += part.samples; total.rays += part.rays; total.launches += part.launches; total.iterations += part.iterations;
     total.pool = part.pool; total.ms_total += part.ms_total; total.ms_traverse += part.ms_traverse; total.ms_shade += part.ms_shade;
     total.ms_raygen += part.ms_raygen; total.ms_finish += part.ms_finish; total.rays_finish += part.rays_finish; total.paths_finish += part.paths_finish;
+    total.node_pairs += part.node_pairs; total.sphere_tests += part.sphere_tests; total.planar_tests += part.planar_tests;
+    total.box_tests += part.box_tests; total.rays_counted += part.rays_counted;
     first_sample += n;
     n_samples -= n;
   }
@@ -1597,6 +1578,7 @@ int32_t rt_device_count(int32_t* n) {
 
 int32_t rt_scene_upload(RtScene* sp, int32_t device) {
   if (!sp) { set_error("null scene"); return RT_ERR_INVALID_ARG; }
+  DeviceGuard guard;
   DeviceScene* ds = nullptr;
   return get_device_scene(*reinterpret_cast<Scene*>(sp), device, &ds);
 }
@@ -1604,6 +1586,7 @@ int32_t rt_scene_upload(RtScene* sp, int32_t device) {
 int32_t rt_render_device(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample,
                          uint64_t n_samples, float* d_sum, float* d_sumsq, void* cuda_stream, RtStats* stats) {
   if (!sp || !rc || !d_sum) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  DeviceGuard guard;
   Scene& s = *reinterpret_cast<Scene*>(sp);
   DeviceScene* ds = nullptr;
   int32_t st = get_device_scene(s, device, &ds);
@@ -1689,6 +1672,7 @@ static bool is_pinned_host(const void* p, size_t bytes) {
 int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample,
                   uint64_t n_samples, float* rgb_out, float* rgb_sumsq_out, RtStats* stats) {
   if (!sp || !rc || !rgb_out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  DeviceGuard guard;
   Scene& s = *reinterpret_cast<Scene*>(sp);
   DeviceScene* ds = nullptr;
   int32_t st = get_device_scene(s, device, &ds);
@@ -1713,9 +1697,7 @@ int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed
     st = run_wavefront(s, *ds, ws, cam, seed, first_sample, n_samples, ws.sum, rgb_sumsq_out ? ws.sumsq : nullptr, stream, stats);
     if (st != RT_OK) return st;
   }
-  cudaEvent_t c0, c1;
-  RT_CUDA(cudaEventCreate(&c0));
-  RT_CUDA(cudaEventCreate(&c1));
+  const cudaEvent_t c0 = ws.copy_ev[0], c1 = ws.copy_ev[1];
   k_scale<<<ds->sm_count * 4, 256, 0, stream>>>(ws.sum, ws.out, (int)elems, 1.0f / (float)cam.spp);   // Ray.hs:232
   RT_CUDA(cudaEventRecord(c0, stream));
   // page-locked caller buffers (rt_host_alloc, …) are written by the copy engine directly; pageable ones go
@@ -1738,14 +1720,13 @@ int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed
     stats->ms_copy = ms;
     stats->launches += 1;
   }
-  cudaEventDestroy(c0);
-  cudaEventDestroy(c1);
   RT_CUDA(cudaGetLastError());
   return RT_OK;
 }
 
 int32_t rt_probe_primary(RtScene* sp, int32_t device, const RtCamera* rc, double time, uint32_t* ids, float* ts) {
   if (!sp || !rc || !ids || !ts) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  DeviceGuard guard;
   Scene& s = *reinterpret_cast<Scene*>(sp);
   DeviceScene* ds = nullptr;
   int32_t st = get_device_scene(s, device, &ds);
@@ -1758,22 +1739,22 @@ int32_t rt_probe_primary(RtScene* sp, int32_t device, const RtCamera* rc, double
   if (st != RT_OK) return st;
   cudaStream_t stream = lease.w->stream;
   const size_t n = (size_t)cam.W * cam.H;
-  uint32_t* d_ids = nullptr;
-  float* d_ts = nullptr;
-  RT_CUDA(cudaMalloc((void**)&d_ids, n * 4));
-  RT_CUDA(cudaMalloc((void**)&d_ts, n * 4));
+  DevBuf b_ids, b_ts;
+  RT_CUDA(cudaMalloc(&b_ids.p, n * 4));
+  RT_CUDA(cudaMalloc(&b_ts.p, n * 4));
+  uint32_t* d_ids = static_cast<uint32_t*>(b_ids.p);
+  float* d_ts = static_cast<float*>(b_ts.p);
   k_probe<<<ds->sm_count * 8, kTraverseBlock, (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t), stream>>>(ds->d, cam, (float)time, d_ids, d_ts);
   cudaError_t e = cudaMemcpyAsync(ids, d_ids, n * 4, cudaMemcpyDeviceToHost, stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(ts, d_ts, n * 4, cudaMemcpyDeviceToHost, stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
-  cudaFree(d_ids);
-  cudaFree(d_ts);
   RT_CUDA(e);
   return RT_OK;
 }
 
 int32_t rt_probe_surface(RtScene* sp, int32_t device, const RtCamera* rc, double time, float* out) {
   if (!sp || !rc || !out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
+  DeviceGuard guard;
   Scene& s = *reinterpret_cast<Scene*>(sp);
   DeviceScene* ds = nullptr;
   int32_t st = get_device_scene(s, device, &ds);
@@ -1786,12 +1767,12 @@ int32_t rt_probe_surface(RtScene* sp, int32_t device, const RtCamera* rc, double
   if (st != RT_OK) return st;
   cudaStream_t stream = lease.w->stream;
   const size_t n = (size_t)cam.W * cam.H * 10;
-  float* d_out = nullptr;
-  RT_CUDA(cudaMalloc((void**)&d_out, n * 4));
+  DevBuf b_out;
+  RT_CUDA(cudaMalloc(&b_out.p, n * 4));
+  float* d_out = static_cast<float*>(b_out.p);
   k_probe_surface<<<ds->sm_count * 8, kTraverseBlock, (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t), stream>>>(ds->d, cam, (float)time, d_out);
   cudaError_t e = cudaMemcpyAsync(out, d_out, n * 4, cudaMemcpyDeviceToHost, stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
-  cudaFree(d_out);
   RT_CUDA(e);
   return RT_OK;
 }
@@ -1806,6 +1787,7 @@ int32_t rt_reduce_image(int32_t device, const void* multicast_ptr, const void* c
   }
   int32_t st = check_device(device);
   if (st != RT_OK) return st;
+  DeviceGuard guard;
   RT_CUDA(cudaSetDevice(device));
   if (n_floats == 0) return RT_OK;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(cuda_stream);
@@ -1831,21 +1813,26 @@ int32_t rt_tonemap_u8(int32_t device, const float* rgb, int32_t n_pixels, int32_
   if (!rgb || !out || n_pixels < 0) { set_error("bad argument"); return RT_ERR_INVALID_ARG; }
   int32_t st = check_device(device);
   if (st != RT_OK) return st;
+  DeviceGuard guard;
   RT_CUDA(cudaSetDevice(device));
   const size_t n = (size_t)n_pixels * 3;
   if (n == 0) return RT_OK;
-  float* d_in = nullptr;
-  uint8_t* d_out = nullptr;
-  RT_CUDA(cudaMalloc((void**)&d_in, n * 4));
-  RT_CUDA(cudaMalloc((void**)&d_out, n));
-  cudaError_t e = cudaMemcpy(d_in, rgb, n * 4, cudaMemcpyHostToDevice);
-  if (e == cudaSuccess) {
-    k_tonemap<<<592, 256>>>(d_in, (int)n, mode, d_out);
-    e = cudaMemcpy(out, d_out, n, cudaMemcpyDeviceToHost);
-  }
-  cudaFree(d_in);
-  cudaFree(d_out);
-  RT_CUDA(e);
+  WorkspaceLease lease;            // the workspace's own stream: no legacy default stream, no implicit device-wide sync
+  st = acquire_workspace(device, &lease.w);
+  if (st != RT_OK) return st;
+  cudaStream_t stream = lease.w->stream;
+  if (lease.w->pending) { RT_CUDA(cudaStreamWaitEvent(stream, lease.w->last_done, 0)); lease.w->pending = false; }
+  DevBuf b_in, b_out;
+  RT_CUDA(cudaMalloc(&b_in.p, n * 4));
+  RT_CUDA(cudaMalloc(&b_out.p, n));
+  int sm = 148;
+  cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, device);
+  const int grid = (int)std::min<size_t>((n + 255) / 256, (size_t)sm * 8);
+  RT_CUDA(cudaMemcpyAsync(b_in.p, rgb, n * 4, cudaMemcpyHostToDevice, stream));
+  k_tonemap<<<grid, 256, 0, stream>>>(static_cast<const float*>(b_in.p), (int)n, mode, static_cast<uint8_t*>(b_out.p));
+  RT_CUDA(cudaMemcpyAsync(out, b_out.p, n, cudaMemcpyDeviceToHost, stream));
+  RT_CUDA(cudaStreamSynchronize(stream));
+  RT_CUDA(cudaGetLastError());
   return RT_OK;
 }
 

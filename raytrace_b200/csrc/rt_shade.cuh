@@ -270,7 +270,15 @@ __device__ __forceinline__ bool shade_bounce(const DScene& sc, const DCamera& ca
       float pdf1 = hemi ? dot3(dir, s.n) * kInvPi : 0.25f * kInvPi;
       if (hemi && !(pdf1 > 0.f)) return false;                      // Ray.hs:197-198
       float pdf = cam.rem_prob * pdf1;
-      for (int k = 0; k < cam.n_targets; k++) pdf = fmaf(cam.targets[k].p, target_pdf(cam.targets[k], s.p, dir), pdf);
+      for (int k = 0; k < cam.n_targets; k++) {
+        // The target the direction was SAMPLED from is hit by construction (Ray.hs:199-202 finds it again with a
+        // parallelogram test): its pdf is t^2 / |crs . dir| with t = |lp - p|.  Re-deriving a, b in fp32 would reject a light
+        // point within a few ulp of an edge (1e-6 of the samples) and, with target probabilities summing to 1, leave
+        // pdf = 0 -> an infinite weight that poisons the pixel.
+        const float pk = k == choice ? __fdividef(l2, fabsf(dot3(ld3(cam.targets[k].crs), dir))) : target_pdf(cam.targets[k], s.p, dir);
+        pdf = fmaf(cam.targets[k].p, pk, pdf);
+      }
+      if (cam.n_targets && !(pdf > 0.f)) return false;              // direction no strategy can produce: no contribution
       f3 f = eval_texture(sc, T, mat.texture, s);
       float w = cam.n_targets ? __fdividef(pdf1, pdf) : 1.f;
       if (mat.kind == RT_MAT_LOMMEL_SEELIGER) {                     // Material.hs:56-61

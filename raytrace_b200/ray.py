@@ -160,25 +160,34 @@ class _PinnedBuffer:
             pass
 
 
-def _image_buffer(h: int, w: int) -> np.ndarray:
+def _image_buffer(h: int, w: int, pinned: bool = True) -> np.ndarray:
     """H×W×3 float32 result array over page-locked memory: rt_render's copy engine writes it directly (no staging
-    memcpy).  ``RT_B200_PINNED_OUT=0`` falls back to an ordinary pageable numpy array."""
-    import os
-    if os.environ.get("RT_B200_PINNED_OUT", "1") == "0":
+    memcpy).  ``pinned=False``: an ordinary pageable numpy array (the library then stages the copy)."""
+    if not pinned:
         return np.empty((h, w, 3), dtype=np.float32)
     return np.asarray(_PinnedBuffer(h * w * 3)).reshape(h, w, 3)
 
 
 
-class CompiledScene:
-    """A committed + uploaded scene; reusable across renders (the upload happens once)."""
+# RtOptions applied to every scene compiled without explicit ``options`` (sweep tools set this; the library itself reads
+# no environment variables)
+DEFAULT_OPTIONS: dict = {}
 
-    def __init__(self, world: Geometry, device: int = 0, noise_tables=None, upload: bool = True):
+
+class CompiledScene:
+    """A committed + uploaded scene; reusable across renders (the upload happens once).
+    ``options``: RtOptions fields by name (include/rt_b200.h), e.g. ``dict(bvh_reference=1)``."""
+
+    def __init__(self, world: Geometry, device: int = 0, noise_tables=None, upload: bool = True, options: Optional[dict] = None):
         if world.payload != "material":
             raise TypeError("raytrace: world must be a Geometry m Material (attach materials with <$)")
         self.handle = _ffi.SceneHandle()
         if noise_tables is not None:
             self.handle.set_noise_tables(*noise_tables)
+        opts = dict(DEFAULT_OPTIONS)
+        opts.update(options or {})
+        if opts:
+            self.handle.set_options(**opts)
         self.handle.commit(world)
         self.device = device
         if upload:
@@ -192,14 +201,14 @@ class CompiledScene:
         return _ffi.make_camera(settings, kind, c0, c1)
 
     def render(self, settings: CameraSettings, seed: StdGen, first_sample: int = 0,
-               n_samples: Optional[int] = None, want_sumsq: bool = False, want_stats: bool = False):
+               n_samples: Optional[int] = None, want_sumsq: bool = False, want_stats: bool = False, pinned_out: bool = True):
         L = _ffi.lib()
         self.handle.upload(self.device)
         cam = self.camera(settings)
         h, w = imageHeight(settings), settings.cs_imageWidth
         n = settings.cs_samplesPerPixel if n_samples is None else int(n_samples)
-        out = _image_buffer(h, w)
-        sq = _image_buffer(h, w) if want_sumsq else None
+        out = _image_buffer(h, w, pinned_out)
+        sq = _image_buffer(h, w, pinned_out) if want_sumsq else None
         stats = _ffi.RtStats()
         _ffi.check(L.rt_render(self.handle.handle, self.device, C.byref(cam), C.c_uint64(seed.seed),
                                C.c_uint64(first_sample), C.c_uint64(n),

@@ -191,14 +191,12 @@ def _cuboid_zoo(tree):
 
 
 @pytest.mark.parametrize("tree", [False, True], ids=["group", "bvhTree"])
-def test_aggregated_cuboids(built, tree, monkeypatch):
+def test_aggregated_cuboids(built, tree):
     """One slab test per cuboid (PRIM_FLAG_BOXHEAD) must pick the same face at the same distance as six independent
-    parallelogram tests (RT_B200_NO_BOXES=1, the reference's formulation) and converge to the oracle's image."""
+    parallelogram tests (RtOptions.aggregate_boxes = 0, the reference's formulation) and converge to the oracle's image."""
     s, world = _cuboid_zoo(tree)
     agg = CompiledScene(world)
-    monkeypatch.setenv("RT_B200_NO_BOXES", "1")
-    faces = CompiledScene(world)
-    monkeypatch.delenv("RT_B200_NO_BOXES")
+    faces = CompiledScene(world, options=dict(aggregate_boxes=0))
     probe_s = s.replace(cs_imageWidth=480)
     for t in (0.0, 0.5, 1.0):
         ia, ta = agg.probe_primary(probe_s, time=t)
@@ -224,7 +222,7 @@ TAIL_CASES = [
 
 
 @pytest.mark.parametrize("name,kw", TAIL_CASES, ids=[c[0] for c in TAIL_CASES])
-def test_tail_kernel_and_tiled_start_order_do_not_change_the_samples(built, name, kw, monkeypatch):
+def test_tail_kernel_and_tiled_start_order_do_not_change_the_samples(built, name, kw):
     """The tail kernel (lanes carry a path to its end and claim the next one) and the 8x4-tiled order in which camera
     paths start only reschedule work: the RNG is keyed by (pixel, sample, bounce), so every variant renders the same
     sample set and images differ by fp32 summation order alone.  Image sizes are deliberately not multiples of the
@@ -234,23 +232,23 @@ def test_tail_kernel_and_tiled_start_order_do_not_change_the_samples(built, name
     cs = CompiledScene(w)
     base, st0 = cs.render(s, rt.mkStdGen(seed), want_stats=True)
     assert np.isfinite(base).all()
-    # RT_B200_PRIMARY_CULL: camera rays that miss the world box end on the background inside k_raygen (pawn: the camera
+    # primary_cull: camera rays that miss the world box end on the background inside k_raygen (pawn: the camera
     # looks at the object from outside) or go through the queue like every other ray - the same paths either way
-    variants = [{"RT_B200_FINISH": "0"}, {"RT_B200_FINISH": "4294967295"}, {"RT_B200_FINISH": "300", "RT_B200_TAIL_BATCH": "1"},
-                {"RT_B200_TILE": "0"}, {"RT_B200_TILE": "1"}, {"RT_B200_FINISH_REFILL": "32", "RT_B200_FINISH": "100000"},
-                {"RT_B200_PRIMARY_CULL": "0"}, {"RT_B200_PRIMARY_CULL": "1"}, {"RT_B200_PRIMARY_CULL": "1", "RT_B200_FINISH": "4294967295"}]
+    ALL = 4294967295
+    variants = [dict(finish_max=0), dict(finish_max=ALL), dict(finish_max=300, tail_batch=1),
+                dict(tile=0), dict(tile=1), dict(finish_refill=32, finish_max=100000),
+                dict(primary_cull=0), dict(primary_cull=1), dict(primary_cull=1, finish_max=ALL),
+                dict(shade_sort=0), dict(shade_sort=1), dict(count_work=1)]
     for env in variants:
-        for k, v in env.items():
-            monkeypatch.setenv(k, v)
+        cs.handle.set_options(**env)
         img, st = cs.render(s, rt.mkStdGen(seed), want_stats=True)
-        for k in env:
-            monkeypatch.delenv(k)
+        cs.handle.set_options(**{k: None for k in env})
         assert st["samples"] == base.shape[0] * base.shape[1] * s.cs_samplesPerPixel
         assert st["rays"] == st0["rays"], env          # the same path segments, however they are scheduled
         assert np.allclose(img, base, rtol=2e-4, atol=2e-5), env
 
 
-def test_page_locked_output_buffers(built, monkeypatch):
+def test_page_locked_output_buffers(built):
     """rt_render writes page-locked caller buffers (rt_host_alloc) directly and pageable ones through its staging
     buffer; both hold the same image.  Freed buffers are recycled; foreign pointers are refused."""
     import ctypes as C
@@ -258,9 +256,7 @@ def test_page_locked_output_buffers(built, monkeypatch):
     s, w = scenes.readme_example(width=80, spp=8)
     cs = CompiledScene(w)
     pinned, sq = cs.render(s, rt.mkStdGen(5), want_sumsq=True)
-    monkeypatch.setenv("RT_B200_PINNED_OUT", "0")
-    pageable, sq2 = cs.render(s, rt.mkStdGen(5), want_sumsq=True)
-    monkeypatch.delenv("RT_B200_PINNED_OUT")
+    pageable, sq2 = cs.render(s, rt.mkStdGen(5), want_sumsq=True, pinned_out=False)
     assert np.allclose(pinned, pageable, rtol=2e-4, atol=2e-5) and np.allclose(sq, sq2, rtol=2e-4, atol=2e-5)
     keep = pinned.copy()
     del pinned, sq                     # buffers go back to the library's free list ...
@@ -304,11 +300,11 @@ def test_render_device_is_stream_ordered(built, name, kw):
     assert np.allclose((a / spp).cpu().numpy().reshape(want.shape), want, rtol=2e-4, atol=2e-5)
 
 
-def test_interior_queries_bounded_by_free_flight_distance(built, monkeypatch):
+def test_interior_queries_bounded_by_free_flight_distance(built):
     """A path that has just scattered inside the scene's only medium, whose boundary is a closed surface shared with the
     surfaces (pawn; a glass ball filled with fog), draws its free-flight distance BEFORE the traversal and bounds the
     surface query with it.  The counter RNG hands out the same number either way, so the event sequence - and the image
-    at equal seeds - is that of the unbounded queries (RT_B200_NO_INTERIOR_BOUND=1 at commit), up to summation order."""
+    at equal seeds - is that of the unbounded queries (RtOptions.interior_bound = 0 at commit), up to summation order."""
     from raytrace_b200 import V3, constantTexture, dielectric, isotropic, group, pureGeometry, constantMedium, sphere, lambertian
     ball = sphere((0, 0, -3), 1.5)
     fog_ball = group([pureGeometry(dielectric(1.5) << ball), isotropic(constantTexture(V3(0.9, 0.6, 0.3))) << constantMedium(3.0, ball),
@@ -318,9 +314,7 @@ def test_interior_queries_bounded_by_free_flight_distance(built, monkeypatch):
     for s, w, seed in ((s_ball, fog_ball, 7), (s_pawn, w_pawn, 55)):
         cs = CompiledScene(w)
         assert cs.info()["n_closed_media"] == 1
-        monkeypatch.setenv("RT_B200_NO_INTERIOR_BOUND", "1")
-        cs_ref = CompiledScene(w)
-        monkeypatch.delenv("RT_B200_NO_INTERIOR_BOUND")
+        cs_ref = CompiledScene(w, options=dict(interior_bound=0))
         assert cs_ref.info()["n_closed_media"] == 0
         a, st_a = cs.render(s, rt.mkStdGen(seed), want_stats=True)
         b, st_b = cs_ref.render(s, rt.mkStdGen(seed), want_stats=True)
@@ -330,13 +324,11 @@ def test_interior_queries_bounded_by_free_flight_distance(built, monkeypatch):
         assert close.mean() >= 0.999, close.mean()
         assert abs(a.mean() - b.mean()) <= 1e-3 * b.mean()
     # the tail kernel (trace_segment) takes the same shortcut
-    monkeypatch.setenv("RT_B200_FINISH", "4294967295")
-    c = CompiledScene(w_pawn).render(s_pawn, rt.mkStdGen(55))
-    monkeypatch.delenv("RT_B200_FINISH")
+    c = CompiledScene(w_pawn, options=dict(finish_max=4294967295)).render(s_pawn, rt.mkStdGen(55))
     assert np.isclose(c, a, rtol=2e-4, atol=2e-5).all(axis=2).mean() >= 0.999
 
 
-def test_primary_ray_culling_with_a_lens(built, monkeypatch):
+def test_primary_ray_culling_with_a_lens(built):
     """Culling is on only when the whole lens lies outside the world box; a thin-lens camera outside the box (defocus
     blur, pool smaller than one sample pass so that compacted tiles cross iteration boundaries) renders the same
     image as with the camera rays sent through the queue, and statistics count the culled rays as path segments."""
@@ -349,9 +341,9 @@ def test_primary_ray_culling_with_a_lens(built, monkeypatch):
     assert cs.info()["n_bvh_nodes"] > 0
     cs.handle.set_pool_size(3072)
     a, sa = cs.render(s, rt.mkStdGen(11), want_stats=True)
-    monkeypatch.setenv("RT_B200_PRIMARY_CULL", "0")
+    cs.handle.set_options(primary_cull=0)
     b, sb = cs.render(s, rt.mkStdGen(11), want_stats=True)
-    monkeypatch.delenv("RT_B200_PRIMARY_CULL")
+    cs.handle.set_options(primary_cull=None)
     assert sa["rays"] == sb["rays"] and sa["samples"] == sb["samples"]
     assert np.allclose(a, b, rtol=2e-4, atol=2e-5)
     assert sa["iterations"] <= sb["iterations"]         # culled paths never occupy pool slots

@@ -6,10 +6,11 @@ Gates (BASELINE.json north_star):
   2. hit distance t within 1e-5 relative;
   3. images agree statistically: mean luminance within 1 %, and no pixel fails a 4-sigma test
      (a pixel fails only if it fails again under an independent re-seed: SURVEY §7.3 item 4).
-Gates 1–2 are evaluated on WELL-CONDITIONED pixels (oracle.harness.probe_stable): where the pixel-centre ray
-runs exactly through a primitive edge or grazes a silhouette the reference's own answer is fp64 rounding noise
-(README scene: the mirror's left edge projects exactly onto pixel column 46, a = 2.2e-16); those pixels are
-counted and reported, and must stay a tiny fraction of the image."""
+Gates 1–2 count ALL pixels (oracle.harness.primary_gate): a pixel whose id differs from the oracle's centre answer
+passes only if the GPU's id is one the oracle itself returns at a ±2e-6 rad tilt of the same ray and the GPU's t is
+within 1e-5 of the oracle's t for that id (the pixel-centre ray runs through a primitive edge: README scene, the
+mirror's left edge projects exactly onto pixel column 46, a = 2.2e-16, and which side wins is fp64 rounding noise in
+the reference itself); raw, tie-explained and unexplained counts are printed."""
 import numpy as np
 import pytest
 
@@ -31,23 +32,62 @@ PROBE_CASES = [
 ]
 
 
+_ORACLE_PROBES = {}
+
+
+def _oracle_probe(name, kw):
+    """centre + four tilted oracle probes of a full-size config (cached: the SAH and reference-tree runs share it)"""
+    if name not in _ORACLE_PROBES:
+        ctor, _ = scenes.CONFIGS[name]
+        s, w = ctor(**kw)
+        _ORACLE_PROBES[name] = OracleScene(w).probe_tilted(s)
+    return _ORACLE_PROBES[name]
+
+
+@pytest.mark.parametrize("tree", ["sah", "reference"])
 @pytest.mark.parametrize("name,kw", PROBE_CASES, ids=[c[0] for c in PROBE_CASES])
-def test_primary_ray_id_and_distance(built, name, kw):
-    """Gates 1 and 2 at BASELINE.json's full image sizes."""
+def test_primary_ray_id_and_distance(built, name, kw, tree):
+    """Gates 1 and 2 at BASELINE.json's full image sizes, over ALL pixels (nothing masked): a pixel passes when the
+    GPU's id is one the oracle returns at the centre ray or at one of the four ±2e-6 rad tilts AND its t is within 1e-5
+    of the oracle's t for that id (oracle.harness.primary_gate); >= 99.99 % of all pixels must pass.  Run for the
+    default device tree (binned SAH, near-first traversal) and for the reference-shaped tree (RtOptions.bvh_reference:
+    the split policy north_star names, Geometry.hs:369-377)."""
+    from oracle.harness import primary_gate
     ctor, _ = scenes.CONFIGS[name]
     s, w = ctor(**kw)
-    ids, ts = CompiledScene(w).probe_primary(s)
-    oids, ots, stable = OracleScene(w).probe_stable(s)
-    assert stable.mean() > 0.99, stable.mean()
-    match = (ids == oids)[stable].mean()
-    raw = (ids == oids).mean()
-    both = stable & (ids == oids) & (oids != MISS)
-    rel = np.abs(ts[both] - ots[both]) / ots[both]
-    print(f"{name}: id match {match:.6f} (raw {raw:.6f}, ill-conditioned px {int((~stable).sum())}), max rel dt {rel.max():.2e}")
-    assert match >= 0.9999
-    assert raw >= 0.999
+    ids, ts = CompiledScene(w, options=dict(bvh_reference=int(tree == "reference"))).probe_primary(s)
+    ids5, ts5 = _oracle_probe(name, kw)
+    g = primary_gate(ids, ts, ids5, ts5)
+    _, _, stable = OracleScene.probe_stable(None, s, tilted=(ids5, ts5))
+    both = stable & (ids == ids5[0]) & (ids5[0] != MISS)
+    rel = np.abs(ts[both] - ts5[0][both]) / ts5[0][both]
+    print(f"{name}/{tree}: {g['pixels']} px, raw id match {g['raw_frac']:.6f} ({g['pixels'] - g['raw_match']} differ: "
+          f"{g['tie_explained']} tie-explained, {g['id_unexplained']} unexplained id, {g['t_failed']} t beyond 1e-5), "
+          f"pass {g['pass_frac']:.6f}; max rel dt on well-conditioned px {rel.max():.2e}")
+    assert g["pass_frac"] >= 0.9999, g
+    assert g["raw_frac"] >= 0.999
     assert rel.max() <= 1e-5
     assert np.isinf(ts[ids == MISS]).all()
+
+
+EQUAL_SEED_TREES = [("demo1", dict(width=96, spp=8)), ("demo2", dict(width=64, spp=8, depth=12)), ("pawn", dict(width=64, spp=8)),
+                    ("bunny_volume", dict(width=64, spp=4)), ("cornell", dict(width=48, spp=8))]
+
+
+@pytest.mark.parametrize("name,kw", EQUAL_SEED_TREES, ids=[c[0] for c in EQUAL_SEED_TREES])
+def test_reference_shaped_tree_renders_the_same_samples(built, name, kw):
+    """The device tree only changes HOW the closest hit is searched: the reference-shaped tree (bvhTree's object-median
+    policy, left-first evaluation order = storage order) and the default SAH tree give the same path segments and,
+    at equal seeds, the same image up to fp32 summation order (a knife-edge tie may flip a handful of paths)."""
+    ctor, seed = scenes.CONFIGS[name]
+    s, w = ctor(**kw)
+    a, sa = CompiledScene(w).render(s, rt.mkStdGen(seed), want_stats=True)
+    b, sb = CompiledScene(w, options=dict(bvh_reference=1)).render(s, rt.mkStdGen(seed), want_stats=True)
+    assert sa["samples"] == sb["samples"]
+    assert abs(int(sa["rays"]) - int(sb["rays"])) <= 2e-4 * sb["rays"] + 2
+    close = np.isclose(a, b, rtol=2e-4, atol=2e-5).all(axis=2)
+    assert close.mean() >= 0.998, close.mean()
+    assert abs(a.mean() - b.mean()) <= 2e-3 * b.mean()
 
 
 STAT_CASES = [
@@ -161,6 +201,28 @@ def test_moving_and_anisotropic(built):
     assert abs(luminance(img).mean() - luminance(ref).mean()) <= 0.01 * luminance(ref).mean()
     z = z_scores(img, sq, 128, ref, rsq, 128)
     assert (np.abs(z) > 4).mean() < 2e-3
+
+
+def test_redirect_probability_one(built):
+    """cs_redirectTargets whose probabilities sum to 1 (rem_prob = 0): the mixture pdf is the light pdf alone, so a
+    sampled light point that fp32 would place a few ulp outside the target must still get its analytic pdf - an
+    unguarded 0 makes the weight infinite and one NaN owns the pixel for the whole render.  Every pixel stays finite and
+    the image agrees with the oracle (same estimator in fp64, Ray.hs:187-206)."""
+    s, w = scenes.cornell_box(spp=512, width=64)
+    (p, q, s0, s1), = s.cs_redirectTargets
+    s = s.replace(cs_redirectTargets=[(1.0, q, s0, s1)], cs_maxRecursionDepth=8)
+    cs, ora = CompiledScene(w), OracleScene(w)
+    img, sq, st, ref, rsq, cnt = _render_both(cs, ora, s, 77)
+    assert np.isfinite(img).all() and np.isfinite(sq).all()
+    assert img.max() < 1e3
+    lg, lo = luminance(img).mean(), luminance(ref).mean()
+    print(f"redirect p=1: luminance gpu {lg:.5f} oracle {lo:.5f}")
+    assert abs(lg - lo) <= 0.02 * lo
+    z = z_scores(img, sq, 512, ref, rsq, 512)
+    assert (np.abs(z) > 4).mean() < 5e-3
+    # a long render: 2^22 redirect samples per pixel-row would have met the 1e-6 edge case many times over
+    big = cs.render(s.replace(cs_samplesPerPixel=4096, cs_imageWidth=48), rt.mkStdGen(3))
+    assert np.isfinite(big).all() and big.max() < 1e3
 
 
 def test_sphere_uv_known_answer_gpu(built):

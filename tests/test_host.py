@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol(built):
     assert declared == set(_ffi.EXPORTS), declared ^ set(_ffi.EXPORTS)
     for name in declared:
         assert hasattr(L, name), name
-    assert L.rt_version() == 0x00010000
+    assert L.rt_version() == 0x00020000
 
 
 def test_no_gpu_is_a_loud_error_not_a_fallback(built):
@@ -65,15 +65,14 @@ def test_product_never_imports_the_oracle():
 
 @pytest.mark.parametrize("policy", ["sah", "reference"])
 @pytest.mark.parametrize("name", ["readme", "cornell", "demo1", "demo2", "pawn", "bunny_volume"])
-def test_flattened_tree_matches_reference_evaluation_order(built, name, policy, monkeypatch):
+def test_flattened_tree_matches_reference_evaluation_order(built, name, policy):
     """bvhTree policy (Geometry.hs:369-377) + group order: the evaluation order the flattener records (it decides exact
     ties) must equal the oracle's evaluation-order leaf sequence (same split axis, same stable sort, same n div 2
     split) — whether the device tree is the default SAH tree (its own storage order) or the reference-shaped one
     (storage order = evaluation order)."""
-    monkeypatch.setenv("RT_B200_BVH", policy)
     ctor, _ = scenes.CONFIGS[name]
     s, w = ctor()
-    cs = CompiledScene(w, upload=False)
+    cs = CompiledScene(w, upload=False, options=dict(bvh_reference=int(policy == "reference")))
     nodes, canon = cs.handle.get_bvh()
     ora = OracleScene(w)
     order = ora.leaf_order()
@@ -310,3 +309,50 @@ def test_closed_boundary_detection(built):
     assert closed(sphere((0, 0, 0), 1.0)) == 1
     assert closed(sphere((0, 0, 0), -1.0)) == 0                         # the hollow-sphere trick: normals point inwards
     assert CompiledScene(scenes.demo2(width=8, spp=1)[1], upload=False).info()["n_media"] == 2        # two media: hint unused
+
+
+def test_options_struct_round_trip(built):
+    """RtOptions (include/rt_b200.h) is the library's only tuning interface - it reads no environment variables:
+    every field defaults to -1, set_options updates by name, unknown names are refused, and commit-time fields reach
+    the flattener (reference-shaped tree: storage order = evaluation order)."""
+    s, w = scenes.demo1(width=16, spp=1)
+    cs = CompiledScene(w, upload=False)
+    o = cs.handle.get_options()
+    assert set(o) == set(_ffi.RtOptions.NAMES) and all(v < 0 for v in o.values())
+    cs.handle.set_options(node_burst=2, pool=4096, sah_node_cost=0.5)
+    o = cs.handle.get_options()
+    assert o["node_burst"] == 2 and o["pool"] == 4096 and o["sah_node_cost"] == 0.5 and o["refill"] == -1
+    cs.handle.set_options(node_burst=None)
+    assert cs.handle.get_options()["node_burst"] == -1
+    cs.handle.set_pool_size(0)
+    assert cs.handle.get_options()["pool"] == -1
+    with pytest.raises(KeyError):
+        cs.handle.set_options(no_such_knob=1)
+    ref = CompiledScene(w, upload=False, options=dict(bvh_reference=1))
+    assert np.array_equal(ref.handle.get_bvh()[1], ref.handle.get_eval_order())
+    assert not np.array_equal(cs.handle.get_bvh()[1], cs.handle.get_eval_order())
+    for src in ("rt_api.cpp", "rt_flatten.cpp", "rt_kernels.cu", "rt_multi.cu"):
+        path = os.path.join(ROOT, "raytrace_b200", "csrc", src)
+        if os.path.exists(path):
+            assert "getenv" not in open(path).read(), src
+
+
+def test_primary_gate_counts_every_pixel():
+    """oracle.harness.primary_gate: raw matches, tie-explained pixels (id equals a TILTED oracle answer and t agrees with
+    the oracle's t for that id) and unexplained ones, over all pixels."""
+    from oracle.harness import primary_gate
+    MISS = 0xFFFFFFFF
+    ids5 = np.zeros((5, 1, 6), np.uint32)
+    ts5 = np.full((5, 1, 6), 2.0)
+    ids5[:, 0, 1] = [3, 3, 4, 3, 3]          # pixel 1: an edge - the tilts see primitive 4 as well
+    ts5[:, 0, 1] = [2.0, 2.0, 2.5, 2.0, 2.0]
+    ids5[:, 0, 5] = MISS
+    ts5[:, 0, 5] = np.inf
+    gpu_ids = np.array([[0, 4, 7, 0, 4, MISS]], np.uint32)
+    gpu_ts = np.array([[2.0, 2.5, 2.0, 2.0001, 2.0, np.inf]], np.float32)
+    g = primary_gate(gpu_ids, gpu_ts, ids5, ts5)
+    assert g["pixels"] == 6 and g["raw_match"] == 3           # pixels 0, 3, 5
+    assert g["tie_explained"] == 1                            # pixel 1
+    assert g["id_unexplained"] == 2                           # pixels 2 and 4: ids the oracle never returns there
+    assert g["t_failed"] == 1                                 # pixel 3: right id, t off by 5e-5
+    assert g["unexplained"] == 3 and abs(g["pass_frac"] - 0.5) < 1e-12

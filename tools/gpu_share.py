@@ -1,6 +1,6 @@
 """Latency of ONE GPU's share of a sample-sharded render (GPU only): renders spp/G samples of a scene on one device under
-different tail settings (RT_B200_FINISH = path count at which k_finish takes over, RT_B200_TAIL_BATCH = iterations per host
-round trip in the tail, RT_B200_FINISH_REFILL) and prints the device-timed total, the time inside the iteration kernels and
+different tail settings (finish_max = path count at which k_finish takes over, tail_batch = iterations per host
+round trip in the tail, finish_refill) and prints the device-timed total, the time inside the iteration kernels and
 the rest (k_finish, host round trips, launch gaps).  The knobs are read per render, so one process sweeps them all.
 
 usage: python tools/gpu_share.py [scene] [shares, e.g. 1,2,4,8]"""
@@ -16,20 +16,18 @@ KW = {"pawn": dict(width=1920, aspect=16 / 9, spp=64), "bunny_volume": dict(spp=
 ctor, seed = scenes.CONFIGS[name]
 s, w = ctor(**KW.get(name, {}))
 cs = CompiledScene(w)
-KNOBS = ("RT_B200_FINISH", "RT_B200_TAIL_BATCH", "RT_B200_FINISH_REFILL")
+KNOBS = ("finish_max", "tail_batch", "finish_refill")
 sweeps = [{}]
 if os.environ.get("SHARE_SWEEP", "full") == "quick":
-    sweeps += [{"RT_B200_FINISH": str(v)} for v in (0, 262144, 1048576, 4194304)]
+    sweeps += [{"finish_max": v} for v in (0, 262144, 1048576, 4194304)]
 else:
-    sweeps += [{"RT_B200_FINISH": str(v)} for v in (0, 262144, 1048576, 2097152, 8388608, 16777216)]
-    sweeps += [{"RT_B200_TAIL_BATCH": str(v)} for v in (2, 3, 6, 8)]
-    sweeps += [{"RT_B200_FINISH_REFILL": str(v)} for v in (1, 12, 32)]
+    sweeps += [{"finish_max": v} for v in (0, 262144, 1048576, 2097152, 8388608, 16777216)]
+    sweeps += [{"tail_batch": v} for v in (2, 3, 6, 8)]
+    sweeps += [{"finish_refill": v} for v in (1, 12, 32)]
 for g in shares:
     n = max(1, s.cs_samplesPerPixel // g)
     for cfg in sweeps:
-        for k in KNOBS:
-            os.environ.pop(k, None)
-        os.environ.update(cfg)
+        cs.handle.set_options(**{k: cfg.get(k) for k in KNOBS})
         best = None
         for rep in range(6):
             img, st = cs.render(s, mkStdGen(seed + rep), n_samples=n, want_stats=True)
