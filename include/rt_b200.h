@@ -304,6 +304,34 @@ int32_t rt_probe_surface(RtScene* scene, int32_t device, const RtCamera* cam, do
 int32_t rt_reduce_image(int32_t device, const void* multicast_ptr, const void* const* peer_ptrs, int32_t n_peers,
                         float* d_out, uint64_t n_floats, float scale, void* cuda_stream);
 
+/*
+ * Multi-GPU rendering inside the library: the reference's `raytrace` is ONE call that uses the whole machine
+ * (Ray.hs:121, parallel array :238).  A context owns a set of GPUs in one process; rt_render_multi splits the samples per
+ * pixel across them (the sample set does not depend on the GPU count), renders every share on its own device
+ * (one host thread and stream per device, the committed scene uploaded once per device) and assembles the image with a
+ * reduce-scatter over NVLink: every device reduces ITS 1/G slice of the image through the NVSwitch multicast mapping
+ * (multimem.ld_reduce; cuMemCreate + cuMulticast*, resolved at run time), normalises it by 1/spp (Ray.hs:232) and copies
+ * that slice straight into the caller's host image.  Falls back to peer loads, then to a gather on the first device,
+ * when the fabric has no multicast / no peer access (RtContextInfo.reduce_mode says which) - always on the GPUs.
+ */
+typedef struct RtContext RtContext;
+typedef struct RtContextInfo {
+  int32_t n_devices;
+  int32_t reduce_mode;      /* 0 = single device (no reduce), 1 = NVSwitch multicast, 2 = peer loads, 3 = gather on the first device;
+                               decided at the first render */
+  int32_t devices[16];
+  char reduce_note[160];    /* why multicast was not used, if it was not */
+} RtContextInfo;
+/* devices == NULL / n_devices == 0: every visible sm_100 device.  A device may be listed more than once (each entry is a
+ * share with its own host thread and stream; the reduce then uses peer loads) - how a one-GPU box exercises the G > 1 path. */
+int32_t rt_context_create(const int32_t* devices, int32_t n_devices, RtContext** out);
+int32_t rt_context_destroy(RtContext* ctx);
+int32_t rt_context_info(const RtContext* ctx, RtContextInfo* info);
+/* Same result as rt_render(scene, dev, cam, seed, 0, cam->samples_per_pixel, ...) up to fp32 summation order.
+ * stats (nullable): sums over the devices; times are the maximum over the devices. */
+int32_t rt_render_multi(RtContext* ctx, RtScene* scene, const RtCamera* cam, uint64_t seed, float* rgb_out,
+                        float* rgb_sumsq_out /*nullable*/, RtStats* stats /*nullable*/);
+
 /* Optional page-locked host buffers for rt_render's outputs.  rt_render accepts ANY host pointer; when rgb_out (and
  * rgb_sumsq_out) point into page-locked memory - from rt_host_alloc, cudaMallocHost or cudaHostRegister - the image is
  * DMA-copied straight into them, otherwise it goes through the library's pinned staging buffer plus one host memcpy

@@ -16,7 +16,7 @@ from .geometry import (M44, Geometry, Mesh, boundingBox, bvhNode, bvhTree, const
                        transformVertices, translate, triangle, triangleMesh, withMaterial)
 from .material import (Material, anisotropic, dielectric, isotropic, lambertian, lightSource,
                        lommelSeeliger, metal, mirror, pitchBlack, transparent)
-from .ray import (CameraSettings, CompiledScene, Ray, StdGen, defaultCameraSettings,
+from .ray import (CameraSettings, CompiledScene, Ray, RenderContext, StdGen, defaultCameraSettings,
                   imageHeight, mkStdGen, raytrace, readImage, writeImage, writeImageSqrt)
 from .texture import (Texture, checkerTexture, constantTexture, imageTexture, marbleTexture,
                       noiseTexture, solidTexture, uvTexture)

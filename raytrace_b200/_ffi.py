@@ -99,6 +99,16 @@ class RtSceneInfo(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class RtContextInfo(C.Structure):
+    _fields_ = [("n_devices", C.c_int32), ("reduce_mode", C.c_int32), ("devices", C.c_int32 * 16), ("reduce_note", C.c_char * 160)]
+
+    MODES = {0: "single", 1: "multicast", 2: "peer", 3: "gather"}
+
+    def as_dict(self):
+        return {"n_devices": self.n_devices, "reduce_mode": self.MODES.get(self.reduce_mode, str(self.reduce_mode)),
+                "devices": list(self.devices[: self.n_devices]), "reduce_note": self.reduce_note.decode("utf-8", "replace")}
+
+
 class RtOptions(C.Structure):
     """include/rt_b200.h RtOptions: negative = library default."""
     _fields_ = [("bvh_reference", C.c_int32), ("leaf_max", C.c_int32), ("collapse", C.c_int32),
@@ -125,6 +135,7 @@ EXPORTS = [
     "rt_probe_primary", "rt_probe_surface", "rt_set_pool_size", "rt_tonemap_u8",
     "rt_obj_parse", "rt_mesh_sizes", "rt_mesh_data", "rt_mesh_destroy", "rt_host_alloc", "rt_host_free", "rt_reduce_image",
     "rt_options_init", "rt_scene_set_options", "rt_scene_get_options",
+    "rt_context_create", "rt_context_destroy", "rt_context_info", "rt_render_multi",
 ]
 
 _lib: Optional[C.CDLL] = None
@@ -166,6 +177,10 @@ def lib() -> C.CDLL:
                                    C.POINTER(C.c_float)]
     L.rt_probe_surface.argtypes = [vp, C.c_int32, C.POINTER(RtCamera), C.c_double, C.POINTER(C.c_float)]
     L.rt_set_pool_size.argtypes = [vp, C.c_uint32]
+    L.rt_context_create.argtypes = [C.POINTER(C.c_int32), C.c_int32, C.POINTER(vp)]
+    L.rt_context_destroy.argtypes = [vp]
+    L.rt_context_info.argtypes = [vp, C.POINTER(RtContextInfo)]
+    L.rt_render_multi.argtypes = [vp, vp, C.POINTER(RtCamera), C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(RtStats)]
     L.rt_options_init.argtypes = [C.POINTER(RtOptions)]
     L.rt_scene_set_options.argtypes = [vp, C.POINTER(RtOptions)]
     L.rt_scene_get_options.argtypes = [vp, C.POINTER(RtOptions)]

@@ -1837,3 +1837,5 @@ int32_t rt_tonemap_u8(int32_t device, const float* rgb, int32_t n_pixels, int32_
 }
 
 }  // extern "C"
+
+#include "rt_multi.cuh"   // rt_context_* / rt_render_multi (uses the static helpers above)

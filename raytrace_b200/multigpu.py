@@ -117,6 +117,20 @@ class ImageReducer:
         return self.out[: self.n]
 
 
+_REDUCERS: dict = {}
+
+
+def cached_reducer(n_floats: int, device, group=None) -> ImageReducer:
+    """One ImageReducer per (size, device, group): its symmetric-memory buffers are a collective allocation, and a rank
+    must not free them while the root may still be reading them through the multicast / peer mapping - so they live as
+    long as the process (what bench.py does by hand)."""
+    import torch
+    key = (int(n_floats), str(torch.device(device)), id(group))
+    if key not in _REDUCERS:
+        _REDUCERS[key] = ImageReducer(n_floats, device, group=group)
+    return _REDUCERS[key]
+
+
 def render_sharded(render_range: Callable[[int, int, "object"], None], acc, spp: int, group=None, dst: int = 0):
     """Generic driver: ``render_range(first, count, acc)`` must ADD the un-normalised sums of global samples
     [first, first + count) into ``acc``; the result lands on rank ``dst`` divided by spp."""
@@ -148,7 +162,7 @@ def raytrace_distributed(settings, world_geometry, seed, compiled=None, device: 
     spp = settings.cs_samplesPerPixel
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
-    red = ImageReducer(h * w * 3, dev, group=group)
+    red = cached_reducer(h * w * 3, dev, group=group)
     acc = red.acc()
     acc.zero_()
     first, count = split_samples(spp, world, rank)

@@ -261,9 +261,68 @@ class CompiledScene:
         return out
 
 
-def raytrace(settings: CameraSettings, world: Geometry, seed: StdGen, device: int = 0) -> np.ndarray:
-    """``raytrace :: CameraSettings -> Geometry m Material -> StdGen -> Matrix D Color`` (Ray.hs:121)."""
-    return CompiledScene(world, device=device).render(settings, seed)
+class RenderContext:
+    """A set of GPUs driven by ONE process (rt_context_create): ``render`` is rt_render_multi - samples per pixel split
+    across the devices, reduce-scatter of the image over NVLink inside the library, every device copying its slice of
+    the result to the host.  ``devices=None``: every visible sm_100 device."""
+
+    def __init__(self, devices: Optional[Sequence[int]] = None):
+        self._L = _ffi.lib()
+        self._h = C.c_void_p()
+        if devices:
+            arr = (C.c_int32 * len(devices))(*[int(d) for d in devices])
+            _ffi.check(self._L.rt_context_create(arr, len(devices), C.byref(self._h)))
+        else:
+            _ffi.check(self._L.rt_context_create(None, 0, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            self._L.rt_context_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self) -> dict:
+        i = _ffi.RtContextInfo()
+        _ffi.check(self._L.rt_context_info(self._h, C.byref(i)))
+        return i.as_dict()
+
+    def render(self, scene: "CompiledScene", settings: CameraSettings, seed: StdGen, want_sumsq: bool = False,
+               want_stats: bool = False, pinned_out: bool = True):
+        cam = scene.camera(settings)
+        h, w = imageHeight(settings), settings.cs_imageWidth
+        out = _image_buffer(h, w, pinned_out)
+        sq = _image_buffer(h, w, pinned_out) if want_sumsq else None
+        stats = _ffi.RtStats() if want_stats else None
+        _ffi.check(self._L.rt_render_multi(self._h, scene.handle.handle, C.byref(cam), C.c_uint64(seed.seed),
+                                           out.ctypes.data_as(C.POINTER(C.c_float)),
+                                           sq.ctypes.data_as(C.POINTER(C.c_float)) if sq is not None else None,
+                                           C.byref(stats) if want_stats else None))
+        res = [out]
+        if want_sumsq:
+            res.append(sq)
+        if want_stats:
+            res.append(stats.as_dict())
+        return res[0] if len(res) == 1 else tuple(res)
+
+
+_ALL_GPUS: Optional[RenderContext] = None
+
+
+def raytrace(settings: CameraSettings, world: Geometry, seed: StdGen, device: Optional[int] = None) -> np.ndarray:
+    """``raytrace :: CameraSettings -> Geometry m Material -> StdGen -> Matrix D Color`` (Ray.hs:121).
+    Like the reference - one call, the whole machine - the render uses EVERY visible GPU (rt_render_multi; one GPU when
+    only one is visible); ``device=k`` pins it to GPU k (rt_render)."""
+    if device is not None:
+        return CompiledScene(world, device=device).render(settings, seed)
+    global _ALL_GPUS
+    if _ALL_GPUS is None:
+        _ALL_GPUS = RenderContext()
+    return _ALL_GPUS.render(CompiledScene(world, upload=False), settings, seed)
 
 
 # ---- image IO (Ray.hs:241-260) ---------------------------------------------------------------------

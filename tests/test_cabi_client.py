@@ -11,14 +11,23 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.fixture(scope="module")
-def client(built, tmp_path_factory):
-    exe = str(tmp_path_factory.mktemp("cabi") / "readme_scene")
+def _compile(tmp_path_factory, name):
+    exe = str(tmp_path_factory.mktemp("cabi") / name)
     libdir = os.path.join(ROOT, "raytrace_b200")
     subprocess.check_call(["gcc", "-std=c11", "-O2", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
-                           os.path.join(ROOT, "tests", "cabi", "readme_scene.c"), "-o", exe,
+                           os.path.join(ROOT, "tests", "cabi", name + ".c"), "-o", exe,
                            "-L", libdir, "-lrt_b200", "-lm", f"-Wl,-rpath,{libdir}"])
     return exe
+
+
+@pytest.fixture(scope="module")
+def client(built, tmp_path_factory):
+    return _compile(tmp_path_factory, "readme_scene")
+
+
+@pytest.fixture(scope="module")
+def multi_client(built, tmp_path_factory):
+    return _compile(tmp_path_factory, "cornell_multi")
 
 
 def _gpu_visible():
@@ -48,3 +57,22 @@ def test_c_client_matches_python_front_end(client):
     img = rt.raytrace(s, w, rt.mkStdGen(100))
     # same scene, same seed, same sample set: equal up to fp32 summation order
     assert abs(mean - float(np.mean(img, dtype=np.float64))) < 2e-5 * mean, (mean, img.mean())
+
+
+def test_multi_gpu_c_client_fails_loudly_without_gpu(multi_client):
+    if _gpu_visible():
+        pytest.skip("a GPU is visible")
+    r = subprocess.run([multi_client, "32", "4"], capture_output=True, text=True)
+    assert "committed: 18 prims" in r.stdout
+    assert r.returncode == 7 and "rt_context_create" in r.stderr and "no CPU fallback" in r.stderr
+
+
+@pytest.mark.gpu
+def test_multi_gpu_c_client_matches_single_gpu_render(multi_client):
+    """rt_context_create(NULL, 0) + rt_render_multi from plain C, one process, ALL visible GPUs (one on the driver's test
+    box; tools/gpu_multi_check.sh runs the same binary on 2 / 8 GPUs): same image as rt_render on device 0 up to fp32
+    summation order, same ray count, sum of squares included."""
+    r = subprocess.run([multi_client, "120", "40"], capture_output=True, text=True)
+    print(r.stdout.strip())
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    assert "pixels beyond tolerance 0" in r.stdout
