@@ -222,7 +222,8 @@ typedef struct RtOptions {
   int32_t timing;            /* 0: no per-kernel events even when stats are requested (default 1) */
   int32_t count_work;        /* 1: run the instrumented traversal kernel and fill RtStats.node_pairs ... (default 0) */
   int32_t debug_sync;        /* 1: synchronise after every launch and name a faulting kernel on stderr */
-  int32_t reserved[8];
+  int32_t raygen_block;      /* culling k_raygen: consecutive samples of one pixel owned by a thread (default 8; 1 = one atomic triple per culled sample) */
+  int32_t reserved[7];
 } RtOptions;
 
 /* library */

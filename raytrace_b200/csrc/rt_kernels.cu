@@ -96,6 +96,12 @@ struct RenderArgs {
   uint32_t tile;                  // camera paths start in 8x4 pixel tiles (1) or in row-major pixel order (0)
   uint32_t cull;                  // k_raygen: camera rays that miss the world box end there (never queued)
   float world_lo[3], world_hi[3];
+  // work-item order: with kblock = K > 1, K consecutive items are K consecutive samples of ONE pixel (a k_raygen thread owns
+  // them and sums the background of its culled camera rays in registers: one atomic triple per pixel instead of one per
+  // sample); kblock = 1: an item is (sample pass, pixel).  A bijection onto (pixel, sample) either way - the RNG is keyed by
+  // (pixel, global sample), so the sample set does not depend on it.
+  uint32_t kblock, ktail;               // K; n_samples % K
+  unsigned long long kfull_items;       // (n_samples / K) * K * n_pixels: items before the ragged last block of samples
 };
 
 // Closes iteration k and prepares iteration k+1 (single thread: the last k_shade block, or k_begin for k = 0).
@@ -153,8 +159,22 @@ __device__ __forceinline__ uint32_t tiled_pixel(uint32_t p, uint32_t W, uint32_t
 struct NewPath { RayT ray; uint32_t pixel; uint32_t sample_lo; };
 // work item → camera path (Ray.hs:157-172,229): item = local sample index * n_pixels + position in the pass
 __device__ __forceinline__ NewPath new_camera_path(const RenderArgs& A, unsigned long long item) {
-  const unsigned long long s_local = item / A.n_pixels;
-  uint32_t pixel = (uint32_t)(item - s_local * A.n_pixels);
+  unsigned long long s_local;
+  uint32_t pixel;
+  if (A.kblock <= 1u) {
+    s_local = item / A.n_pixels;
+    pixel = (uint32_t)(item - s_local * A.n_pixels);
+  } else if (item < A.kfull_items) {
+    const uint32_t per_blk = A.kblock * A.n_pixels;                   // < 2^32: checked on the host
+    const unsigned long long blk = item / per_blk;
+    const uint32_t rem = (uint32_t)(item - blk * per_blk);
+    pixel = rem / A.kblock;
+    s_local = blk * A.kblock + (rem - pixel * A.kblock);
+  } else {                                                           // last block of samples: ktail = n_samples % K per pixel
+    const uint32_t idx = (uint32_t)(item - A.kfull_items);
+    pixel = idx / A.ktail;
+    s_local = A.kfull_items / A.n_pixels + (idx - pixel * A.ktail);
+  }
   if (A.tile) pixel = tiled_pixel(pixel, (uint32_t)A.cam.W, (uint32_t)A.cam.H);
   const unsigned long long sample = A.first_sample + s_local;
   const uint4 r0 = rng4(A.key, pixel, sample, 0, RNG_RAYGEN);
@@ -192,55 +212,75 @@ __global__ void __launch_bounds__(kRaygenBlock) k_raygen(Ctl* __restrict__ ctl, 
   const uint32_t fill = n > lo ? n - lo : 0u, lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   const float4 wlo = make_float4(A.world_lo[0], A.world_lo[1], A.world_lo[2], 0.f), whi = make_float4(A.world_hi[0], A.world_hi[1], A.world_hi[2], 0.f);
   unsigned int culled = 0;
-  for (uint32_t base = blockIdx.x * blockDim.x; base < fill; base += gridDim.x * blockDim.x) {   // uniform per block
-    const uint32_t t = base + threadIdx.x;
-    bool keep = false;
-    NewPath np{};
-    if (t < fill) {
-      np = new_camera_path(A, item0 + t);
-      f3 inv;
-      inv.x = fabsf(np.ray.d.x) > 1e-30f ? __frcp_rn(np.ray.d.x) : copysignf(1e30f, np.ray.d.x);
-      inv.y = fabsf(np.ray.d.y) > 1e-30f ? __frcp_rn(np.ray.d.y) : copysignf(1e30f, np.ray.d.y);
-      inv.z = fabsf(np.ray.d.z) > 1e-30f ? __frcp_rn(np.ray.d.z) : copysignf(1e30f, np.ray.d.z);
-      float tn;
-      keep = box_hit(wlo, whi, inv, np.ray.o * inv, 1e-4f, __int_as_float(0x7f800000), tn);
-      if (!keep) {   // miss: emitted = background, path ends (throughput is still 1)
-        const f3 c = background(A.cam, np.ray.d);
-        culled++;
-        if (c.x != 0.f || c.y != 0.f || c.z != 0.f) {
-          float* s = A.sum + 3 * (size_t)np.pixel;
-          atomicAdd(s, c.x);
-          atomicAdd(s + 1, c.y);
-          atomicAdd(s + 2, c.z);
-          if (A.sumsq) {
-            float* s2 = A.sumsq + 3 * (size_t)np.pixel;
-            atomicAdd(s2, c.x * c.x);
-            atomicAdd(s2 + 1, c.y * c.y);
-            atomicAdd(s2 + 2, c.z * c.z);
-          }
-        }
+  // A thread owns K = A.kblock consecutive work items (K samples of one pixel, unless its run straddles a pixel boundary
+  // because this iteration's first item is not a multiple of K): the background radiance of its culled rays is summed in
+  // registers and flushed with ONE atomic triple when the pixel changes.  Per round k the block compacts its survivors as
+  // before (ballot ranks, one atomic per 256 items), so queue order stays "256-pixel tile after tile".
+  const uint32_t K = max(A.kblock, 1u);
+  const uint32_t chunks = (fill + K - 1u) / K;
+  uint32_t acc_pixel = kNone;
+  f3 acc = mk3(0.f, 0.f, 0.f), acc2 = mk3(0.f, 0.f, 0.f);
+  auto flush = [&]() {
+    if (acc_pixel != kNone && (acc.x != 0.f || acc.y != 0.f || acc.z != 0.f)) {
+      float* sp = A.sum + 3 * (size_t)acc_pixel;
+      atomicAdd(sp, acc.x);
+      atomicAdd(sp + 1, acc.y);
+      atomicAdd(sp + 2, acc.z);
+      if (A.sumsq) {
+        float* s2 = A.sumsq + 3 * (size_t)acc_pixel;
+        atomicAdd(s2, acc2.x);
+        atomicAdd(s2 + 1, acc2.y);
+        atomicAdd(s2 + 2, acc2.z);
       }
     }
-    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
-    if (lane == 0) s_cnt[warp] = __popc(mask);
-    __syncthreads();
-    uint32_t before = 0, total = 0;
+    acc = mk3(0.f, 0.f, 0.f);
+    acc2 = mk3(0.f, 0.f, 0.f);
+  };
+  for (uint32_t cbase = blockIdx.x * blockDim.x; cbase < chunks; cbase += gridDim.x * blockDim.x) {   // uniform per block
+    const uint32_t c = cbase + threadIdx.x;
+    for (uint32_t k = 0; k < K; k++) {
+      const uint32_t t = c * K + k;
+      bool keep = false;
+      NewPath np{};
+      if (c < chunks && t < fill) {
+        np = new_camera_path(A, item0 + t);
+        f3 inv;
+        inv.x = fabsf(np.ray.d.x) > 1e-30f ? __frcp_rn(np.ray.d.x) : copysignf(1e30f, np.ray.d.x);
+        inv.y = fabsf(np.ray.d.y) > 1e-30f ? __frcp_rn(np.ray.d.y) : copysignf(1e30f, np.ray.d.y);
+        inv.z = fabsf(np.ray.d.z) > 1e-30f ? __frcp_rn(np.ray.d.z) : copysignf(1e30f, np.ray.d.z);
+        float tn;
+        keep = box_hit(wlo, whi, inv, np.ray.o * inv, 1e-4f, __int_as_float(0x7f800000), tn);
+        if (!keep) {   // miss: emitted = background, path ends (throughput is still 1)
+          const f3 cbg = background(A.cam, np.ray.d);
+          culled++;
+          if (np.pixel != acc_pixel) { flush(); acc_pixel = np.pixel; }
+          acc = acc + cbg;
+          acc2 = acc2 + cbg * cbg;
+        }
+      }
+      const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
+      if (lane == 0) s_cnt[warp] = __popc(mask);
+      __syncthreads();
+      uint32_t before = 0, total = 0;
 #pragma unroll
-    for (int w = 0; w < kRaygenBlock / 32; w++) {
-      const uint32_t c = s_cnt[w];
-      before += (w < (int)warp) ? c : 0u;
-      total += c;
+      for (int w = 0; w < kRaygenBlock / 32; w++) {
+        const uint32_t cw = s_cnt[w];
+        before += (w < (int)warp) ? cw : 0u;
+        total += cw;
+      }
+      if (threadIdx.x == 0 && total) s_base = atomicAdd(&ctl->n_gen, total);
+      __syncthreads();
+      if (keep) {
+        const uint32_t slot = lo + s_base + before + __popc(mask & ((1u << lane) - 1u));
+        q.o[slot] = make_float4(np.ray.o.x, np.ray.o.y, np.ray.o.z, np.ray.time);
+        q.d[slot] = make_float4(np.ray.d.x, np.ray.d.y, np.ray.d.z, __uint_as_float(kNone));
+        q.thr[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(np.pixel));
+        q.meta[slot] = make_uint2(np.sample_lo, 0u);
+      }
+      __syncthreads();   // s_cnt / s_base are reused by the next round
     }
-    if (threadIdx.x == 0 && total) s_base = atomicAdd(&ctl->n_gen, total);
-    __syncthreads();
-    if (keep) {
-      const uint32_t slot = lo + s_base + before + __popc(mask & ((1u << lane) - 1u));
-      q.o[slot] = make_float4(np.ray.o.x, np.ray.o.y, np.ray.o.z, np.ray.time);
-      q.d[slot] = make_float4(np.ray.d.x, np.ray.d.y, np.ray.d.z, __uint_as_float(kNone));
-      q.thr[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(np.pixel));
-      q.meta[slot] = make_uint2(np.sample_lo, 0u);
-    }
-    __syncthreads();   // s_cnt / s_base are reused by the next tile
+    flush();
+    acc_pixel = kNone;
   }
   for (int o = 16; o > 0; o >>= 1) culled += __shfl_down_sync(0xFFFFFFFFu, culled, o);
   if (lane == 0 && culled) atomicAdd(&ctl->culled, culled);
@@ -1375,6 +1415,15 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   }
   if (O.primary_cull >= 0) A.cull = (O.primary_cull && dev.d.has_world_box && !dev.has_flat) ? 1u : 0u;
   for (int k = 0; k < 3; k++) { A.world_lo[k] = dev.d.world_lo[k]; A.world_hi[k] = dev.d.world_hi[k]; }
+  // culling iterations: a k_raygen thread owns K consecutive samples of a pixel (one background atomic triple per K samples)
+  A.kblock = 1u;
+  if (A.cull) {
+    A.kblock = 8u;
+    if (O.raygen_block >= 0) A.kblock = (uint32_t)std::min(64, std::max(1, (int)O.raygen_block));
+    while (A.kblock > 1u && (unsigned long long)A.kblock * n_pixels >= 0xFFFFFFFFull) A.kblock /= 2u;
+  }
+  A.ktail = (uint32_t)(n_samples % A.kblock);
+  A.kfull_items = (n_samples / A.kblock) * A.kblock * (unsigned long long)n_pixels;
   int tail_batch = 3;                // iterations (each followed by a k_finish check) per host round trip once all paths have started
   if (O.tail_batch >= 0) tail_batch = std::min(64, std::max(1, (int)O.tail_batch));
   if (O.node_burst >= 0) A.node_burst = std::min(8, std::max(1, (int)O.node_burst));

@@ -238,7 +238,8 @@ def test_tail_kernel_and_tiled_start_order_do_not_change_the_samples(built, name
     variants = [dict(finish_max=0), dict(finish_max=ALL), dict(finish_max=300, tail_batch=1),
                 dict(tile=0), dict(tile=1), dict(finish_refill=32, finish_max=100000),
                 dict(primary_cull=0), dict(primary_cull=1), dict(primary_cull=1, finish_max=ALL),
-                dict(shade_sort=0), dict(shade_sort=1), dict(count_work=1)]
+                dict(shade_sort=0), dict(shade_sort=1), dict(count_work=1),
+                dict(primary_cull=1, raygen_block=1), dict(primary_cull=1, raygen_block=3), dict(primary_cull=1, raygen_block=5, pool=2048)]
     for env in variants:
         cs.handle.set_options(**env)
         img, st = cs.render(s, rt.mkStdGen(seed), want_stats=True)
