@@ -185,7 +185,8 @@ typedef struct RtSceneInfo {
   uint64_t device_bytes;      /* scene bytes resident in HBM */
   uint32_t n_closed_media;    /* media whose boundary is a shared, closed, outward-oriented surface (interior queries
                                * are then bounded by the free-flight distance) */
-  uint32_t reserved;
+  uint32_t n_moving_list;     /* moving / instanced primitives kept outside the tree in a short list scanned once per segment
+                               * (RtOptions.split_moving): the static primitives then run the kernel without the transform branch */
 } RtSceneInfo;
 
 typedef struct RtScene RtScene;

@@ -295,7 +295,7 @@ int32_t rt_scene_info(const RtScene* sp, RtSceneInfo* info) {
   info->device_bytes = f.bytes();
   info->n_closed_media = 0;
   for (uint32_t k = 0; k < f.n_media; k++) info->n_closed_media += f.media[k].closed ? 1u : 0u;
-  info->reserved = 0;
+  info->n_moving_list = f.moving_count;
   return RT_OK;
 }
 

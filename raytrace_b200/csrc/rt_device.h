@@ -57,6 +57,12 @@ constexpr uint32_t PRIM_FLAG_BOXTAIL = 64u; // faces 1..5 of an aggregated cuboi
 // scene feature bits: which code the traversal kernel must contain (template specialisation)
 constexpr uint32_t TF_SPHERE = 1u, TF_PLANAR = 2u, TF_MOVING = 4u, TF_MEDIA = 8u;
 constexpr uint32_t TF_BOX = 16u;   // some cuboids are aggregated (PRIM_FLAG_BOXHEAD / BOXTAIL occur)
+// The scene's few moving / instanced primitives are kept OUT of the tree, in the short list [moving_first, moving_first +
+// moving_count) that every segment scans once: the thousands of static primitives then run the traversal code without the
+// per-primitive transform branch (demo2: one moving sphere used to put all 3407 primitives on the catch-all kernel).
+// TF_MOVING (moving primitives inside the tree, transform branch in every primitive test) remains the fallback.
+constexpr uint32_t TF_MOVLIST = 32u;
+constexpr uint32_t kMaxMovingList = 32u;
 
 struct DNode {  // 32 bytes
   float lo[3];
@@ -143,6 +149,7 @@ struct DScene {     // device pointers of one uploaded scene
   // background inside k_raygen and never enter the queue (rt_kernels.cu::k_raygen).
   float world_lo[3], world_hi[3];
   uint32_t has_world_box;
+  uint32_t moving_first, moving_count;   // TF_MOVLIST: the moving primitives, outside the tree (scanned once per segment)
 };
 
 }  // namespace rtb

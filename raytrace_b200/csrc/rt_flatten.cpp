@@ -621,7 +621,7 @@ struct Builder {
     const RNode& n = rnodes[r];
     if (n.kind == RNode::LEAF) {
       const HPrim& p = prims[n.prim];
-      if ((p.flags & PRIM_FLAG_BOXTAIL) && !out.empty()) {   // faces 1..5 travel with their head
+      if ((p.flags & PRIM_FLAG_BOXTAIL) && !out.empty() && out.back().prim + out.back().n == n.prim) {   // faces 1..5 travel with their head
         out.back().n++;
         out.back().box.join(p.box);
         return;
@@ -630,6 +630,32 @@ struct Builder {
       return;
     }
     for (int c : n.children) collect_items(c, out);
+  }
+  // Moving / instanced primitives of the surface tree kept out of it (TF_MOVLIST, rt_device.h): decided by
+  // plan_moving_list() before the surface tree is built
+  bool split_moving = false;
+  uint32_t moving_first = 0, moving_count = 0;
+  uint32_t count_moving(int r) const {
+    const RNode& n = rnodes[r];
+    if (n.kind == RNode::LEAF) return (prims[n.prim].flags & PRIM_FLAG_MOVING) ? 1u : 0u;
+    uint32_t t = 0;
+    for (int c : n.children) t += count_moving(c);
+    return t;
+  }
+  uint32_t count_leaves(int r) const {
+    const RNode& n = rnodes[r];
+    if (n.kind == RNode::LEAF) return 1u;
+    uint32_t t = 0;
+    for (int c : n.children) t += count_leaves(c);
+    return t;
+  }
+  void plan_moving_list(int surf, bool enabled) {
+    split_moving = false;
+    if (!enabled || !sah || surf < 0) return;
+    const uint32_t nm = count_moving(surf), nall = count_leaves(surf);
+    if (nm == 0 || nm > kMaxMovingList || nall - nm <= kLeafMax) return;      // nothing to gain for a short list of statics
+    for (const MediumRec& m : media) if (count_moving(m.rtree)) return;        // a moving medium boundary: keep the fallback
+    split_moving = true;
   }
   int sah_leaf(std::vector<Item>& items, size_t lo, size_t hi) {
     std::sort(items.begin() + lo, items.begin() + hi, [&](const Item& a, const Item& b) { return prims[a.prim].ref_index < prims[b.prim].ref_index; });
@@ -719,9 +745,25 @@ struct Builder {
     hnodes[me].box.join(hnodes[r].box);
     return me;
   }
-  int to_device_sah(int r) {
+  int to_device_sah(int r, bool is_surface = false) {
     std::vector<Item> items;
     collect_items(r, items);
+    std::vector<Item> movers;
+    if (is_surface && split_moving) {
+      std::vector<Item> keep;
+      for (const Item& it : items) ((prims[it.prim].flags & PRIM_FLAG_MOVING) ? movers : keep).push_back(it);
+      items.swap(keep);
+    }
+    struct AfterTree {     // the moving list is stored right behind the tree's primitives, in evaluation order
+      Builder& b; std::vector<Item>& mv;
+      ~AfterTree() {
+        if (mv.empty()) return;
+        std::sort(mv.begin(), mv.end(), [&](const Item& x, const Item& y) { return b.prims[x.prim].ref_index < b.prims[y.prim].ref_index; });
+        b.moving_first = b.next_storage;
+        for (const Item& it : mv) for (uint32_t k = 0; k < it.n; k++) b.prims[it.prim + k].index = b.next_storage++;
+        b.moving_count = b.next_storage - b.moving_first;
+      }
+    } after{*this, movers};
     uint32_t n_prims = 0;
     for (Item& it : items) {
       n_prims += it.n;
@@ -731,8 +773,8 @@ struct Builder {
     return sah_node(items, 0, items.size(), 0);
   }
 
-  int to_device(int r) {
-    if (sah) return to_device_sah(r);
+  int to_device(int r, bool is_surface = false) {
+    if (sah) return to_device_sah(r, is_surface);
     const RNode n = rnodes[r];  // copy: hnodes/rnodes may grow
     if (n.kind == RNode::LEAF) {
       hnodes.emplace_back();
@@ -1021,10 +1063,13 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
 
     FlatScene fs;
     uint32_t max_depth = 0;
+    b.plan_moving_list(surf, O.split_moving != 0);
     if (surf >= 0) {
-      int h = b.to_device(surf);
+      int h = b.to_device(surf, true);
       fs.surface_root = b.emit_ref(fs, h, 0, max_depth);
     }
+    fs.moving_first = b.moving_first;
+    fs.moving_count = b.moving_count;
     lap("surface tree to device");
     std::vector<uint32_t> surf_geoms;
     if (surf >= 0) b.collect_geoms(surf, surf_geoms);
@@ -1072,7 +1117,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
     for (const HPrim& p : b.prims) {
       if (p.index == kNone) continue;
       fs.features |= (p.type == PRIM_SPHERE) ? TF_SPHERE : TF_PLANAR;
-      if (p.flags & PRIM_FLAG_MOVING) fs.features |= TF_MOVING;
+      if (p.flags & PRIM_FLAG_MOVING) fs.features |= b.split_moving ? TF_MOVLIST : TF_MOVING;
       if (p.flags & PRIM_FLAG_BOXHEAD) fs.features |= TF_BOX;
     }
     if (!b.media.empty()) fs.features |= TF_MEDIA;

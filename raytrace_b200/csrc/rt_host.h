@@ -55,6 +55,7 @@ struct FlatScene {
   uint32_t features = 0;       // TF_* bits: selects the kernel specialisation
   float world_lo[3] = {0, 0, 0}, world_hi[3] = {0, 0, 0};   // box of all primitives (outward rounded)
   uint32_t has_world_box = 0;
+  uint32_t moving_first = 0, moving_count = 0;   // TF_MOVLIST
   uint64_t bytes() const;
 };
 

@@ -424,6 +424,7 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
                 // as an ordinary one (once per ~1e4 interior segments)
                 tmin = tmin0;
                 h = Hit{inf, kNone, false};
+                if constexpr ((F & TF_MOVLIST) != 0) scan_moving<F>(sc, ray, tmin, origin_geom, h);
                 cur = sc.surface_root;
                 break;
               }
@@ -536,6 +537,10 @@ __global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl
                 if (h.t < inf) tmin = 0.f;
               }
             }
+            if constexpr ((F & TF_MOVLIST) != 0) {   // the moving primitives, outside the tree: once per segment
+              if constexpr (kCount) for (uint32_t k = 0; k < sc.moving_count; k++) count_prim(sc.moving_first + k);
+              scan_moving<F>(sc, ray, tmin, origin_geom, h);
+            }
           }
         }
       }
@@ -606,6 +611,7 @@ static TraverseFn pick_planar_variant(uint32_t features) {
 }
 template <template <uint32_t> class K>
 static TraverseFn pick_by_features(uint32_t features) {
+  if (features & TF_MOVLIST) return K<TF_SPHERE | TF_PLANAR | TF_MEDIA | TF_BOX | TF_MOVLIST>::fn();   // static tree + short moving list
   if (features & TF_BOX) return pick_planar_variant<K, TF_BOX>(features);   // aggregated cuboids present (implies planar)
   if (!(features & TF_MOVING)) {
     if ((features & (TF_SPHERE | TF_PLANAR | TF_MEDIA)) == TF_SPHERE) return K<TF_SPHERE>::fn();
@@ -820,7 +826,7 @@ __global__ void __launch_bounds__(kShadeBlock, RT_TRACE_FLAT_MINB) k_trace_flat(
 
 using TraceFlatFn = void (*)(Ctl*, Queue, Queue, const DScene, const RenderArgs, const FlatList);
 static TraceFlatFn pick_trace_flat(uint32_t features) {
-  if (features & (TF_MOVING | TF_MEDIA)) return nullptr;
+  if (features & (TF_MOVING | TF_MEDIA | TF_MOVLIST)) return nullptr;
   switch (features & (TF_SPHERE | TF_PLANAR)) {
     case TF_SPHERE: return k_trace_flat<TF_SPHERE>;
     case TF_PLANAR: return k_trace_flat<TF_PLANAR>;
@@ -955,7 +961,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_probe(const __grid_constant_
     ray.time = time;
     ray.o = ld3(c.center);
     ray.d = normalize3(fma3((float)i + 0.5f, ld3(c.pixel_u), fma3((float)j + 0.5f, ld3(c.pixel_v), ld3(c.top_left))));
-    Hit h = trace_segment<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_BOX>(sc, ray, kNone, false, make_uint2(0, 0), 0, 0, 0, s_stack + threadIdx.x, kTraverseBlock);
+    Hit h = trace_segment<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_BOX | TF_MOVLIST>(sc, ray, kNone, false, make_uint2(0, 0), 0, 0, 0, s_stack + threadIdx.x, kTraverseBlock);
     ids[p] = h.prim == kNone ? kNone : sc.canonical[h.prim];
     ts[p] = h.t;
   }
@@ -977,7 +983,7 @@ __global__ void __launch_bounds__(kTraverseBlock) k_probe_surface(const __grid_c
     ray.time = time;
     ray.o = ld3(cam.center);
     ray.d = normalize3(fma3((float)i + 0.5f, ld3(cam.pixel_u), fma3((float)j + 0.5f, ld3(cam.pixel_v), ld3(cam.top_left))));
-    Hit h = trace_segment<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_BOX>(sc, ray, kNone, false, make_uint2(0, 0), 0, 0, 0, s_stack + threadIdx.x, kTraverseBlock);
+    Hit h = trace_segment<TF_SPHERE | TF_PLANAR | TF_MOVING | TF_BOX | TF_MOVLIST>(sc, ray, kNone, false, make_uint2(0, 0), 0, 0, 0, s_stack + threadIdx.x, kTraverseBlock);
     float* o = out + 10 * (size_t)p;
     for (int k = 0; k < 10; k++) o[k] = 0.f;
     if (h.prim == kNone) continue;
@@ -1236,6 +1242,8 @@ static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
   for (int k = 0; k < 3; k++) { d.world_lo[k] = f.world_lo[k]; d.world_hi[k] = f.world_hi[k]; }
   d.has_world_box = f.has_world_box;
   d.n_prims = (uint32_t)f.canonical.size();
+  d.moving_first = f.moving_first;
+  d.moving_count = f.moving_count;
   s.devices[device] = ds;
   *out = ds;
   return RT_OK;
@@ -1395,17 +1403,21 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   // the depth limit leaves dozens of near-empty iterations to replace (demo1 / demo2, depth 50); at depth 20 with
   // subsurface media (pawn, bunny) the iterations are cheaper.  Sweeps: profiles/r01h_sweep_tail.txt
   const RtOptions& O = s.opts;
-  A.finish_max = dev.has_flat ? 0xFFFFFFFFu : (cam.max_depth > 24 ? 1u << 20 : 0u);
+  // "flat scene" = the fused one-launch kernel applies: the surfaces are one short list AND nothing needs the generic
+  // traversal (no media, no moving instances); a short list with media / movers runs the BVH kernels on a leaf root
+  const TraceFlatFn fused = dev.has_flat ? pick_trace_flat(s.flat.features) : nullptr;
+  const bool flat_scene = fused != nullptr;
+  A.finish_max = flat_scene ? 0xFFFFFFFFu : (cam.max_depth > 24 ? 1u << 20 : 0u);
   if (O.finish_max >= 0) A.finish_max = (uint32_t)std::min<int64_t>(O.finish_max, 0xFFFFFFFFll);
   A.finish_refill = 4;
   if (O.finish_refill >= 0) A.finish_refill = std::min(32, std::max(1, (int)O.finish_refill));
-  A.tile = dev.has_flat ? 0u : 1u;   // coherence only matters to the BVH kernels; the flat scan is the same for every ray
+  A.tile = flat_scene ? 0u : 1u;   // coherence only matters to the BVH kernels; the flat scan is the same for every ray
   if (O.tile >= 0) A.tile = O.tile ? 1u : 0u;
   // Camera rays that miss the world box end inside k_raygen.  Worth the test (and the compaction it brings) only when the
   // lens lies OUTSIDE the box - from inside it every ray passes (demo1 / demo2: +1 ms for nothing).  Flat scenes: the fused
   // kernel generates its own camera rays.
   A.cull = 0u;
-  if (dev.d.has_world_box && !dev.has_flat) {
+  if (dev.d.has_world_box && !flat_scene) {
     float lens = 0.f;
     if (cam.has_defocus)
       lens = std::max(std::sqrt(cam.defocus_u[0] * cam.defocus_u[0] + cam.defocus_u[1] * cam.defocus_u[1] + cam.defocus_u[2] * cam.defocus_u[2]),
@@ -1413,7 +1425,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
     for (int k = 0; k < 3; k++)
       if (cam.center[k] + lens < dev.d.world_lo[k] || cam.center[k] - lens > dev.d.world_hi[k]) A.cull = 1u;
   }
-  if (O.primary_cull >= 0) A.cull = (O.primary_cull && dev.d.has_world_box && !dev.has_flat) ? 1u : 0u;
+  if (O.primary_cull >= 0) A.cull = (O.primary_cull && dev.d.has_world_box && !flat_scene) ? 1u : 0u;
   for (int k = 0; k < 3; k++) { A.world_lo[k] = dev.d.world_lo[k]; A.world_hi[k] = dev.d.world_hi[k]; }
   // culling iterations: a k_raygen thread owns K consecutive samples of a pixel (one background atomic triple per K samples)
   A.kblock = 1u;
@@ -1443,7 +1455,6 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
 
   const bool count_work = stats != nullptr && O.count_work > 0;
   const TraverseFn traverse = count_work ? pick_by_features<CountedK>(s.flat.features) : pick_by_features<PersistentK>(s.flat.features);
-  const TraceFlatFn fused = dev.has_flat ? pick_trace_flat(s.flat.features) : nullptr;
   const TraverseFn finish = pick_by_features<FinishK>(s.flat.features);
   const FinishFlatFn finish_flat = fused ? pick_finish_flat(s.flat.features) : nullptr;
   int g_trav = dev.sm_count * 8, g_shade = dev.sm_count * 8, g_gen = dev.sm_count * 4;

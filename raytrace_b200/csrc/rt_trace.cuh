@@ -129,6 +129,13 @@ struct ParamRec {
   __device__ __forceinline__ float4 r2() const { return R[2]; }
 };
 
+// Planar coordinates a, b are computed in fp32 from p = o + t d (rounding ~ 3e-7 at Cornell's scale): with the exact bounds
+// 0 <= a, b <= 1 (Geometry.hs:150,174) a ray through the shared edge of two parallelograms / triangles can fall OUTSIDE both
+// and see the background through a closed wall (28 pixel centres on Cornell's wall / floor edge, one on the pawn).  The
+// bounds are therefore widened by kEdgeEps: on the edge both primitives are hit and the closer one - or, on an exact tie,
+// the one the reference evaluates first - wins, which is what the fp64 reference does on one side or the other.
+constexpr float kEdgeEps = 1e-6f;
+
 // Exact tie between two primitives (same t to the last bit: coplanar duplicates, shared edges): the reference keeps the
 // one it evaluates first (Geometry.hs:340-345,356-361).  Device indices follow the device tree, so the evaluation order
 // is looked up — on ties only.
@@ -283,7 +290,7 @@ __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, u
         const float a = dot3(mk3(p1.z, p1.w, p2.x), pr), b = dot3(mk3(p2.y, p2.z, p2.w), pr);
         const bool pgram = (tf & PRIM_TYPE_MASK) == PRIM_PGRAM;           // uniform (constant bank)
         const float lim = pgram ? fmaxf(a, b) : a + b;                    // a, b <= 1  |  a + b <= 1
-        const bool ok = (a >= 0.f) & (b >= 0.f) & (lim <= 1.f) & (fabsf(denom) > 1e-8f) & (t > tmin) & (t < best.t) & (geom != skip_a);
+        const bool ok = (a >= -kEdgeEps) & (b >= -kEdgeEps) & (lim <= 1.f + kEdgeEps) & (fabsf(denom) > 1e-8f) & (t > tmin) & (t < best.t) & (geom != skip_a);
         if (ok) {
           best.t = t;
           best.prim = i;
@@ -298,8 +305,8 @@ __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, u
       const float4 p2 = rec.r2();
       f3 pr = fma3(t, d, -qo);                   // p - q
       float a = dot3(mk3(p1.z, p1.w, p2.x), pr), b = dot3(mk3(p2.y, p2.z, p2.w), pr);
-      if ((tf & PRIM_TYPE_MASK) == PRIM_PGRAM) { if (!(0.f <= a && a <= 1.f && 0.f <= b && b <= 1.f)) return; }
-      else { if (!(a >= 0.f && b >= 0.f && a + b <= 1.f)) return; }
+      if ((tf & PRIM_TYPE_MASK) == PRIM_PGRAM) { if (!(-kEdgeEps <= a && a <= 1.f + kEdgeEps && -kEdgeEps <= b && b <= 1.f + kEdgeEps)) return; }
+      else { if (!(a >= -kEdgeEps && b >= -kEdgeEps && a + b <= 1.f + kEdgeEps)) return; }
       front = denom < 0.f;
     } else return;
   }
@@ -320,6 +327,13 @@ __device__ __forceinline__ uint32_t intersect_prim(const DScene& sc, uint32_t i,
   intersect_rec<F>(sc, rec, i, ray, tmin, skip_a, skip_b, best);
   if constexpr ((F & TF_BOX) != 0) return (__float_as_uint(rec.hi.b.x) & PRIM_FLAG_BOXHEAD) ? 6u : 1u;
   return 1u;
+}
+
+// TF_MOVLIST: the scene's moving / instanced primitives live outside the tree; every closest-hit query over the SURFACES
+// scans them once.
+template <uint32_t F>
+__device__ __forceinline__ void scan_moving(const DScene& sc, const RayT& ray, float tmin, uint32_t skip_a, Hit& best) {
+  for (uint32_t k = 0; k < sc.moving_count;) k += intersect_prim<(F & ~TF_MOVLIST) | TF_MOVING>(sc, sc.moving_first + k, ray, tmin, skip_a, kNone, best);
 }
 
 // slab test of one 32-byte node against the clipped interval (tmin, tmax]
@@ -408,6 +422,7 @@ __device__ __forceinline__ Hit trace_segment(const DScene& sc, const RayT& ray, 
   }
   // the bounded query looks at (0, bound]: a scatter point lies on no surface, and a boundary crossing inside (0, tmin] -
   // which the reference's open interval skips, so that it sees the ray as already outside - must be noticed
+  if constexpr ((F & TF_MOVLIST) != 0) scan_moving<F>(sc, ray, best.t < inf ? 0.f : tmin, origin_geom, best);
   closest_hit<F>(sc, sc.surface_root, ray, best.t < inf ? 0.f : tmin, origin_geom, kNone, stack, stride, best);
   if constexpr ((F & TF_MEDIA) != 0) {
     if (best.prim == kNone && best.t < inf) {   // nothing before the free-flight distance: the scatter event
@@ -417,6 +432,7 @@ __device__ __forceinline__ Hit trace_segment(const DScene& sc, const RayT& ray, 
     }
     if (best.prim != kNone && !(best.t > tmin)) {   // crossing within tmin: an ordinary segment after all (~1e-4 of them)
       best = Hit{inf, kNone, false};
+      if constexpr ((F & TF_MOVLIST) != 0) scan_moving<F>(sc, ray, tmin, origin_geom, best);
       closest_hit<F>(sc, sc.surface_root, ray, tmin, origin_geom, kNone, stack, stride, best);
     }
     if (with_media) {

@@ -350,3 +350,31 @@ def test_primary_ray_culling_with_a_lens(built):
     assert sa["iterations"] <= sb["iterations"]         # culled paths never occupy pool slots
     ref, _ = OracleScene(world).render(s, 11)
     assert abs(luminance(a.astype(np.float64)).mean() - luminance(ref).mean()) < 0.03 * luminance(ref).mean()
+
+
+def test_moving_primitives_in_a_list_of_their_own(built):
+    """demo2's one motion-blurred sphere lives outside the tree (TF_MOVLIST: scanned once per segment) so that the 3406
+    static primitives run the traversal kernel without the per-primitive transform branch; with RtOptions.split_moving = 0
+    it sits in the tree and every primitive test carries the branch.  Same primitive ids and distances at three shutter
+    times, same path segments, same image at equal seeds."""
+    s, w = scenes.demo2(width=72, spp=8, depth=12)
+    a, b = CompiledScene(w), CompiledScene(w, options=dict(split_moving=0))
+    assert a.info()["n_moving_list"] == 1 and b.info()["n_moving_list"] == 0
+    probe = s.replace(cs_imageWidth=400)
+    for t in (0.0, 0.5, 1.0):
+        ia, ta = a.probe_primary(probe, time=t)
+        ib, tb = b.probe_primary(probe, time=t)
+        assert (ia == ib).mean() >= 0.9999
+        hit = (ia == ib) & (ia != 0xFFFFFFFF)
+        assert np.all(np.abs(ta[hit] - tb[hit]) <= 1e-5 * np.abs(tb[hit]))
+    moving_id = 3401                                   # the lambertian moving sphere is hit somewhere in the frame
+    img_a, st_a = a.render(s, rt.mkStdGen(1234), want_stats=True)
+    img_b, st_b = b.render(s, rt.mkStdGen(1234), want_stats=True)
+    assert abs(int(st_a["rays"]) - int(st_b["rays"])) <= 1e-4 * st_b["rays"] + 2
+    assert np.isclose(img_a, img_b, rtol=2e-4, atol=2e-5).all(axis=2).mean() >= 0.999
+    # the tail kernel and the instrumented traversal see the list too
+    a.handle.set_options(finish_max=4294967295, count_work=1)
+    img_c, st_c = a.render(s, rt.mkStdGen(1234), want_stats=True)
+    assert np.isclose(img_c, img_a, rtol=2e-4, atol=2e-5).all(axis=2).mean() >= 0.999
+    assert st_c["rays_counted"] > 0 and st_c["sphere_tests"] >= st_c["rays_counted"]     # every segment tests the moving sphere
+    del moving_id
