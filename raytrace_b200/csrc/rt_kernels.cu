@@ -100,6 +100,7 @@ struct RenderArgs {
   // them and sums the background of its culled camera rays in registers: one atomic triple per pixel instead of one per
   // sample); kblock = 1: an item is (sample pass, pixel).  A bijection onto (pixel, sample) either way - the RNG is keyed by
   // (pixel, global sample), so the sample set does not depend on it.
+  uint32_t shade_sort;                  // k_shade: deal the paths of a tile to the threads by material class
   uint32_t kblock, ktail;               // K; n_samples % K
   unsigned long long kfull_items;       // (n_samples / K) * K * n_pixels: items before the ragged last block of samples
 };
@@ -695,6 +696,8 @@ __device__ __forceinline__ void shade_tiles(Ctl* __restrict__ ctl, const Queue& 
   __shared__ uint8_t s_perm[3 * 256];
   __shared__ uint32_t s_cnt[2][kShadeBlock / 32];
   __shared__ uint32_t s_base[2];
+  __shared__ uint32_t s_bin[FF ? 1 : 64];        // material-coherent shading: class histogram and permutation of the tile
+  __shared__ uint8_t s_order[FF ? 1 : kShadeBlock];
   // double-buffered tile of queue records, filled by TMA one iteration ahead (16 KB per stage)
   __shared__ __align__(128) float4 s_o[2][kShadeBlock];
   __shared__ __align__(128) float4 s_d[2][kShadeBlock];
@@ -749,26 +752,70 @@ __device__ __forceinline__ void shade_tiles(Ctl* __restrict__ ctl, const Queue& 
     f3 thr = mk3(0.f, 0.f, 0.f);
     uint32_t origin_geom = kNone, pixel = 0;
     uint2 meta = make_uint2(0, 0);
-    if (i < n) {
-      if (GEN && i >= n_stored) {   // Ray.hs:229-231 for work item fill_item0 + (slot - fill_lo), as k_raygen numbers them
-        const NewPath np = new_camera_path(A, item0 + (i - n_stored));
+    // Material-coherent shading (the reference author's own note, Material.hs:36-38): the 256 paths of the tile
+    // are re-dealt to the threads by MATERIAL CLASS (miss / material kind / texture family - a counting sort through shared
+    // memory, where the tile already sits), so that a warp shades one kind of surface instead of serialising ten.  Only the
+    // thread -> path assignment changes: same paths, same RNG counters, same results.
+    uint32_t src = threadIdx.x;         // which path of the tile this thread shades
+    if constexpr (FF == 0) {
+      if (A.shade_sort) {
+        uint32_t key = 63u;               // slots past the end of the queue sort last
+        if (i < n) {
+          const uint32_t prim = __float_as_uint(s_h[par][threadIdx.x].y);
+          key = 0u;                       // miss: background
+          if (prim != kNone) {
+            const uint32_t m = prim >= kMediumBase ? sc.media[prim - kMediumBase].material : __float_as_uint(__ldg(sc.prims + 4 * (size_t)prim + 3).w);
+            const DMaterial mat = sc.materials[m];
+            key = (uint32_t)mat.kind;     // 1 .. 10
+            if (mat.kind != RT_MAT_PITCH_BLACK && mat.kind != RT_MAT_DIELECTRIC) {
+              const int tk = sc.textures[mat.texture].kind;
+              if (tk == RT_TEX_NOISE || tk == RT_TEX_MARBLE) key += 16u;          // Perlin octaves: by far the longest shader
+              else if (tk == RT_TEX_IMAGE || tk == RT_TEX_CHECKER) key += 32u;     // needs uv (atan2 / acos on spheres)
+            }
+          }
+        }
+        if (threadIdx.x < 64) s_bin[threadIdx.x] = 0u;
+        __syncthreads();
+        const uint32_t rank = atomicAdd(&s_bin[key], 1u);
+        __syncthreads();
+        if (warp == 0) {                  // exclusive prefix over the 64 bins: two bins per lane, one shuffle scan
+          const uint32_t v0 = s_bin[2 * lane], v1 = s_bin[2 * lane + 1];
+          uint32_t incl = v0 + v1;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if ((int)lane >= o) incl += up;
+          }
+          s_bin[2 * lane] = incl - v0 - v1;
+          s_bin[2 * lane + 1] = incl - v1;
+        }
+        __syncthreads();
+        s_order[s_bin[key] + rank] = (uint8_t)threadIdx.x;
+        __syncthreads();
+        src = s_order[threadIdx.x];
+      }
+    }
+    const uint32_t i_src = base + src;
+    if (i_src < n) {
+      if (GEN && i_src >= n_stored) {   // Ray.hs:229-231 for work item fill_item0 + (slot - fill_lo), as k_raygen numbers them
+        const NewPath np = new_camera_path(A, item0 + (i_src - n_stored));
         ray = np.ray;
         thr = mk3(1.f, 1.f, 1.f);
         pixel = np.pixel;
         meta = make_uint2(np.sample_lo, 0u);
       } else {
-        const float4 o4 = s_o[par][threadIdx.x], d4 = s_d[par][threadIdx.x], t4 = s_t[par][threadIdx.x];
-        meta = s_m[par][threadIdx.x];
+        const float4 o4 = s_o[par][src], d4 = s_d[par][src], t4 = s_t[par][src];
+        meta = s_m[par][src];
         ray = RayT{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
         thr = mk3(t4.x, t4.y, t4.z);
         pixel = __float_as_uint(t4.w);
         origin_geom = __float_as_uint(d4.w);
       }
       Hit hit;
-      if (FF) {   // closest hit over the constant-bank list (same code and order as k_traverse_flat)
+      if (FF) {   // closest hit over the constant-bank list
         hit = scan_flat<FF ? FF : TF_SPHERE>(sc, *L, ray, origin_geom);
       } else {
-        const float2 h2 = s_h[par][threadIdx.x];
+        const float2 h2 = s_h[par][src];
         hit = Hit{fabsf(h2.x), __float_as_uint(h2.y), !(h2.x < 0.f)};
       }
       alive = shade_path(sc, A, T, ray, hit, thr, origin_geom, pixel, meta);
@@ -1427,6 +1474,14 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   }
   if (O.primary_cull >= 0) A.cull = (O.primary_cull && dev.d.has_world_box && !flat_scene) ? 1u : 0u;
   for (int k = 0; k < 3; k++) { A.world_lo[k] = dev.d.world_lo[k]; A.world_hi[k] = dev.d.world_hi[k]; }
+  {   // material-coherent shading pays when warps would otherwise mix several shaders: three or more material kinds, or
+      // procedural / image textures next to plain ones (sweep: profiles/r02*_sweep_shade_sort.txt)
+    uint32_t kinds = 0, texk = 0;
+    for (const DMaterial& m : s.flat.materials) kinds |= 1u << (m.kind & 31);
+    for (const DTexture& t : s.flat.textures) texk |= 1u << (t.kind & 31);
+    A.shade_sort = (__builtin_popcount(kinds) >= 3 || (texk & ~(1u << RT_TEX_CONSTANT)) != 0) ? 1u : 0u;
+    if (O.shade_sort >= 0) A.shade_sort = O.shade_sort ? 1u : 0u;
+  }
   // culling iterations: a k_raygen thread owns K consecutive samples of a pixel (one background atomic triple per K samples)
   A.kblock = 1u;
   if (A.cull) {
