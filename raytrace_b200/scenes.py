@@ -26,8 +26,9 @@ from .material import (dielectric, isotropic, lambertian, lightSource, lommelSee
 from .ray import CameraSettings, Ray, defaultCameraSettings
 from .texture import (checkerTexture, constantTexture, imageTexture, marbleTexture, noiseTexture)
 
-ASSET_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
-                         "tests", "golden", "assets")
+# package data: the reference's own input files (images/pawn.obj, images/bunny.obj, images/earthmap.jpg), read the way the
+# reference reads them - readObj / parseObj through the library's C++ loader (rt_obj_parse) and readImage
+ASSET_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "assets")
 
 SEEDS = {"readme": 100, "cornell": 234, "demo1": 1, "demo2": 1234, "pawn": 55, "bunny": 55,
          "lommel": 55, "sphere_uv": 12}
@@ -50,6 +51,8 @@ def black(_ray: Ray):
 
 
 # ---- assets ---------------------------------------------------------------------------------------
+_EARTH = None
+_MESHES: dict = {}
 
 def _srgb8_to_linear(img_u8: np.ndarray) -> np.ndarray:
     c = img_u8.astype(np.float64) / 255.0
@@ -57,15 +60,20 @@ def _srgb8_to_linear(img_u8: np.ndarray) -> np.ndarray:
 
 
 def load_earthmap() -> np.ndarray:
-    """images/earthmap.jpg decoded (PIL) and linearised as `readImage` does (Ray.hs:241-245)."""
-    z = np.load(os.path.join(ASSET_DIR, "earthmap.npz"))
-    return _srgb8_to_linear(z["rgb8"])
+    """images/earthmap.jpg through `readImage` (decode, then sRGB -> linear; Ray.hs:241-245)."""
+    global _EARTH
+    if _EARTH is None:
+        from .ray import readImage
+        _EARTH = readImage(os.path.join(ASSET_DIR, "earthmap.jpg"))
+    return _EARTH
 
 
 def load_mesh(name: str) -> Mesh:
-    """images/<name>.obj parsed with parseObj's rules (Geometry.hs:207-285)."""
-    z = np.load(os.path.join(ASSET_DIR, f"{name}.npz"))
-    return Mesh(z["verts"], z["uvs"], z["faces"])
+    """images/<name>.obj through readObj: the .obj TEXT parsed by the library's loader (rt_obj_parse, Geometry.hs:207-285)."""
+    if name not in _MESHES:
+        from .geometry import readObj
+        _MESHES[name] = readObj(os.path.join(ASSET_DIR, f"{name}.obj"))
+    return _MESHES[name]
 
 
 # ---- config 1: README example (README.md:41-55) --------------------------------------------------

@@ -5,6 +5,8 @@ Run HERE (the authoring container, where /root/reference exists):
 Nothing in tests/, smoke() or bench.py reads /root/reference at run time; they read the
 .npz files this script writes.
 
+  raytrace_b200/assets/{pawn.obj,bunny.obj,earthmap.jpg} — the reference's input files, copied as package data (what the
+                                       product reads: .obj text through rt_obj_parse, the JPEG through readImage)
   assets/pawn.npz, assets/bunny.npz  — images/*.obj parsed by the pure-Python restatement of
                                        parseObj (oracle/obj_oracle.py; Geometry.hs:207-285)
   assets/earthmap.npz                — images/earthmap.jpg decoded by PIL to 8-bit sRGB
@@ -30,6 +32,11 @@ REF = "/root/reference"
 
 
 def main():
+    import shutil
+    pkg = os.path.join(ROOT, "raytrace_b200", "assets")
+    os.makedirs(pkg, exist_ok=True)
+    for f in ("pawn.obj", "bunny.obj", "earthmap.jpg"):
+        shutil.copyfile(f"{REF}/images/{f}", os.path.join(pkg, f))
     os.makedirs(os.path.join(HERE, "assets"), exist_ok=True)
     os.makedirs(os.path.join(HERE, "png"), exist_ok=True)
     for name in ("pawn", "bunny"):
