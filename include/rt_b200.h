@@ -354,6 +354,26 @@ int32_t rt_set_pool_size(RtScene* scene, uint32_t n_paths);            /* = opti
 int32_t rt_tonemap_u8(int32_t device, const float* rgb_host, int32_t n_pixels, int32_t mode,
                       uint8_t* rgb8_host);
 
+/*
+ * Allocation-free variant of rt_tonemap_u8.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same kernel arithmetic and same result as rt_tonemap_u8, but the staging memory is a file-scope
+ * `static __device__` array inside the library instead of two cudaMalloc'ed buffers: the call performs no cudaMalloc,
+ * cudaFree, stream / event creation or any other allocating routine.
+ *   - limit: n_pixels <= RT_TONEMAP_STATIC_MAX_PIXELS (2 Mi pixels - a 1920 x 1080 frame fits); more is rejected with
+ *     RT_ERR_INVALID_ARG and a message.  Every GPU that loads the library holds the array (30 MiB) until the process exits.
+ *   - rgb / rgb8_out may be host OR device pointers (the copies use cudaMemcpyDefault); the work is queued on cuda_stream
+ *     (a cudaStream_t, NULL = the default stream) and the call waits for it unless that stream is being captured.
+ *   - the first call on a device resolves the array's device address (cudaGetSymbolAddress, which loads the module on that
+ *     device): make that call once outside any capture.
+ *   - every call on a device SHARES the one array, and it keeps the last call's contents (nothing in it needs to start at
+ *     zero: a call overwrites what it reads).  Calls that overlap on the same GPU - two streams, two threads - race on it:
+ *     serialise them.
+ */
+#define RT_TONEMAP_STATIC_MAX_PIXELS 2097152
+int32_t rt_tonemap_u8_static(int32_t device, const float* rgb, int32_t n_pixels, int32_t mode,
+                             uint8_t* rgb8_out, void* cuda_stream);
+
 /* .obj loader with the rules of parseObj (Geometry.hs:207-285). Buffers are owned by the
  * returned handle. */
 typedef struct RtMesh RtMesh;

@@ -136,6 +136,7 @@ EXPORTS = [
     "rt_obj_parse", "rt_mesh_sizes", "rt_mesh_data", "rt_mesh_destroy", "rt_host_alloc", "rt_host_free", "rt_reduce_image",
     "rt_options_init", "rt_scene_set_options", "rt_scene_get_options",
     "rt_context_create", "rt_context_destroy", "rt_context_info", "rt_render_multi",
+    "rt_tonemap_u8_static",
 ]
 
 _lib: Optional[C.CDLL] = None
@@ -186,6 +187,7 @@ def lib() -> C.CDLL:
     L.rt_scene_get_options.argtypes = [vp, C.POINTER(RtOptions)]
     L.rt_tonemap_u8.argtypes = [C.c_int32, C.POINTER(C.c_float), C.c_int32, C.c_int32,
                                 C.POINTER(C.c_uint8)]
+    L.rt_tonemap_u8_static.argtypes = [C.c_int32, vp, C.c_int32, C.c_int32, vp, vp]
     L.rt_obj_parse.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(vp)]
     L.rt_mesh_sizes.argtypes = [vp, u32p, u32p, u32p]
     L.rt_mesh_data.argtypes = [vp, C.POINTER(C.POINTER(C.c_double)), C.POINTER(C.POINTER(C.c_double)),

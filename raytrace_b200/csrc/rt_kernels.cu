@@ -1951,6 +1951,96 @@ int32_t rt_tonemap_u8(int32_t device, const float* rgb, int32_t n_pixels, int32_
   return RT_OK;
 }
 
+// ---- allocation-free tone mapping (no counterpart in the reference) ------
+// rt_tonemap_u8 stages the image through two cudaMalloc'ed buffers per call.  Some callers cannot call cudaMalloc (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid it), so this variant stages through a FILE-SCOPE
+// static device array instead: every GPU that loads the library holds kStaticTonemapBytes (30 MiB) until exit.
+// Layout: [0, 12 * kStaticTonemapMaxPixels) the linear float image, then the 8-bit result.  In HOST code the array's name is
+// only a host-side stand-in, not a device address: the address a kernel may use comes from cudaGetSymbolAddress, asked
+// once per device with that device current (static_scratch_for, below).
+constexpr size_t kStaticTonemapMaxPixels = RT_TONEMAP_STATIC_MAX_PIXELS;            // 2 Mi pixels: covers 1920 x 1080
+constexpr size_t kStaticTonemapOutOffset = kStaticTonemapMaxPixels * 3 * sizeof(float);   // a multiple of 256
+constexpr size_t kStaticTonemapBytes = kStaticTonemapOutOffset + kStaticTonemapMaxPixels * 3;
+static __device__ __align__(256) unsigned char g_tonemap_scratch[kStaticTonemapBytes];
+
+}  // extern "C"
+
+namespace rtb {
+
+// k_tonemap on the static scratch: reads n floats at `scratch`, writes n bytes at `scratch + kStaticTonemapOutOffset`
+__global__ void __launch_bounds__(256) k_tonemap_static(unsigned char* __restrict__ scratch, int n, int mode) {
+  const float* __restrict__ rgb = reinterpret_cast<const float*>(scratch);
+  uint8_t* __restrict__ out = scratch + kStaticTonemapOutOffset;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+    float x = rgb[k];
+    x = fminf(1.f, fmaxf(0.f, x));     // NaN -> 0
+    const float y = mode == 1 ? sqrtf(x) : (x <= 0.0031308f ? 12.92f * x : 1.055f * powf(x, 1.f / 2.4f) - 0.055f);
+    out[k] = (uint8_t)min(255, (int)floorf(y * 256.f));      // the reference encoder's quantiser (see k_tonemap)
+  }
+}
+
+// device address of g_tonemap_scratch on `device` (which must be current): resolved once per device, kept in a fixed table
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_static_mu;
+static unsigned char* g_static_ptr[kStaticMaxDevices] = {};
+static int g_static_sms[kStaticMaxDevices] = {};
+static int32_t static_scratch_for(int device, unsigned char** ptr, int* sms) {
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_ptr[device]) {
+    void* p = nullptr;
+    RT_CUDA(cudaGetSymbolAddress(&p, g_tonemap_scratch));
+    int major = 0, sm = 0;
+    RT_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+    RT_CUDA(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, device));
+    if (major < 10) { set_error("device " + std::to_string(device) + " is not sm_100 (kernels are built for sm_100a only)"); return RT_ERR_NO_DEVICE; }
+    g_static_sms[device] = sm;
+    g_static_ptr[device] = static_cast<unsigned char*>(p);
+  }
+  *ptr = g_static_ptr[device];
+  *sms = g_static_sms[device];
+  return RT_OK;
+}
+
+}  // namespace rtb
+
+extern "C" {
+
+int32_t rt_tonemap_u8_static(int32_t device, const float* rgb, int32_t n_pixels, int32_t mode, uint8_t* out, void* cuda_stream) {
+  if (!rgb || !out || n_pixels < 0) { set_error("rt_tonemap_u8_static: bad argument"); return RT_ERR_INVALID_ARG; }
+  if ((size_t)n_pixels > kStaticTonemapMaxPixels) {
+    set_error("rt_tonemap_u8_static: " + std::to_string(n_pixels) + " pixels exceed the static scratch array (at most " +
+              std::to_string(kStaticTonemapMaxPixels) + " pixels per call); use rt_tonemap_u8, which allocates, or split the image");
+    return RT_ERR_INVALID_ARG;
+  }
+  int visible = 0;
+  if (cudaGetDeviceCount(&visible) != cudaSuccess || visible == 0) {
+    cudaGetLastError();
+    set_error("no CUDA device visible: raytrace_b200 runs only on an sm_100 GPU (there is no CPU fallback)");
+    return RT_ERR_NO_DEVICE;
+  }
+  if (device < 0 || device >= visible || device >= kStaticMaxDevices) { set_error("device index out of range"); return RT_ERR_INVALID_ARG; }
+  DeviceGuard guard;
+  RT_CUDA(cudaSetDevice(device));
+  unsigned char* scratch = nullptr;
+  int sms = 0;
+  int32_t st = static_scratch_for(device, &scratch, &sms);
+  if (st != RT_OK) return st;
+  const size_t n = (size_t)n_pixels * 3;
+  if (n == 0) return RT_OK;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(cuda_stream);
+  // nothing in the array has to start at zero: [0, 4n) and the n result bytes are overwritten before they are read, and
+  // nothing beyond them is touched, so what an earlier (larger) call left behind is never seen
+  RT_CUDA(cudaMemcpyAsync(scratch, rgb, n * sizeof(float), cudaMemcpyDefault, stream));
+  const int grid = (int)std::min<size_t>((n + 255) / 256, (size_t)sms * 8);
+  k_tonemap_static<<<grid, 256, 0, stream>>>(scratch, (int)n, mode);
+  RT_CUDA(cudaGetLastError());
+  RT_CUDA(cudaMemcpyAsync(out, scratch + kStaticTonemapOutOffset, n, cudaMemcpyDefault, stream));
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
+  if (cap == cudaStreamCaptureStatusNone) RT_CUDA(cudaStreamSynchronize(stream));    // a capturing stream must not be synchronised
+  return RT_OK;
+}
+
 }  // extern "C"
 
 #include "rt_multi.cuh"   // rt_context_* / rt_render_multi (uses the static helpers above)
