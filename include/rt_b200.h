@@ -206,7 +206,7 @@ typedef struct RtOptions {
   int32_t shared_boundary;   /* 1 (default): a medium boundary that is also a surface is answered from the surface hit */
   int32_t interior_bound;    /* 1 (default): interior segments of a closed shared boundary are bounded by the free-flight distance */
   int32_t world_box;         /* 1 (default): keep the world box (camera rays that miss it end in k_raygen) */
-  int32_t split_moving;      /* 1 (default): moving instances get a tree of their own so that static primitives run the kernel without the per-primitive transform */
+  int32_t split_moving;      /* 1: moving instances live in a short list outside the tree so that static primitives run the kernel without the per-primitive transform branch (default 0: measured slower on demo2) */
   int32_t trace_commit;      /* 1: print the phases of the host scene pipeline to stderr */
   double sah_node_cost;      /* cost of a node step in primitive tests (default 1.0) */
   /* ---- render time ---- */
@@ -219,7 +219,7 @@ typedef struct RtOptions {
   int32_t trav_blocks;       /* k_traverse_p: resident blocks per SM (default 8) */
   int32_t tile;              /* 1: camera paths start in 8x4 pixel tiles (default for BVH scenes) */
   int32_t primary_cull;      /* 1/0: force camera-ray culling against the world box on/off (default: on when the lens is outside it) */
-  int32_t shade_sort;        /* 1: k_shade handles paths grouped by material class (default: on when the scene mixes Perlin / image textures with plain ones) */
+  int32_t shade_sort;        /* 1: k_shade handles paths grouped by material class (default: on when the scene has Perlin or image textures) */
   int32_t timing;            /* 0: no per-kernel events even when stats are requested (default 1) */
   int32_t count_work;        /* 1: run the instrumented traversal kernel and fill RtStats.node_pairs ... (default 0) */
   int32_t debug_sync;        /* 1: synchronise after every launch and name a faulting kernel on stderr */

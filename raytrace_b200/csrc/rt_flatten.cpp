@@ -1063,7 +1063,9 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
 
     FlatScene fs;
     uint32_t max_depth = 0;
-    b.plan_moving_list(surf, O.split_moving != 0);
+    // measured (profiles/r02c_sweep.txt, demo2): scanning the moving list once per segment costs more than the per-primitive
+    // transform branch it removes (45.2 vs 43.8 ms per 100 spp) - opt-in only
+    b.plan_moving_list(surf, O.split_moving > 0);
     if (surf >= 0) {
       int h = b.to_device(surf, true);
       fs.surface_root = b.emit_ref(fs, h, 0, max_depth);

@@ -1474,12 +1474,12 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   }
   if (O.primary_cull >= 0) A.cull = (O.primary_cull && dev.d.has_world_box && !flat_scene) ? 1u : 0u;
   for (int k = 0; k < 3; k++) { A.world_lo[k] = dev.d.world_lo[k]; A.world_hi[k] = dev.d.world_hi[k]; }
-  {   // material-coherent shading pays when warps would otherwise mix several shaders: three or more material kinds, or
-      // procedural / image textures next to plain ones (sweep: profiles/r02*_sweep_shade_sort.txt)
-    uint32_t kinds = 0, texk = 0;
-    for (const DMaterial& m : s.flat.materials) kinds |= 1u << (m.kind & 31);
+  {   // Material-coherent shading pays only when some shader is MUCH longer than the others (Perlin octaves, image-texture
+      // uv): demo2 47.0 -> 45.2 ms per 100 spp.  With plain constant textures the sort costs more than the divergence it
+      // removes (demo1 22.3 -> 23.3, pawn 23.2 -> 24.1; profiles/r02c_sweep.txt), so it stays off there.
+    uint32_t texk = 0;
     for (const DTexture& t : s.flat.textures) texk |= 1u << (t.kind & 31);
-    A.shade_sort = (__builtin_popcount(kinds) >= 3 || (texk & ~(1u << RT_TEX_CONSTANT)) != 0) ? 1u : 0u;
+    A.shade_sort = (texk & ((1u << RT_TEX_NOISE) | (1u << RT_TEX_MARBLE) | (1u << RT_TEX_IMAGE))) != 0 ? 1u : 0u;
     if (O.shade_sort >= 0) A.shade_sort = O.shade_sort ? 1u : 0u;
   }
   // culling iterations: a k_raygen thread owns K consecutive samples of a pixel (one background atomic triple per K samples)

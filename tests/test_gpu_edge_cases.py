@@ -354,11 +354,11 @@ def test_primary_ray_culling_with_a_lens(built):
 
 def test_moving_primitives_in_a_list_of_their_own(built):
     """demo2's one motion-blurred sphere lives outside the tree (TF_MOVLIST: scanned once per segment) so that the 3406
-    static primitives run the traversal kernel without the per-primitive transform branch; with RtOptions.split_moving = 0
-    it sits in the tree and every primitive test carries the branch.  Same primitive ids and distances at three shutter
+    static primitives run the traversal kernel without the per-primitive transform branch (RtOptions.split_moving = 1); by
+    default it sits in the tree and every primitive test carries the branch.  Same primitive ids and distances at three shutter
     times, same path segments, same image at equal seeds."""
     s, w = scenes.demo2(width=72, spp=8, depth=12)
-    a, b = CompiledScene(w), CompiledScene(w, options=dict(split_moving=0))
+    a, b = CompiledScene(w, options=dict(split_moving=1)), CompiledScene(w)
     assert a.info()["n_moving_list"] == 1 and b.info()["n_moving_list"] == 0
     probe = s.replace(cs_imageWidth=400)
     for t in (0.0, 0.5, 1.0):

@@ -105,9 +105,9 @@ def test_scene_counts(built):
     s, w = scenes.demo2(width=16, spp=1)
     info = CompiledScene(w, upload=False).info()
     assert info["n_media"] == 2 and info["n_planars"] == 2401 and info["n_spheres"] == 1008
-    assert info["n_moving_list"] == 1        # the one motion-blurred sphere lives outside the tree (TF_MOVLIST)
-    assert CompiledScene(w, upload=False, options=dict(split_moving=0)).info()["n_moving_list"] == 0
-    assert CompiledScene(w, upload=False, options=dict(bvh_reference=1)).info()["n_moving_list"] == 0
+    assert info["n_moving_list"] == 0        # default: the motion-blurred sphere stays in the tree
+    assert CompiledScene(w, upload=False, options=dict(split_moving=1)).info()["n_moving_list"] == 1     # TF_MOVLIST, opt-in
+    assert CompiledScene(w, upload=False, options=dict(split_moving=1, bvh_reference=1)).info()["n_moving_list"] == 0
     s, w = scenes.cornell_box()
     info = CompiledScene(w, upload=False).info()
     assert info["n_prims"] == 18 and info["n_media"] == 0
