@@ -1,6 +1,6 @@
 """north_star gates 1 + 2 at BASELINE.json's full sizes over ALL pixels, for the default (SAH) device tree and the
 reference-shaped one, with every pixel that does not pass listed (GPU box only; the committed evidence is
-profiles/r02*_parity_id_t_gates.txt).  usage: python tools/gpu_id_gate.py [scene ...]"""
+profiles/r02*_parity_id_t_gates.txt).  usage: python tools/gpu_id_gate.py [--head GITHASH] [scene ...]"""
 import json, os, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
 import numpy as np
@@ -10,11 +10,11 @@ from oracle.harness import OracleScene, primary_gate
 
 CASES = {"readme": dict(), "cornell": dict(spp=1), "demo1": dict(spp=1), "demo2": dict(width=800, spp=1),
          "pawn": dict(width=1920, aspect=16 / 9, spp=1), "bunny_volume": dict(spp=1)}
-try:
-    head = subprocess.run(["git", "rev-parse", "--short", "HEAD"], cwd=ROOT, capture_output=True, text=True).stdout.strip()
-except Exception:
-    head = ""
-for name in (sys.argv[1:] or list(CASES)):
+argv = sys.argv[1:]
+head = ""
+if argv and argv[0] == "--head":      # the GPU box has no .git: the caller passes `git rev-parse --short HEAD`
+    head, argv = argv[1], argv[2:]
+for name in (argv or list(CASES)):
     ctor, _ = scenes.CONFIGS[name]
     s, w = ctor(**CASES[name])
     ids5, ts5 = OracleScene(w).probe_tilted(s)
