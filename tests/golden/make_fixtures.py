@@ -15,7 +15,8 @@ Nothing in tests/, smoke() or bench.py reads /root/reference at run time; they r
   png/<name>.npz                     — the reference's golden renders, decoded to 8-bit RGB:
                                        example_image (README scene, seed 100, 50 spp, writeImage),
                                        cornell_box_noisy / cornell_box_redirect (200 spp, writeImageSqrt),
-                                       pawn_demo (500x500, 400 spp, depth 20, writeImage)
+                                       pawn_demo (500x500, 400 spp, depth 20, writeImage),
+                                       demo2 (800x800, scene from mkStdGen 1234, writeImageSqrt; spp / depth unrecorded)
 """
 import os
 import sys
@@ -47,7 +48,7 @@ def main():
     img = np.asarray(Image.open(f"{REF}/images/earthmap.jpg").convert("RGB"), dtype=np.uint8)
     np.savez_compressed(os.path.join(HERE, "assets", "earthmap.npz"), rgb8=img)
     print("earthmap", img.shape)
-    for name in ("example_image", "cornell_box_noisy", "cornell_box_redirect", "pawn_demo"):
+    for name in ("example_image", "cornell_box_noisy", "cornell_box_redirect", "pawn_demo", "demo2"):
         a = np.asarray(Image.open(f"{REF}/{name}.png").convert("RGB"), dtype=np.uint8)
         np.savez_compressed(os.path.join(HERE, "png", f"{name}.npz"), rgb8=a)
         print(name, a.shape)
