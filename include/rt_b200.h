@@ -187,6 +187,9 @@ typedef struct RtSceneInfo {
                                * are then bounded by the free-flight distance) */
   uint32_t n_moving_list;     /* moving / instanced primitives kept outside the tree in a short list scanned once per segment
                                * (RtOptions.split_moving): the static primitives then run the kernel without the transform branch */
+  uint32_t n_shared_trees;    /* media whose boundary geometry IS the surface geometry: their boundary queries walk the surface
+                               * tree, no second tree is built or uploaded (pawn, bunny) */
+  uint32_t reserved;
 } RtSceneInfo;
 
 typedef struct RtScene RtScene;

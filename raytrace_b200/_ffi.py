@@ -93,7 +93,8 @@ class RtSceneInfo(C.Structure):
                 ("n_bvh_nodes", C.c_uint32), ("n_media", C.c_uint32), ("n_materials", C.c_uint32),
                 ("n_textures", C.c_uint32), ("n_xforms", C.c_uint32), ("surface_root", C.c_uint32),
                 ("max_depth", C.c_uint32), ("device_bytes", C.c_uint64),
-                ("n_closed_media", C.c_uint32), ("n_moving_list", C.c_uint32)]
+                ("n_closed_media", C.c_uint32), ("n_moving_list", C.c_uint32),
+                ("n_shared_trees", C.c_uint32), ("reserved", C.c_uint32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -296,6 +296,8 @@ int32_t rt_scene_info(const RtScene* sp, RtSceneInfo* info) {
   info->n_closed_media = 0;
   for (uint32_t k = 0; k < f.n_media; k++) info->n_closed_media += f.media[k].closed ? 1u : 0u;
   info->n_moving_list = f.moving_count;
+  info->n_shared_trees = f.n_shared_trees;
+  info->reserved = 0;
   return RT_OK;
 }
 

@@ -56,6 +56,7 @@ struct FlatScene {
   float world_lo[3] = {0, 0, 0}, world_hi[3] = {0, 0, 0};   // box of all primitives (outward rounded)
   uint32_t has_world_box = 0;
   uint32_t moving_first = 0, moving_count = 0;   // TF_MOVLIST
+  uint32_t n_shared_trees = 0;   // media whose boundary queries walk the surface tree (boundary geometry == surface geometry)
   uint64_t bytes() const;
 };
 

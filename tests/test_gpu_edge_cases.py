@@ -378,3 +378,24 @@ def test_moving_primitives_in_a_list_of_their_own(built):
     assert np.isclose(img_c, img_a, rtol=2e-4, atol=2e-5).all(axis=2).mean() >= 0.999
     assert st_c["rays_counted"] > 0 and st_c["sphere_tests"] >= st_c["rays_counted"]     # every segment tests the moving sphere
     del moving_id
+
+
+@pytest.mark.parametrize("name,kw", [("pawn", dict(width=64, spp=16)), ("bunny_volume", dict(width=64, spp=8))], ids=["pawn", "bunny"])
+def test_boundary_queries_on_the_surface_tree(built, name, kw):
+    """When a medium's boundary IS the surface geometry its boundary queries walk the surface tree (RtSceneInfo.n_shared_trees);
+    with RtOptions.shared_boundary = 0 the boundary has a tree of its own and every boundary query is a traversal of it.  Same
+    primitives, same records: the same events at equal seeds (the bunny has holes, so its second boundary queries are real
+    traversals of the shared tree), up to a knife-edge tie."""
+    ctor, seed = scenes.CONFIGS[name]
+    s, w = ctor(**kw)
+    a, b = CompiledScene(w), CompiledScene(w, options=dict(shared_boundary=0))
+    assert a.info()["n_shared_trees"] == 1 and b.info()["n_shared_trees"] == 0
+    ia, sa = a.render(s, rt.mkStdGen(seed), want_stats=True)
+    ib, sb = b.render(s, rt.mkStdGen(seed), want_stats=True)
+    assert np.isfinite(ia).all()
+    assert abs(int(sa["rays"]) - int(sb["rays"])) <= 2e-4 * sb["rays"] + 2
+    assert np.isclose(ia, ib, rtol=2e-4, atol=2e-5).all(axis=2).mean() >= 0.998
+    assert abs(ia.mean() - ib.mean()) <= 2e-3 * ib.mean()
+    ida, ta = a.probe_primary(s.replace(cs_imageWidth=320))
+    idb, tb = b.probe_primary(s.replace(cs_imageWidth=320))
+    assert np.array_equal(ida, idb) and np.array_equal(ta, tb)

@@ -98,7 +98,32 @@ def test_flattened_tree_matches_reference_evaluation_order(built, name, policy):
             for ch in (c, c + 1):
                 assert (lo[k] <= lo[ch] + 1e-3).all() and (hi[k] >= hi[ch] - 1e-3).all()
     if len(nodes):                 # every primitive is reachable through some leaf (a medium whose boundary is one
-        assert (~seen).sum() <= 32 * max(1, info["n_media"])      # leaf is referenced from its DMedium record, not a node)
+        # a leaf root is referenced from its DMedium record, not a node; a medium whose boundary IS the surface geometry walks
+        # the surface tree, so its own copies of the records (half of the primitives: pawn, bunny) hang on no leaf
+        spare = info["n_prims"] // 2 if info["n_shared_trees"] else 0
+        assert (~seen).sum() <= 32 * max(1, info["n_media"]) + spare
+        if info["n_shared_trees"]:
+            assert (~seen).sum() == spare and not seen[spare:].any()      # exactly the boundary's records, stored behind the tree's
+
+
+def test_boundary_that_is_the_surface_shares_its_tree(built):
+    """`dielectric <$ mesh` + `constantMedium rho mesh` (pawn, bunny): the medium's boundary is exactly the surface geometry,
+    so its root IS the surface root and no second tree is built; with the shortcut off (or when the surfaces hold more than
+    the boundary, demo2) the boundary keeps a tree of its own.  Evaluation order and primitive bookkeeping are unchanged."""
+    for name in ("pawn", "bunny_volume"):
+        ctor, _ = scenes.CONFIGS[name]
+        s, w = ctor()
+        a = CompiledScene(w, upload=False)
+        b = CompiledScene(w, upload=False, options=dict(shared_boundary=0))
+        ia, ib = a.info(), b.info()
+        assert ia["n_shared_trees"] == 1 and ib["n_shared_trees"] == 0
+        assert ia["n_prims"] == ib["n_prims"] and ia["n_bvh_nodes"] * 2 == ib["n_bvh_nodes"]      # one tree instead of two equal ones
+        assert np.array_equal(a.handle.get_eval_order(), b.handle.get_eval_order())
+        assert sorted(a.handle.get_bvh()[1].tolist()) == sorted(b.handle.get_bvh()[1].tolist())
+        r = CompiledScene(w, upload=False, options=dict(bvh_reference=1)).info()
+        assert r["n_shared_trees"] == 1
+    s, w = scenes.demo2(width=16, spp=1)
+    assert CompiledScene(w, upload=False).info()["n_shared_trees"] == 0
 
 
 def test_scene_counts(built):
@@ -165,7 +190,9 @@ def test_outermost_material_wins_and_shared_geometry(built):
     assert cs.info()["n_prims"] == 2
     s, w = scenes.pawn(spp=1, width=8)           # the same mesh object is surface and medium boundary
     nodes, canon = CompiledScene(w, upload=False).handle.get_bvh()
-    assert np.array_equal(np.sort(canon[:1200]), np.arange(1200)) and np.array_equal(canon[:1200], canon[1200:])
+    # surface records in the tree's leaf order, then the boundary's copies of the SAME canonical primitives (they share the
+    # surface tree, so they are stored in evaluation order behind it)
+    assert np.array_equal(np.sort(canon[:1200]), np.arange(1200)) and np.array_equal(np.sort(canon[1200:]), np.arange(1200))
 
 
 def test_image_height_round_half_even(built):
