@@ -267,14 +267,30 @@ class SceneHandle:
             pass
 
     # -- serialisation (memoised on object identity: a shared subtree is sent once) --------
+    # Description objects are immutable (frozen dataclasses), so the handle-independent part of each struct - kind, vectors,
+    # scalars, matrix, colours - is filled ONCE and kept on the object as bytes (`_rt_desc`); serialising the same world again
+    # (another RtScene: every `raytrace` call, every bench step) copies those bytes and sets only what belongs to this scene:
+    # child / material / texture ids and array pointers.  demo1 (969 nodes, 462 textures, 484 materials): 15 -> 5 ms.
+    @staticmethod
+    def _cached(obj, cls, fill):
+        raw = obj.__dict__.get("_rt_desc")
+        if raw is None:
+            d = cls()
+            fill(d)
+            raw = bytes(d)
+            object.__setattr__(obj, "_rt_desc", raw)      # frozen dataclass: a private cache, not a field
+        return cls.from_buffer_copy(raw)
+
     def add_texture(self, tex) -> int:
         key = id(tex)
         if key in self._tex_ids:
             return self._tex_ids[key]
-        d = RtTextureDesc()
-        d.kind = int(tex.kind)
-        d.i0, d.i1, d.freq = tex.i0, tex.i1, tex.freq
-        d.c0, d.c1, d.shift, d.dir = _d3(tex.c0), _d3(tex.c1), _d3(tex.shift), _d3(tex.dir)
+
+        def fill(d):
+            d.kind = int(tex.kind)
+            d.i0, d.i1, d.freq = tex.i0, tex.i1, tex.freq
+            d.c0, d.c1, d.shift, d.dir = _d3(tex.c0), _d3(tex.c1), _d3(tex.shift), _d3(tex.dir)
+        d = self._cached(tex, RtTextureDesc, fill)
         if tex.image is not None:
             img = np.ascontiguousarray(tex.image, dtype=np.float32)
             self._keep.append(img)
@@ -290,10 +306,12 @@ class SceneHandle:
         key = id(mat)
         if key in self._mat_ids:
             return self._mat_ids[key]
-        d = RtMaterialDesc()
-        d.kind = int(mat.kind)
+
+        def fill(d):
+            d.kind = int(mat.kind)
+            d.param = float(mat.param)
+        d = self._cached(mat, RtMaterialDesc, fill)
         d.texture = self.add_texture(mat.texture) if mat.texture is not None else 0
-        d.param = float(mat.param)
         out = C.c_uint32()
         check(self._L.rt_scene_add_material(self._h, C.byref(d), C.byref(out)))
         self._keep.append(mat)
@@ -305,23 +323,25 @@ class SceneHandle:
         if key in self._node_ids:
             return self._node_ids[key]
         child_ids = [self.add_node(c) for c in g.children]
-        d = RtNodeDesc()
-        d.kind = int(g.kind)
+
+        def fill(d):
+            d.kind = int(g.kind)
+            for k, vec in enumerate(g.v[:3]):
+                d.v[k] = _d3(vec)
+            for k, sc in enumerate(g.s[:2]):
+                d.s[k] = float(sc)
+            for k, uv in enumerate(g.uv[:3]):
+                d.uv[k][0], d.uv[k][1] = float(uv[0]), float(uv[1])
+            if g.m is not None:
+                flat = g.m.a.reshape(-1)
+                for k in range(16):
+                    d.m[k] = float(flat[k])
+        d = self._cached(g, RtNodeDesc, fill)
         d.n_children = len(child_ids)
         if child_ids:
             arr = (C.c_uint32 * len(child_ids))(*child_ids)
             self._keep.append(arr)
             d.children = C.cast(arr, C.POINTER(C.c_uint32))
-        for k, vec in enumerate(g.v[:3]):
-            d.v[k] = _d3(vec)
-        for k, sc in enumerate(g.s[:2]):
-            d.s[k] = float(sc)
-        for k, uv in enumerate(g.uv[:3]):
-            d.uv[k][0], d.uv[k][1] = float(uv[0]), float(uv[1])
-        if g.m is not None:
-            flat = g.m.a.reshape(-1)
-            for k in range(16):
-                d.m[k] = float(flat[k])
         if g.mesh is not None:
             m = g.mesh
             self._keep.append(m)
