@@ -158,25 +158,8 @@ __device__ __forceinline__ uint32_t tiled_pixel(uint32_t p, uint32_t W, uint32_t
 }
 
 struct NewPath { RayT ray; uint32_t pixel; uint32_t sample_lo; };
-// work item → camera path (Ray.hs:157-172,229): item = local sample index * n_pixels + position in the pass
-__device__ __forceinline__ NewPath new_camera_path(const RenderArgs& A, unsigned long long item) {
-  unsigned long long s_local;
-  uint32_t pixel;
-  if (A.kblock <= 1u) {
-    s_local = item / A.n_pixels;
-    pixel = (uint32_t)(item - s_local * A.n_pixels);
-  } else if (item < A.kfull_items) {
-    const uint32_t per_blk = A.kblock * A.n_pixels;                   // < 2^32: checked on the host
-    const unsigned long long blk = item / per_blk;
-    const uint32_t rem = (uint32_t)(item - blk * per_blk);
-    pixel = rem / A.kblock;
-    s_local = blk * A.kblock + (rem - pixel * A.kblock);
-  } else {                                                           // last block of samples: ktail = n_samples % K per pixel
-    const uint32_t idx = (uint32_t)(item - A.kfull_items);
-    pixel = idx / A.ktail;
-    s_local = A.kfull_items / A.n_pixels + (idx - pixel * A.ktail);
-  }
-  if (A.tile) pixel = tiled_pixel(pixel, (uint32_t)A.cam.W, (uint32_t)A.cam.H);
+// camera path of (pixel, local sample index) (Ray.hs:157-172,229)
+__device__ __forceinline__ NewPath make_camera_path(const RenderArgs& A, uint32_t pixel, unsigned long long s_local) {
   const unsigned long long sample = A.first_sample + s_local;
   const uint4 r0 = rng4(A.key, pixel, sample, 0, RNG_RAYGEN);
   float lu = 0.f, lv = 0.f;
@@ -186,6 +169,52 @@ __device__ __forceinline__ NewPath new_camera_path(const RenderArgs& A, unsigned
     lv = u01(r1.y);
   }
   return NewPath{camera_ray(A.cam, pixel, u01(r0.x), lu, lv, u01(r0.y), u01(r0.z)), pixel, (uint32_t)sample};
+}
+// Work item -> (position in the pass, local sample index).  kblock <= 1: item = sample pass * n_pixels + position.  kblock = K:
+// K consecutive items are K consecutive samples of ONE position (a bijection either way; RenderArgs::kblock).
+struct ItemCursor {
+  uint32_t pos;                 // position in the sample pass (pixel before the 8x4 tile mapping)
+  uint32_t j, kcur;             // sample within the current block of kcur samples
+  unsigned long long blk_s0;    // first local sample index of the current block
+  __device__ __forceinline__ unsigned long long s_local() const { return blk_s0 + j; }
+};
+__device__ __forceinline__ ItemCursor decode_item(const RenderArgs& A, unsigned long long item) {
+  ItemCursor c;
+  if (A.kblock <= 1u) {
+    const unsigned long long pass = item / A.n_pixels;
+    c.pos = (uint32_t)(item - pass * A.n_pixels);
+    c.j = 0u; c.kcur = 1u; c.blk_s0 = pass;
+  } else if (item < A.kfull_items) {
+    const uint32_t per_blk = A.kblock * A.n_pixels;                   // < 2^32: checked on the host
+    const unsigned long long blk = item / per_blk;
+    const uint32_t rem = (uint32_t)(item - blk * per_blk);
+    c.pos = rem / A.kblock;
+    c.j = rem - c.pos * A.kblock; c.kcur = A.kblock; c.blk_s0 = blk * A.kblock;
+  } else {                                                           // last block of samples: ktail = n_samples % K per pixel
+    const uint32_t idx = (uint32_t)(item - A.kfull_items);
+    c.pos = idx / A.ktail;
+    c.j = idx - c.pos * A.ktail; c.kcur = A.ktail; c.blk_s0 = A.kfull_items / A.n_pixels;
+  }
+  return c;
+}
+// the next work item, without divisions; returns true when the position (hence the pixel) changed
+__device__ __forceinline__ bool advance_item(const RenderArgs& A, ItemCursor& c) {
+  if (++c.j < c.kcur) return false;
+  c.j = 0u;
+  if (++c.pos == A.n_pixels) {          // next block of samples
+    c.pos = 0u;
+    c.blk_s0 += c.kcur;
+    if (A.kblock > 1u && c.blk_s0 * A.n_pixels >= A.kfull_items) c.kcur = A.ktail;
+  }
+  return true;
+}
+__device__ __forceinline__ uint32_t item_pixel(const RenderArgs& A, const ItemCursor& c) {
+  return A.tile ? tiled_pixel(c.pos, (uint32_t)A.cam.W, (uint32_t)A.cam.H) : c.pos;
+}
+// work item -> camera path
+__device__ __forceinline__ NewPath new_camera_path(const RenderArgs& A, unsigned long long item) {
+  const ItemCursor c = decode_item(A, item);
+  return make_camera_path(A, item_pixel(A, c), c.s_local());
 }
 
 // Camera rays of the refilled queue tail.  With A.cull (the scene has a finite world box) a camera ray that misses the box
@@ -239,12 +268,17 @@ __global__ void __launch_bounds__(kRaygenBlock) k_raygen(Ctl* __restrict__ ctl, 
   };
   for (uint32_t cbase = blockIdx.x * blockDim.x; cbase < chunks; cbase += gridDim.x * blockDim.x) {   // uniform per block
     const uint32_t c = cbase + threadIdx.x;
+    // index arithmetic once per chunk (a 64-bit division and the tile mapping's four divisions), then increments
+    ItemCursor cur{};
+    uint32_t cur_pixel = 0u;
+    if (c < chunks) { cur = decode_item(A, item0 + (unsigned long long)c * K); cur_pixel = item_pixel(A, cur); }
     for (uint32_t k = 0; k < K; k++) {
       const uint32_t t = c * K + k;
       bool keep = false;
       NewPath np{};
       if (c < chunks && t < fill) {
-        np = new_camera_path(A, item0 + t);
+        if (k != 0u && advance_item(A, cur)) cur_pixel = item_pixel(A, cur);
+        np = make_camera_path(A, cur_pixel, cur.s_local());
         f3 inv;
         inv.x = fabsf(np.ray.d.x) > 1e-30f ? __frcp_rn(np.ray.d.x) : copysignf(1e30f, np.ray.d.x);
         inv.y = fabsf(np.ray.d.y) > 1e-30f ? __frcp_rn(np.ray.d.y) : copysignf(1e30f, np.ray.d.y);
