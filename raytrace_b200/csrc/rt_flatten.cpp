@@ -25,6 +25,8 @@
 #include <cstring>
 #include <functional>
 #include <limits>
+#include <unordered_map>
+#include <unordered_set>
 
 #include "rt_host.h"
 
@@ -148,6 +150,8 @@ struct Builder {
   std::vector<uint32_t> memo_chain;
   uint32_t memo_chain_id = kNone;
   uint32_t memo_node = kNone, memo_xf = kNone, memo_canon = 0, memo_geom = 0;   // last (node, xform) looked up
+  struct MeshMemo { uint32_t p0, p1; int r0, r1, root; };          // prims / rnodes ranges of a walked mesh, and its tree's root
+  std::map<std::pair<uint32_t, uint32_t>, MeshMemo> mesh_memo;      // (desc node, xform id)
   struct MediumRec { double density; int rtree; uint32_t material; };
   std::vector<MediumRec> media;
   std::vector<char> mat_used, tex_used;
@@ -394,6 +398,29 @@ struct Builder {
       case RT_NODE_MESH: {  // triangleMesh, Geometry.hs:288-294
         size_t nf = n.faces.size() / 6;
         if (nf == 0) fail(RT_ERR_EMPTY_BVH, "bvhTree: empty list");
+        // The same mesh under the same transform again (`dielectric <$ mesh` + `constantMedium rho mesh`): its triangles and
+        // its reference-policy tree (a sort at every level) are those of the first visit - clone them, new material only.
+        const uint32_t xf_id = xform_id(xf);
+        auto seen = mesh_memo.find({id, xf_id});
+        if (seen != mesh_memo.end()) {
+          const MeshMemo mm = seen->second;
+          const uint32_t dp = (uint32_t)prims.size() - mm.p0;
+          const int dr = (int)rnodes.size() - mm.r0;
+          prims.reserve(prims.size() + (mm.p1 - mm.p0));
+          for (uint32_t i = mm.p0; i < mm.p1; i++) { prims.push_back(prims[i]); prims.back().material = material; }
+          rnodes.reserve(rnodes.size() + (size_t)(mm.r1 - mm.r0));
+          for (int r = mm.r0; r < mm.r1; r++) {
+            rnodes.push_back(rnodes[r]);
+            RNode& c = rnodes.back();
+            if (c.kind == RNode::LEAF) c.prim += dp;
+            else for (int& ch : c.children) ch += dr;
+          }
+          result = mm.root + dr;
+          rb = rnodes[result].ref_box;
+          break;
+        }
+        const uint32_t memo_p0 = (uint32_t)prims.size();
+        const int memo_r0 = (int)rnodes.size();
         static const double def_uv[3][2] = {{0, 0}, {1, 0}, {0, 1}};
         std::vector<int> tris;
         tris.reserve(nf);
@@ -416,6 +443,7 @@ struct Builder {
         }
         result = bvh_tree(std::move(tris));
         rb = rnodes[result].ref_box;
+        mesh_memo[{id, xf_id}] = MeshMemo{memo_p0, (uint32_t)prims.size(), memo_r0, (int)rnodes.size(), result};
         break;
       }
       case RT_NODE_GROUP:
@@ -845,8 +873,7 @@ struct Builder {
       const HPrim& p = prims[ps[0]];
       return p.type == PRIM_SPHERE && p.r > 0 && !(p.flags & PRIM_FLAG_MOVING);
     }
-    // vertices are identified by their exact coordinates (sort + unique: O(n log n), a million triangles in a fraction
-    // of a second), directed edges by the pair of vertex ids packed into 64 bits
+    // vertices are identified by their exact coordinates, directed edges by the pair of vertex ids (hash maps: O(n))
     const uint32_t xf0 = prims[ps[0]].xform;
     std::vector<std::array<double, 3>> pts;
     pts.reserve(3 * ps.size());
@@ -860,21 +887,32 @@ struct Builder {
       }
       vol6 += dot(p.corner[0], cross(p.corner[1], p.corner[2]));
     }
-    std::vector<std::array<double, 3>> uniq(pts);
-    std::sort(uniq.begin(), uniq.end());
-    uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
-    std::vector<uint64_t> edges;
-    edges.reserve(pts.size());
+    // vertex ids by exact coordinates (hash of the three bit patterns), directed edges as id pairs packed into 64 bits
+    struct KeyHash {
+      size_t operator()(const std::array<uint64_t, 3>& k) const {
+        uint64_t h = k[0] * 0x9e3779b97f4a7c15ULL;
+        h ^= (k[1] + 0x9e3779b97f4a7c15ULL + (h << 6) + (h >> 2)) * 0xbf58476d1ce4e5b9ULL;
+        h ^= (k[2] + 0x94d049bb133111ebULL + (h << 6) + (h >> 2)) * 0xff51afd7ed558ccdULL;
+        return (size_t)(h ^ (h >> 31));
+      }
+    };
+    std::unordered_map<std::array<uint64_t, 3>, uint32_t, KeyHash> ids;
+    ids.reserve(pts.size());
+    std::unordered_set<uint64_t> edges;
+    edges.reserve(pts.size() * 2);
     for (size_t t = 0; t < pts.size(); t += 3) {
       uint64_t id[3];
-      for (int k = 0; k < 3; k++) id[k] = (uint64_t)(std::lower_bound(uniq.begin(), uniq.end(), pts[t + k]) - uniq.begin());
+      for (int k = 0; k < 3; k++) {
+        std::array<uint64_t, 3> key;
+        std::memcpy(key.data(), pts[t + k].data(), 24);
+        id[k] = ids.emplace(key, (uint32_t)ids.size()).first->second;
+      }
       if (id[0] == id[1] || id[1] == id[2] || id[0] == id[2]) return false;   // degenerate triangle
-      for (int k = 0; k < 3; k++) edges.push_back(id[k] << 32 | id[(k + 1) % 3]);
+      for (int k = 0; k < 3; k++)
+        if (!edges.insert(id[k] << 32 | id[(k + 1) % 3]).second) return false;     // a directed edge used twice
     }
-    std::sort(edges.begin(), edges.end());
-    if (std::adjacent_find(edges.begin(), edges.end()) != edges.end()) return false;       // a directed edge used twice
-    for (uint64_t e : edges)                                                                // ... and its reverse exactly once
-      if (!std::binary_search(edges.begin(), edges.end(), (e << 32) | (e >> 32))) return false;
+    for (uint64_t e : edges)                                                        // ... and its reverse exactly once
+      if (!edges.count((e << 32) | (e >> 32))) return false;
     // orientation in WORLD space: a reflecting instance transform (det < 0) turns the surface inside out
     const double* M = xforms[xf0].fwd.M;
     const double det = M[0] * (M[4] * M[8] - M[5] * M[7]) - M[1] * (M[3] * M[8] - M[5] * M[6]) + M[2] * (M[3] * M[7] - M[4] * M[6]);
