@@ -191,7 +191,12 @@ int32_t rt_scene_add_texture(RtScene* sp, const RtTextureDesc* d, uint32_t* id) 
   t.d.image = nullptr;
   if (d->kind == RT_TEX_IMAGE) {
     if (!d->image || d->width <= 0 || d->height <= 0) { set_error("imageTexture: null or empty image"); return RT_ERR_INVALID_ARG; }
-    t.image.assign(d->image, d->image + (size_t)d->width * d->height * 3);
+    // stored as float4 texels right away (the device format): ONE pass over the image, commit only memcpy's it
+    const size_t n = (size_t)d->width * d->height;
+    t.image.resize(n * 4);
+    const float* src = d->image;
+    float* dst = t.image.data();
+    for (size_t k = 0; k < n; k++, dst += 4, src += 3) { dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2]; dst[3] = 0.f; }
   }
   *id = (uint32_t)s.textures.size();
   s.textures.push_back(std::move(t));

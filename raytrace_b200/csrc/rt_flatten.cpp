@@ -1209,12 +1209,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
         if (t.d.width <= 0 || t.d.height <= 0 || t.image.empty()) b.fail(RT_ERR_INVALID_ARG, "imageTexture: empty image");
         d.w = t.d.width; d.h = t.d.height;
         d.image_offset = (uint32_t)(fs.texels.size() / 4);
-        size_t n = (size_t)d.w * d.h;
-        const size_t at = fs.texels.size();
-        fs.texels.resize(at + n * 4);
-        float* dst = fs.texels.data() + at;
-        const float* src = t.image.data();
-        for (size_t k = 0; k < n; k++, dst += 4, src += 3) { dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2]; dst[3] = 0.f; }
+        fs.texels.insert(fs.texels.end(), t.image.begin(), t.image.end());      // already float4 texels
       }
       if (t.d.kind == RT_TEX_NOISE || t.d.kind == RT_TEX_MARBLE) fs.has_noise = 1;
     }

@@ -18,7 +18,7 @@ void set_error(const std::string& msg);  // thread-local last-error string
 
 struct HostTexture {
   RtTextureDesc d;
-  std::vector<float> image;  // w*h*3 linear floats (copied at add time)
+  std::vector<float> image;  // w*h float4 texels {r, g, b, 0}, linear (converted at add time)
 };
 
 struct HostNode {  // one node of the description tree, copied at add time

@@ -1270,12 +1270,19 @@ static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
       {f.texels.data(), f.texels.size() * sizeof(float), 0}, {f.canonical.data(), f.canonical.size() * sizeof(uint32_t), 0},
       {f.noise_grad.data(), f.noise_grad.size() * sizeof(float), 0}, {f.noise_perm.data(), f.noise_perm.size(), 0},
       {f.ref_order.data(), f.ref_order.size() * sizeof(uint32_t), 0}};
+  // arena layout: the small sections first (they travel in ONE staged copy), large ones (image texels: 8 MB for demo2) behind
+  // them - those are copied straight from their vectors, with no zero-filled staging image and no extra host pass
+  constexpr size_t kDirect = 256u << 10;
   size_t total_bytes = 0;
-  for (Sec& x : secs) { x.off = total_bytes; total_bytes += (x.bytes + 255) / 256 * 256 + 256; }
-  std::vector<unsigned char> staging(total_bytes, 0);
-  for (const Sec& x : secs) if (x.bytes) std::memcpy(staging.data() + x.off, x.src, x.bytes);
+  for (Sec& x : secs) if (x.bytes < kDirect) { x.off = total_bytes; total_bytes += (x.bytes + 255) / 256 * 256 + 256; }
+  const size_t staged_end = total_bytes;
+  for (Sec& x : secs) if (x.bytes >= kDirect) { x.off = total_bytes; total_bytes += (x.bytes + 255) / 256 * 256 + 256; }
+  std::vector<unsigned char> staging(staged_end, 0);
+  for (const Sec& x : secs) if (x.bytes && x.bytes < kDirect) std::memcpy(staging.data() + x.off, x.src, x.bytes);
   cudaError_t e = cudaMalloc(&ds->arena, total_bytes);
-  if (e == cudaSuccess) e = cudaMemcpy(ds->arena, staging.data(), total_bytes, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess && staged_end) e = cudaMemcpy(ds->arena, staging.data(), staged_end, cudaMemcpyHostToDevice);
+  for (const Sec& x : secs)
+    if (e == cudaSuccess && x.bytes >= kDirect) e = cudaMemcpy(static_cast<unsigned char*>(ds->arena) + x.off, x.src, x.bytes, cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
     set_error(std::string("scene upload failed: ") + cudaGetErrorString(e));
     destroy_device_scene(ds);
