@@ -172,12 +172,19 @@ raytrace CameraSettings{..} world gen = unsafePerformIO $ do
       , camDefocus = cs_defocusAngle, camFocus = cs_focusDist, camBg0 = t3 bg0, camBg1 = t3 bg1, camBgKind = bgKind
       , camWidth = fromIntegral w, camSpp = fromIntegral cs_samplesPerPixel, camDepth = fromIntegral cs_maxRecursionDepth
       , camTargets = pt, camNTargets = fromIntegral nt }
-    c_render scene 0 cam seed 0 (fromIntegral cs_samplesPerPixel) o nullPtr nullPtr >>= check
+    -- every visible GPU renders its share of the samples and DMA-copies its slice of the reduced image into the buffer
+    -- (one GPU: the same as rt_render scene 0 ...)
+    c_render_multi allGpus scene cam seed o nullPtr nullPtr >>= check
   _ <- c_scene_destroy scene
   px <- withForeignPtr buf (peekArray (w * h * 3))
   let img = A.fromList A.Seq (map realToFrac px) :: A.Vector U Double
   pure $ A.makeArray A.Par (A.Sz2 h w) $ \(j :. i) ->           -- index (j :. i), row 0 = top (Ray.hs:238)
     let k = (j * w + i) * 3 in V3 (img A.! k) (img A.! (k + 1)) (img A.! (k + 2))
+
+-- | The process-wide context over all sm_100 GPUs (rt_context_create NULL 0), made on first use and kept until exit.
+allGpus :: Ptr RtContext
+allGpus = unsafePerformIO $ alloca $ \pp -> c_context_create nullPtr 0 pp >>= check >> peek pp
+{-# NOINLINE allGpus #-}
 
 serialiseMaterial :: Ptr RtScene -> Material -> IO Word32
 serialiseMaterial scene m = do

@@ -15,6 +15,7 @@ import Foreign.C.Types
 
 data RtScene   -- opaque handle
 data RtMesh    -- opaque handle
+data RtContext -- opaque handle: a set of GPUs driven by one process
 
 -- | Status codes (@RtStatus@).
 rtOk, rtErrEmptyBvh, rtErrUserDefined :: Int32
@@ -148,6 +149,15 @@ foreign import ccall safe   "rt_scene_commit"           c_scene_commit   :: Ptr 
 foreign import ccall safe   "rt_scene_upload"           c_scene_upload   :: Ptr RtScene -> Int32 -> IO Int32
 foreign import ccall safe   "rt_render"                 c_render         :: Ptr RtScene -> Int32 -> Ptr () -> Word64 -> Word64 -> Word64
                                                                          -> Ptr CFloat -> Ptr CFloat -> Ptr () -> IO Int32
+-- one call, the whole machine (Ray.hs:121,238): a context over every visible GPU; rt_render_multi splits the samples per pixel
+-- across its devices and assembles the image inside the library (reduce-scatter over NVLink, every GPU copies its slice)
+foreign import ccall safe   "rt_context_create"         c_context_create :: Ptr Int32 -> Int32 -> Ptr (Ptr RtContext) -> IO Int32   -- nullPtr 0 = all sm_100 GPUs
+foreign import ccall safe   "rt_context_destroy"        c_context_destroy :: Ptr RtContext -> IO Int32
+foreign import ccall safe   "rt_render_multi"           c_render_multi   :: Ptr RtContext -> Ptr RtScene -> Ptr () -> Word64
+                                                                         -> Ptr CFloat -> Ptr CFloat -> Ptr () -> IO Int32
+-- tuning / A-B options are a struct (RtOptions), never environment variables
+foreign import ccall unsafe "rt_options_init"           c_options_init   :: Ptr () -> IO Int32
+foreign import ccall safe   "rt_scene_set_options"      c_scene_set_options :: Ptr RtScene -> Ptr () -> IO Int32
 foreign import ccall safe   "rt_host_alloc"             c_host_alloc     :: CSize -> Ptr (Ptr ()) -> IO Int32
 foreign import ccall safe   "&rt_host_free"             p_host_free      :: FunPtr (Ptr CFloat -> IO ())   -- ForeignPtr finaliser (status ignored)
 foreign import ccall safe   "rt_probe_primary"          c_probe_primary  :: Ptr RtScene -> Int32 -> Ptr () -> Double -> Ptr Word32 -> Ptr CFloat -> IO Int32
