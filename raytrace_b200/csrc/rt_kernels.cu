@@ -50,6 +50,20 @@ struct DevBuf {                   // cudaMalloc'ed scratch freed on every exit p
   ~DevBuf() { if (p) cudaFree(p); }
 };
 
+// No C++ exception crosses the C ABI: an entry point's body runs inside this guard (std::bad_alloc from a vector, ...).
+template <class F>
+static int32_t abi_guard(const char* what, F&& body) {
+  try {
+    return body();
+  } catch (const std::exception& e) {
+    set_error(std::string(what) + ": " + e.what());
+    return RT_ERR_CUDA;
+  } catch (...) {
+    set_error(std::string(what) + ": unknown C++ exception");
+    return RT_ERR_CUDA;
+  }
+}
+
 constexpr int kTraverseBlock = 128;
 constexpr int kShadeBlock = 256;
 #ifndef RT_SHADE_MINB
@@ -1250,9 +1264,14 @@ static int32_t check_device(int device) {
 
 static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
   if (!s.committed) { set_error("scene not committed"); return RT_ERR_NOT_COMMITTED; }
-  std::lock_guard<std::mutex> lock(s.devices_mu);
-  auto it = s.devices.find(device);
-  if (it != s.devices.end()) { *out = it->second; RT_CUDA(cudaSetDevice(device)); return RT_OK; }
+  {
+    std::lock_guard<std::mutex> lock(s.devices_mu);
+    auto it = s.devices.find(device);
+    if (it != s.devices.end()) { *out = it->second; RT_CUDA(cudaSetDevice(device)); return RT_OK; }
+  }
+  // The upload itself runs WITHOUT the lock: rt_render_multi uploads a fresh scene to all its devices from one thread per
+  // device, and every GPU has its own PCIe link (8 x 1.1 ms one after the other for demo2's 8.8 MB otherwise).  Two threads
+  // that race for the SAME device both upload; the loser's copy is dropped below.
   int32_t st = check_device(device);
   if (st != RT_OK) return st;
   RT_CUDA(cudaSetDevice(device));
@@ -1332,7 +1351,17 @@ static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
   d.n_prims = (uint32_t)f.canonical.size();
   d.moving_first = f.moving_first;
   d.moving_count = f.moving_count;
-  s.devices[device] = ds;
+  {
+    std::lock_guard<std::mutex> lock(s.devices_mu);
+    auto it = s.devices.find(device);
+    if (it != s.devices.end()) {          // another thread uploaded this device meanwhile: keep its copy
+      destroy_device_scene(ds);
+      RT_CUDA(cudaSetDevice(device));
+      *out = it->second;
+      return RT_OK;
+    }
+    s.devices[device] = ds;
+  }
   *out = ds;
   return RT_OK;
 }
@@ -1732,15 +1761,22 @@ int32_t rt_device_count(int32_t* n) {
   return RT_OK;
 }
 
+static int32_t rt_scene_upload_impl(RtScene* sp, int32_t device);
 int32_t rt_scene_upload(RtScene* sp, int32_t device) {
+  return abi_guard("rt_scene_upload", [&]() { return rt_scene_upload_impl(sp, device); });
+}
+static int32_t rt_scene_upload_impl(RtScene* sp, int32_t device) {
   if (!sp) { set_error("null scene"); return RT_ERR_INVALID_ARG; }
   DeviceGuard guard;
   DeviceScene* ds = nullptr;
   return get_device_scene(*reinterpret_cast<Scene*>(sp), device, &ds);
 }
 
-int32_t rt_render_device(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample,
-                         uint64_t n_samples, float* d_sum, float* d_sumsq, void* cuda_stream, RtStats* stats) {
+static int32_t rt_render_device_impl(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample, uint64_t n_samples, float* d_sum, float* d_sumsq, void* cuda_stream, RtStats* stats);
+int32_t rt_render_device(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample, uint64_t n_samples, float* d_sum, float* d_sumsq, void* cuda_stream, RtStats* stats) {
+  return abi_guard("rt_render_device", [&]() { return rt_render_device_impl(sp, device, rc, seed, first_sample, n_samples, d_sum, d_sumsq, cuda_stream, stats); });
+}
+static int32_t rt_render_device_impl(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample, uint64_t n_samples, float* d_sum, float* d_sumsq, void* cuda_stream, RtStats* stats) {
   if (!sp || !rc || !d_sum) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
   DeviceGuard guard;
   Scene& s = *reinterpret_cast<Scene*>(sp);
@@ -1825,8 +1861,11 @@ static bool is_pinned_host(const void* p, size_t bytes) {
   return a0.type == cudaMemoryTypeHost && a1.type == cudaMemoryTypeHost;
 }
 
-int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample,
-                  uint64_t n_samples, float* rgb_out, float* rgb_sumsq_out, RtStats* stats) {
+static int32_t rt_render_impl(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample, uint64_t n_samples, float* rgb_out, float* rgb_sumsq_out, RtStats* stats);
+int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample, uint64_t n_samples, float* rgb_out, float* rgb_sumsq_out, RtStats* stats) {
+  return abi_guard("rt_render", [&]() { return rt_render_impl(sp, device, rc, seed, first_sample, n_samples, rgb_out, rgb_sumsq_out, stats); });
+}
+static int32_t rt_render_impl(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed, uint64_t first_sample, uint64_t n_samples, float* rgb_out, float* rgb_sumsq_out, RtStats* stats) {
   if (!sp || !rc || !rgb_out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
   DeviceGuard guard;
   Scene& s = *reinterpret_cast<Scene*>(sp);
@@ -1880,7 +1919,11 @@ int32_t rt_render(RtScene* sp, int32_t device, const RtCamera* rc, uint64_t seed
   return RT_OK;
 }
 
+static int32_t rt_probe_primary_impl(RtScene* sp, int32_t device, const RtCamera* rc, double time, uint32_t* ids, float* ts);
 int32_t rt_probe_primary(RtScene* sp, int32_t device, const RtCamera* rc, double time, uint32_t* ids, float* ts) {
+  return abi_guard("rt_probe_primary", [&]() { return rt_probe_primary_impl(sp, device, rc, time, ids, ts); });
+}
+static int32_t rt_probe_primary_impl(RtScene* sp, int32_t device, const RtCamera* rc, double time, uint32_t* ids, float* ts) {
   if (!sp || !rc || !ids || !ts) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
   DeviceGuard guard;
   Scene& s = *reinterpret_cast<Scene*>(sp);
@@ -1908,7 +1951,11 @@ int32_t rt_probe_primary(RtScene* sp, int32_t device, const RtCamera* rc, double
   return RT_OK;
 }
 
+static int32_t rt_probe_surface_impl(RtScene* sp, int32_t device, const RtCamera* rc, double time, float* out);
 int32_t rt_probe_surface(RtScene* sp, int32_t device, const RtCamera* rc, double time, float* out) {
+  return abi_guard("rt_probe_surface", [&]() { return rt_probe_surface_impl(sp, device, rc, time, out); });
+}
+static int32_t rt_probe_surface_impl(RtScene* sp, int32_t device, const RtCamera* rc, double time, float* out) {
   if (!sp || !rc || !out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
   DeviceGuard guard;
   Scene& s = *reinterpret_cast<Scene*>(sp);
@@ -1965,7 +2012,11 @@ int32_t rt_reduce_image(int32_t device, const void* multicast_ptr, const void* c
   return RT_OK;
 }
 
+static int32_t rt_tonemap_u8_impl(int32_t device, const float* rgb, int32_t n_pixels, int32_t mode, uint8_t* out);
 int32_t rt_tonemap_u8(int32_t device, const float* rgb, int32_t n_pixels, int32_t mode, uint8_t* out) {
+  return abi_guard("rt_tonemap_u8", [&]() { return rt_tonemap_u8_impl(device, rgb, n_pixels, mode, out); });
+}
+static int32_t rt_tonemap_u8_impl(int32_t device, const float* rgb, int32_t n_pixels, int32_t mode, uint8_t* out) {
   if (!rgb || !out || n_pixels < 0) { set_error("bad argument"); return RT_ERR_INVALID_ARG; }
   int32_t st = check_device(device);
   if (st != RT_OK) return st;
@@ -2046,7 +2097,11 @@ static int32_t static_scratch_for(int device, unsigned char** ptr, int* sms) {
 
 extern "C" {
 
+static int32_t rt_tonemap_u8_static_impl(int32_t device, const float* rgb, int32_t n_pixels, int32_t mode, uint8_t* out, void* cuda_stream);
 int32_t rt_tonemap_u8_static(int32_t device, const float* rgb, int32_t n_pixels, int32_t mode, uint8_t* out, void* cuda_stream) {
+  return abi_guard("rt_tonemap_u8_static", [&]() { return rt_tonemap_u8_static_impl(device, rgb, n_pixels, mode, out, cuda_stream); });
+}
+static int32_t rt_tonemap_u8_static_impl(int32_t device, const float* rgb, int32_t n_pixels, int32_t mode, uint8_t* out, void* cuda_stream) {
   if (!rgb || !out || n_pixels < 0) { set_error("rt_tonemap_u8_static: bad argument"); return RT_ERR_INVALID_ARG; }
   if ((size_t)n_pixels > kStaticTonemapMaxPixels) {
     set_error("rt_tonemap_u8_static: " + std::to_string(n_pixels) + " pixels exceed the static scratch array (at most " +

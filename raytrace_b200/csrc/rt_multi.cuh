@@ -293,7 +293,17 @@ using namespace rtb;
 
 extern "C" {
 
+static int32_t context_create_impl(const int32_t* devices, int32_t n_devices, RtContext** out);
 int32_t rt_context_create(const int32_t* devices, int32_t n_devices, RtContext** out) {
+  try {
+    return context_create_impl(devices, n_devices, out);
+  } catch (const std::exception& e) {
+    set_error(std::string("rt_context_create: ") + e.what());
+    if (out) *out = nullptr;
+    return RT_ERR_CUDA;
+  }
+}
+static int32_t context_create_impl(const int32_t* devices, int32_t n_devices, RtContext** out) {
   if (!out || n_devices < 0 || (n_devices > 0 && !devices)) { set_error("rt_context_create: bad argument"); return RT_ERR_INVALID_ARG; }
   *out = nullptr;
   DeviceGuard guard;
@@ -367,8 +377,25 @@ int32_t rt_context_info(const RtContext* cp, RtContextInfo* info) {
   return RT_OK;
 }
 
+static int32_t render_multi_impl(RtContext* cp, RtScene* sp, const RtCamera* rc, uint64_t seed, float* rgb_out, float* rgb_sumsq_out,
+                                 RtStats* stats);
+
+// no C++ exception crosses the ABI: thread creation (std::system_error) and allocations (std::bad_alloc) are caught here
 int32_t rt_render_multi(RtContext* cp, RtScene* sp, const RtCamera* rc, uint64_t seed, float* rgb_out, float* rgb_sumsq_out,
                         RtStats* stats) {
+  try {
+    return render_multi_impl(cp, sp, rc, seed, rgb_out, rgb_sumsq_out, stats);
+  } catch (const std::exception& e) {
+    set_error(std::string("rt_render_multi: ") + e.what());
+    return RT_ERR_CUDA;
+  } catch (...) {
+    set_error("rt_render_multi: unknown C++ exception");
+    return RT_ERR_CUDA;
+  }
+}
+
+static int32_t render_multi_impl(RtContext* cp, RtScene* sp, const RtCamera* rc, uint64_t seed, float* rgb_out, float* rgb_sumsq_out,
+                                 RtStats* stats) {
   if (!cp || !sp || !rc || !rgb_out) { set_error("null argument"); return RT_ERR_INVALID_ARG; }
   DeviceGuard guard;
   Context& c = *reinterpret_cast<Context*>(cp);
@@ -394,7 +421,7 @@ int32_t rt_render_multi(RtContext* cp, RtScene* sp, const RtCamera* rc, uint64_t
   std::vector<RtStats> part(G);
   auto work = [&](int g) {
     CtxDevice& d = c.dev[g];
-    auto run = [&]() -> int32_t {
+    auto run_unchecked = [&]() -> int32_t {
       DeviceScene* ds = nullptr;
       int32_t r = get_device_scene(s, d.device, &ds);       // sets the device
       if (r != RT_OK) return r;
@@ -416,13 +443,25 @@ int32_t rt_render_multi(RtContext* cp, RtScene* sp, const RtCamera* rc, uint64_t
       RT_CUDA(cudaEventRecord(d.done, d.stream));
       return RT_OK;
     };
+    auto run = [&]() -> int32_t {          // an exception must not leave a worker thread (std::terminate)
+      try { return run_unchecked(); }
+      catch (const std::exception& e) { set_error(std::string("worker: ") + e.what()); return RT_ERR_CUDA; }
+      catch (...) { set_error("worker: unknown C++ exception"); return RT_ERR_CUDA; }
+    };
     status[g] = run();
     if (status[g] != RT_OK) errors[g] = rt_last_error();     // the message is thread-local: carry it to the caller
   };
   if (G == 1) work(0);
   else {
     std::vector<std::thread> threads;
-    for (int g = 0; g < G; g++) threads.emplace_back(work, g);
+    threads.reserve(G);
+    try {
+      for (int g = 0; g < G; g++) threads.emplace_back(work, g);
+    } catch (...) {                        // could not start a thread: wait for the ones that run, then report
+      for (auto& t : threads) t.join();
+      for (CtxDevice& d : c.dev) { cudaSetDevice(d.device); cudaStreamSynchronize(d.stream); }
+      throw;
+    }
     for (auto& t : threads) t.join();
   }
   for (int g = 0; g < G; g++)
