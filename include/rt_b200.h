@@ -219,7 +219,7 @@ typedef struct RtOptions {
   int32_t tail_batch;        /* iterations per host round trip once all paths have started (default 3) */
   int32_t node_burst;        /* k_traverse_p: node steps per vote (default 4) */
   int32_t refill;            /* k_traverse_p: idle lanes per warp that trigger a fetch (default 24) */
-  int32_t trav_blocks;       /* k_traverse_p: resident blocks per SM (default 8) */
+  int32_t trav_blocks;       /* k_traverse_p: blocks per SM in its persistent grid (default: what the occupancy query says is resident, 8 or 9) */
   int32_t tile;              /* 1: camera paths start in 8x4 pixel tiles (default for BVH scenes) */
   int32_t primary_cull;      /* 1/0: force camera-ray culling against the world box on/off (default: on when the lens is outside it) */
   int32_t shade_sort;        /* 1: k_shade handles paths grouped by material class (default: on when the scene has Perlin or image textures) */

@@ -363,13 +363,20 @@ __global__ void __launch_bounds__(kRaygenBlock) k_raygen(Ctl* __restrict__ ctl, 
 
 constexpr int kPrimBurst = 8;   // primitives tested per PRIMITIVE step
 
-#ifndef RT_TRAV_MINB
-#define RT_TRAV_MINB 8   // resident-block floor of k_traverse_p: caps it at 64 registers (profiles/r01g_sweep_sah.txt)
+// Resident-block floor of k_traverse_p (the kernel is bound by memory latency, so warps in flight matter): 9 blocks = 56
+// registers = 36 warps / SM where that fits without spills - every specialisation WITHOUT moving instances (pawn / bunny <10>,
+// demo1 <1>: 0 bytes spilled; traversal -3 %) - and 8 blocks = 64 registers for the catch-all variants with the per-primitive
+// transform (<15>, <31>, <59>: 66 - 120 bytes of spills at 56 registers, demo2 +4 %).  profiles/r02p_sweep_trav_minb.txt; round 1
+// found 10 blocks = 48 registers far worse (profiles/r01d_rejected_experiments.txt).
+#ifdef RT_TRAV_MINB
+constexpr int trav_minb(uint32_t) { return RT_TRAV_MINB; }
+#else
+constexpr int trav_minb(uint32_t F) { return (F & (TF_MOVING | TF_MOVLIST)) ? 8 : 9; }
 #endif
 // kCount: instrumented variant (RtOptions.count_work) - counts the node pairs and primitive records this traversal really
 // fetches (per lane, warp-reduced once at the end) so that the roofline is computed from EXECUTED work.
 template <uint32_t F, bool kCount>
-__global__ void __launch_bounds__(kTraverseBlock, RT_TRAV_MINB) k_traverse_p(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
+__global__ void __launch_bounds__(kTraverseBlock, trav_minb(F)) k_traverse_p(Ctl* __restrict__ ctl, Queue q, const __grid_constant__ DScene sc,
                                                                const __grid_constant__ RenderArgs A) {
   extern __shared__ uint32_t s_stack[];
   uint32_t w_pairs = 0, w_sph = 0, w_pl = 0, w_box = 0, w_rays = 0;
@@ -1582,9 +1589,15 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   const TraverseFn traverse = count_work ? pick_by_features<CountedK>(s.flat.features) : pick_by_features<PersistentK>(s.flat.features);
   const TraverseFn finish = pick_by_features<FinishK>(s.flat.features);
   const FinishFlatFn finish_flat = fused ? pick_finish_flat(s.flat.features) : nullptr;
-  int g_trav = dev.sm_count * 8, g_shade = dev.sm_count * 8, g_gen = dev.sm_count * 4;
-  if (O.trav_blocks >= 0) g_trav = dev.sm_count * std::max(1, (int)O.trav_blocks);
   const size_t stack_bytes = (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t);
+  int g_trav = dev.sm_count * 8, g_shade = dev.sm_count * 8, g_gen = dev.sm_count * 4;
+  {   // the persistent traversal grid = exactly the blocks that are resident at once (8 or 9 per SM, by specialisation)
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse, kTraverseBlock, stack_bytes) == cudaSuccess && per_sm > 0)
+      g_trav = dev.sm_count * per_sm;
+    else cudaGetLastError();
+  }
+  if (O.trav_blocks >= 0) g_trav = dev.sm_count * std::max(1, (int)O.trav_blocks);
   uint64_t launches = 0;
   size_t timed = 0;
   std::vector<char> has_fin(timing ? kMaxTimed : 0, 0);   // iteration k was followed by a (timed) k_finish launch
