@@ -150,6 +150,18 @@ struct DScene {     // device pointers of one uploaded scene
   float world_lo[3], world_hi[3];
   uint32_t has_world_box;
   uint32_t moving_first, moving_count;   // TF_MOVLIST: the moving primitives, outside the tree (scanned once per segment)
+  // array sizes, read only by the RT_CHECKED build's assertions (RT_ASSERT below)
+  uint32_t n_nodes, n_materials, n_textures, n_xforms, stack_entries;
 };
+
+// -DRT_CHECKED: every index the kernels compute (queue slot, node, primitive, stack entry, pixel, material, texture) is
+// asserted against the size of the array it goes into.  compute-sanitizer is not available on the GPU pool this was developed
+// on, so the checked build run through the whole GPU test suite stands in for a memcheck pass (profiles/r02u_checked_build.txt).
+#ifdef RT_CHECKED
+#include <assert.h>
+#define RT_ASSERT(c) assert(c)
+#else
+#define RT_ASSERT(c) ((void)0)
+#endif
 
 }  // namespace rtb

@@ -243,6 +243,7 @@ __global__ void __launch_bounds__(kRaygenBlock) k_raygen(Ctl* __restrict__ ctl, 
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; lo + t < n; t += gridDim.x * blockDim.x) {
       const NewPath np = new_camera_path(A, item0 + t);
       const uint32_t slot = lo + t;
+      RT_ASSERT(slot < ctl->pool);
       q.o[slot] = make_float4(np.ray.o.x, np.ray.o.y, np.ray.o.z, np.ray.time);
       q.d[slot] = make_float4(np.ray.d.x, np.ray.d.y, np.ray.d.z, __uint_as_float(kNone));
       q.thr[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(np.pixel));
@@ -299,6 +300,7 @@ __global__ void __launch_bounds__(kRaygenBlock) k_raygen(Ctl* __restrict__ ctl, 
         inv.z = fabsf(np.ray.d.z) > 1e-30f ? __frcp_rn(np.ray.d.z) : copysignf(1e30f, np.ray.d.z);
         float tn;
         keep = box_hit(wlo, whi, inv, np.ray.o * inv, 1e-4f, __int_as_float(0x7f800000), tn);
+        RT_ASSERT(np.pixel < A.n_pixels);
         if (!keep) {   // miss: emitted = background, path ends (throughput is still 1)
           const f3 cbg = background(A.cam, np.ray.d);
           culled++;
@@ -321,6 +323,7 @@ __global__ void __launch_bounds__(kRaygenBlock) k_raygen(Ctl* __restrict__ ctl, 
       __syncthreads();
       if (keep) {
         const uint32_t slot = lo + s_base + before + __popc(mask & ((1u << lane) - 1u));
+        RT_ASSERT(slot < ctl->pool);
         q.o[slot] = make_float4(np.ray.o.x, np.ray.o.y, np.ray.o.z, np.ray.time);
         q.d[slot] = make_float4(np.ray.d.x, np.ray.d.y, np.ray.d.z, __uint_as_float(kNone));
         q.thr[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(np.pixel));
@@ -423,6 +426,7 @@ __global__ void __launch_bounds__(kTraverseBlock, trav_minb(F)) k_traverse_p(Ctl
     if (active && pc == pe && (cur & kLeafBit) && cur != kNone) {   // leaf reference → primitive range; next node from the stack
       pc = (cur & ~kLeafBit) >> kLeafShift;
       pe = pc + (cur & kLeafCountMask) + 1u;
+      RT_ASSERT(pe <= sc.n_prims);
       if (sp > 0) { sp--; cur = stack[sp * stride]; }
       else cur = kNone;
     }
@@ -438,6 +442,7 @@ __global__ void __launch_bounds__(kTraverseBlock, trav_minb(F)) k_traverse_p(Ctl
         // lanes that take it; lanes that reach a leaf early sit out the rest of the burst
 #pragma unroll 1
         for (int burst = 0; burst < A.node_burst && !(cur & kLeafBit) && want_n; burst++) {
+          RT_ASSERT(cur + 1u < sc.n_nodes && (cur & 1u) == 0u);
           const float4* N = sc.nodes + 2 * (size_t)cur;
           const F8 c0 = ldg256(N), c1 = ldg256(N + 2);
           const float4 l0 = c0.a, h0 = c0.b, l1 = c1.a, h1 = c1.b;
@@ -448,6 +453,7 @@ __global__ void __launch_bounds__(kTraverseBlock, trav_minb(F)) k_traverse_p(Ctl
           const uint32_t r0 = __float_as_uint(l0.w), r1 = __float_as_uint(l1.w);
           if (hit0 && hit1) {
             const bool first0 = tn0 <= tn1;
+            RT_ASSERT((uint32_t)sp < sc.stack_entries);
             stack[sp * stride] = first0 ? r1 : r0;
             sp++;
             cur = first0 ? r0 : r1;
@@ -466,6 +472,7 @@ __global__ void __launch_bounds__(kTraverseBlock, trav_minb(F)) k_traverse_p(Ctl
     // ---- FINISH step: next query of the segment, or its result --------------------------------------------------
     if (want_f) {
       if constexpr (!kMedia) {
+        RT_ASSERT(slot < n);
         __stcs(A.hits + slot, make_float2(h.front ? h.t : -h.t, __uint_as_float(h.prim)));
         active = false;
       } else {
@@ -711,6 +718,7 @@ __device__ __forceinline__ bool shade_path(const DScene& sc, const RenderArgs& A
   const unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
   const uint4 rnd = rng4(A.key, pixel, sample, meta.y, RNG_SHADE);
   f3 contrib;
+  RT_ASSERT(pixel < A.n_pixels);
   bool alive = shade_bounce(sc, A.cam, T, ray, hit, thr, origin_geom, rnd, contrib);
   // a non-finite weight (pdf underflow at a grazing light direction) must not reach the accumulators: one NaN would own
   // the pixel for the whole render
@@ -889,6 +897,7 @@ __device__ __forceinline__ void shade_tiles(Ctl* __restrict__ ctl, const Queue& 
     __syncthreads();
     if (alive) {
       const uint32_t slot = s_base[par] + before + __popc(mask & ((1u << lane) - 1u));
+      RT_ASSERT(slot < ctl->pool);
       qn.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.time);
       qn.d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(origin_geom));
       qn.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(pixel));
@@ -1358,6 +1367,11 @@ static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
   d.n_prims = (uint32_t)f.canonical.size();
   d.moving_first = f.moving_first;
   d.moving_count = f.moving_count;
+  d.n_nodes = (uint32_t)f.nodes.size();
+  d.n_materials = (uint32_t)f.materials.size();
+  d.n_textures = (uint32_t)f.textures.size();
+  d.n_xforms = (uint32_t)f.xforms.size();
+  d.stack_entries = f.max_depth + 1;
   {
     std::lock_guard<std::mutex> lock(s.devices_mu);
     auto it = s.devices.find(device);

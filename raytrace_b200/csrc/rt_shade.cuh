@@ -21,6 +21,7 @@ struct Surf {          // HitRecord (Core.hs:155-162) + what `<$` attached
 __device__ __forceinline__ Surf reconstruct(const DScene& sc, const RayT& ray, const Hit& hit) {
   Surf s;
   s.p = fma3(hit.t, ray.d, ray.o);
+  RT_ASSERT(hit.prim != kNone && (hit.prim >= kMediumBase ? hit.prim - kMediumBase < sc.n_media : hit.prim < sc.n_prims));
   if (hit.prim >= kMediumBase) {       // constantMedium hit (Geometry.hs:321-327)
     s.n = -ray.d;
     s.front = true;
@@ -144,6 +145,7 @@ __device__ __forceinline__ int floor_mod(int a, int m) {
   return r < 0 ? r + m : r;
 }
 __device__ f3 eval_texture(const DScene& sc, const NoiseTab& T, uint32_t id, const Surf& s) {
+  RT_ASSERT(id < sc.n_textures);
   const DTexture& tx = sc.textures[id];
   switch (tx.kind) {
     case RT_TEX_CHECKER: {
@@ -157,6 +159,7 @@ __device__ f3 eval_texture(const DScene& sc, const NoiseTab& T, uint32_t id, con
       surf_uv(sc, s, u, v);
       int i = floor_mod((int)floorf(u * (float)tx.w), tx.w);
       int j = floor_mod((int)floorf((1.f - v) * (float)tx.h), tx.h);
+      RT_ASSERT(i >= 0 && i < tx.w && j >= 0 && j < tx.h);
       float4 t = __ldg(sc.texels + tx.image_offset + (size_t)j * tx.w + i);
       return mk3(t.x, t.y, t.z);
     }
@@ -209,6 +212,7 @@ __device__ __forceinline__ bool shade_bounce(const DScene& sc, const DCamera& ca
     return false;
   }
   const Surf s = reconstruct(sc, ray, hit);
+  RT_ASSERT(s.material < sc.n_materials);
   const DMaterial mat = sc.materials[s.material];
   const f3 in_dir = ray.d;
   f3 dir;

@@ -209,6 +209,7 @@ __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, u
   f3 o = ray.o, d = ray.d;
   if constexpr ((F & TF_MOVING) != 0) {
     if (tf & PRIM_FLAG_MOVING) {  // transform / moving instance kept local (Geometry.hs:388-389,452-454)
+      RT_ASSERT(__float_as_uint(m4.z) < sc.n_xforms);
       const DXform& X = sc.xforms[__float_as_uint(m4.z)];
       f3 b = fma3(ray.time, ld3(X.binv1), ld3(X.binv0));
       o = mat3(X.Ainv, ray.o) + b;
@@ -322,6 +323,7 @@ __device__ __forceinline__ void intersect_rec(const DScene& sc, const Rec rec, u
 template <uint32_t F>
 __device__ __forceinline__ uint32_t intersect_prim(const DScene& sc, uint32_t i, const RayT& ray, float tmin,
                                                    uint32_t skip_a, uint32_t skip_b, Hit& best) {
+  RT_ASSERT(i < sc.n_prims);
   const float4* P = sc.prims + 4 * (size_t)i;
   const GlobalRec rec{ldg256(P), ldg256(P + 2)};
   intersect_rec<F>(sc, rec, i, ray, tmin, skip_a, skip_b, best);
@@ -362,6 +364,7 @@ __device__ __forceinline__ void closest_hit(const DScene& sc, uint32_t root, con
   int sp = 0;
   while (cur != kNone) {
     while (!(cur & kLeafBit)) {
+      RT_ASSERT(cur + 1u < sc.n_nodes && (cur & 1u) == 0u);
       const float4* N = sc.nodes + 2 * (size_t)cur;
       const F8 c0 = ldg256(N), c1 = ldg256(N + 2);
       const float4 l0 = c0.a, h0 = c0.b, l1 = c1.a, h1 = c1.b;
@@ -371,6 +374,7 @@ __device__ __forceinline__ void closest_hit(const DScene& sc, uint32_t root, con
       const uint32_t r0 = __float_as_uint(l0.w), r1 = __float_as_uint(l1.w);
       if (hit0 && hit1) {
         const bool first0 = tn0 <= tn1;     // near child first; results do not depend on the order
+        RT_ASSERT((uint32_t)sp < sc.stack_entries);
         stack[sp * stride] = first0 ? r1 : r0;
         sp++;
         cur = first0 ? r0 : r1;
