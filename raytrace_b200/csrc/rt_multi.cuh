@@ -328,6 +328,10 @@ static int32_t context_create_impl(const int32_t* devices, int32_t n_devices, Rt
   if ((int)ids.size() > kMaxPeers) { set_error("rt_context_create: at most 16 devices"); return RT_ERR_INVALID_ARG; }
   auto* c = new (std::nothrow) Context();
   if (!c) { set_error("out of memory"); return RT_ERR_INVALID_ARG; }
+  struct Owner {          // a throwing allocation below must not leak the half-built context
+    Context* c;
+    ~Owner() { if (c) rt_context_destroy(reinterpret_cast<RtContext*>(c)); }
+  } owner{c};
   c->dev.resize(ids.size());
   cudaError_t e = cudaSuccess;
   for (size_t g = 0; g < ids.size() && e == cudaSuccess; g++) {
@@ -342,9 +346,9 @@ static int32_t context_create_impl(const int32_t* devices, int32_t n_devices, Rt
   }
   if (e != cudaSuccess) {
     set_error(std::string("rt_context_create: ") + cudaGetErrorString(e));
-    rt_context_destroy(reinterpret_cast<RtContext*>(c));
-    return RT_ERR_CUDA;
+    return RT_ERR_CUDA;            // ~Owner destroys the streams / events created so far
   }
+  owner.c = nullptr;
   *out = reinterpret_cast<RtContext*>(c);
   return RT_OK;
 }
