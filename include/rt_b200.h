@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define RT_B200_VERSION 0x00020000u
+#define RT_B200_VERSION 0x00020001u
 
 typedef enum RtStatus {
   RT_OK = 0,
@@ -189,7 +189,9 @@ typedef struct RtSceneInfo {
                                * (RtOptions.split_moving): the static primitives then run the kernel without the transform branch */
   uint32_t n_shared_trees;    /* media whose boundary geometry IS the surface geometry: their boundary queries walk the surface
                                * tree, no second tree is built or uploaded (pawn, bunny) */
-  uint32_t reserved;
+  uint32_t gpu_build;         /* surface tree: 0 = built by the host at commit; 1 = left to the device, not built yet (the first
+                               * upload / render builds it: n_bvh_nodes and max_depth then cover the media trees only);
+                               * 2 = built on the device (RtOptions.gpu_build) */
 } RtSceneInfo;
 
 typedef struct RtScene RtScene;
@@ -211,6 +213,8 @@ typedef struct RtOptions {
   int32_t world_box;         /* 1 (default): keep the world box (camera rays that miss it end in k_raygen) */
   int32_t split_moving;      /* 1: moving instances live in a short list outside the tree so that static primitives run the kernel without the per-primitive transform branch (default 0: measured slower on demo2) */
   int32_t trace_commit;      /* 1: print the phases of the host scene pipeline to stderr */
+  int32_t gpu_build;         /* surface tree built by the GPU at the first upload (binned SAH, same cost model as the host builder):
+                              * default: trees of >= 1024 items; 0: never (host builder); 1: every tree with an inner node */
   double sah_node_cost;      /* cost of a node step in primitive tests (default 1.0) */
   /* ---- render time ---- */
   int64_t pool;              /* live-path pool size (default 2^24; rounded up to 1024) */

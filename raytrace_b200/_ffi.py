@@ -94,7 +94,7 @@ class RtSceneInfo(C.Structure):
                 ("n_textures", C.c_uint32), ("n_xforms", C.c_uint32), ("surface_root", C.c_uint32),
                 ("max_depth", C.c_uint32), ("device_bytes", C.c_uint64),
                 ("n_closed_media", C.c_uint32), ("n_moving_list", C.c_uint32),
-                ("n_shared_trees", C.c_uint32), ("reserved", C.c_uint32)]
+                ("n_shared_trees", C.c_uint32), ("gpu_build", C.c_uint32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -114,7 +114,7 @@ class RtOptions(C.Structure):
     """include/rt_b200.h RtOptions: negative = library default."""
     _fields_ = [("bvh_reference", C.c_int32), ("leaf_max", C.c_int32), ("collapse", C.c_int32),
                 ("aggregate_boxes", C.c_int32), ("shared_boundary", C.c_int32), ("interior_bound", C.c_int32),
-                ("world_box", C.c_int32), ("split_moving", C.c_int32), ("trace_commit", C.c_int32),
+                ("world_box", C.c_int32), ("split_moving", C.c_int32), ("trace_commit", C.c_int32), ("gpu_build", C.c_int32),
                 ("sah_node_cost", C.c_double),
                 ("pool", C.c_int64), ("finish_max", C.c_int64),
                 ("finish_refill", C.c_int32), ("tail_batch", C.c_int32), ("node_burst", C.c_int32),
@@ -123,7 +123,7 @@ class RtOptions(C.Structure):
                 ("count_work", C.c_int32), ("debug_sync", C.c_int32), ("raygen_block", C.c_int32), ("reserved", C.c_int32 * 7)]
 
     NAMES = ("bvh_reference", "leaf_max", "collapse", "aggregate_boxes", "shared_boundary", "interior_bound", "world_box",
-             "split_moving", "trace_commit", "sah_node_cost", "pool", "finish_max", "finish_refill", "tail_batch",
+             "split_moving", "trace_commit", "gpu_build", "sah_node_cost", "pool", "finish_max", "finish_refill", "tail_batch",
              "node_burst", "refill", "trav_blocks", "tile", "primary_cull", "shade_sort", "timing", "count_work", "debug_sync", "raygen_block")
 
 

@@ -302,7 +302,7 @@ int32_t rt_scene_info(const RtScene* sp, RtSceneInfo* info) {
   for (uint32_t k = 0; k < f.n_media; k++) info->n_closed_media += f.media[k].closed ? 1u : 0u;
   info->n_moving_list = f.moving_count;
   info->n_shared_trees = f.n_shared_trees;
-  info->reserved = 0;
+  info->gpu_build = f.deferred.pending ? 1u : f.deferred.built ? 2u : 0u;
   return RT_OK;
 }
 
@@ -310,6 +310,10 @@ int32_t rt_scene_get_bvh(const RtScene* sp, float* nodes, uint32_t* canon) {
   if (!sp) { set_error("null scene"); return RT_ERR_INVALID_ARG; }
   const Scene& s = *reinterpret_cast<const Scene*>(sp);
   if (!s.committed) { set_error("scene not committed"); return RT_ERR_NOT_COMMITTED; }
+  if (s.flat.deferred.pending) {
+    set_error("the surface tree of this scene is built on the device by the first upload (RtOptions.gpu_build): nothing to read yet");
+    return RT_ERR_NOT_COMMITTED;
+  }
   if (nodes) std::memcpy(nodes, s.flat.nodes.data(), s.flat.nodes.size() * sizeof(DNode));
   if (canon) std::memcpy(canon, s.flat.canonical.data(), s.flat.canonical.size() * 4);
   return RT_OK;

@@ -71,6 +71,16 @@ struct DNode {  // 32 bytes
   uint32_t b;
 };
 
+// One input record of the device-side tree build (rt_build.cuh): an item is what a leaf may not split - one primitive, or the
+// six faces of an aggregated cuboid.  Items are listed in the reference's evaluation order; `prov` is the first of the item's
+// `n` consecutive PROVISIONAL storage slots (the order the host packed the records in), the box is rounded outward from fp64.
+struct BuildItem {  // 32 bytes = two float4
+  float lo[3];
+  uint32_t prov;
+  float hi[3];
+  uint32_t n;
+};
+
 struct DXform {  // world->local: o' = Ainv*o + binv0 + time*binv1 ; local->world normal: A*n
   float Ainv[9];
   float binv0[3], binv1[3];

@@ -156,6 +156,7 @@ struct Builder {
   std::vector<MediumRec> media;
   std::vector<char> mat_used, tex_used;
   int depth_guard = 0;
+  double ms_ref_tree = 0;           // time inside the meshes' reference-policy trees (trace_commit)
 
   explicit Builder(Scene& s) : sc(s) {
     XfState id;
@@ -441,7 +442,9 @@ struct Builder {
           }
           tris.push_back(make_planar(id, (uint32_t)f, true, p[0], p[1] - p[0], p[2] - p[0], uv, xf, material, p));
         }
+        const auto t_tree = std::chrono::steady_clock::now();
         result = bvh_tree(std::move(tris));
+        ms_ref_tree += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_tree).count();
         rb = rnodes[result].ref_box;
         mesh_memo[{id, xf_id}] = MeshMemo{memo_p0, (uint32_t)prims.size(), memo_r0, (int)rnodes.size(), result};
         break;
@@ -798,7 +801,41 @@ struct Builder {
       for (int k = 0; k < 3; k++) it.c[k] = (it.box.lo[k] + it.box.hi[k]) / 2;
     }
     if (n_prims <= kLeafMax) return sah_leaf(items, 0, items.size());   // short list: one leaf, scanned (flat kernels)
+    if (is_surface && defer_to_device(items)) return kDeferred;
     return sah_node(items, 0, items.size(), 0);
+  }
+
+  // ---- surface tree left to the device (RtOptions.gpu_build, rt_build.cuh) ---------------------------------------------
+  // The host keeps what only it can do - the reference-policy pass that fixes the evaluation order - and hands the
+  // binned-SAH build (same bins, same cost model as sah_node above) to the GPU: the items travel in evaluation order with
+  // outward-rounded fp32 boxes, the primitive records are packed in that same order (provisional slots), and the first
+  // upload builds the tree, reads nodes and leaf order back and permutes the records once.
+  int gpu_build = -1;                          // -1: trees of >= kGpuBuildMin items; 0: never; 1: every tree with an inner node
+  static constexpr int kDeferred = -2;
+  static constexpr size_t kGpuBuildMin = 1024, kGpuBuildMax = 1u << 20;
+  DeferredTree deferred;
+  bool defer_to_device(const std::vector<Item>& items) {
+    if (gpu_build == 0 || items.size() < 2 || items.size() > kGpuBuildMax) return false;
+    if (gpu_build < 0 && items.size() < kGpuBuildMin) return false;
+    for (const Item& it : items) {
+      if (it.n != 1 && !(it.n == 6 && (prims[it.prim].flags & PRIM_FLAG_BOXHEAD))) return false;
+      for (int k = 0; k < 3; k++)
+        if (!std::isfinite(it.box.lo[k]) || !std::isfinite(it.box.hi[k]) || std::fabs(it.box.lo[k]) > 1e30 || std::fabs(it.box.hi[k]) > 1e30) return false;
+    }
+    deferred.pending = true;
+    deferred.first = next_storage;
+    deferred.collapse = kCollapse;
+    deferred.node_cost = (float)sah_node_cost;
+    deferred.items.resize(items.size());
+    for (size_t i = 0; i < items.size(); i++) {
+      BuildItem& bi = deferred.items[i];
+      for (int k = 0; k < 3; k++) { bi.lo[k] = round_down(items[i].box.lo[k]); bi.hi[k] = round_up(items[i].box.hi[k]); }
+      bi.prov = next_storage;
+      bi.n = items[i].n;
+      for (uint32_t k = 0; k < items[i].n; k++) prims[items[i].prim + k].index = next_storage++;
+    }
+    deferred.n_prims = next_storage - deferred.first;
+    return true;
   }
 
   // storage slots for a subtree's primitives without a tree over them (evaluation order)
@@ -1102,6 +1139,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
     BoxD rb;
     int surf = b.walk(root, id, kNone, &rb);
     lap("walk (description tree)");
+    if (trace) std::fprintf(stderr, "[rt_b200 commit]   of which mesh reference trees %8.3f ms\n", b.ms_ref_tree);
     if (surf >= 0) b.number(surf, true);
     for (auto& m : b.media) b.number(m.rtree, false);
     lap("number");
@@ -1112,10 +1150,14 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
     // measured (profiles/r02c_sweep.txt, demo2): scanning the moving list once per segment costs more than the per-primitive
     // transform branch it removes (45.2 vs 43.8 ms per 100 spp) - opt-in only
     b.plan_moving_list(surf, O.split_moving > 0);
+    if (O.gpu_build >= 0) b.gpu_build = O.gpu_build;
+    bool deferred = false;
     if (surf >= 0) {
       int h = b.to_device(surf, true);
-      fs.surface_root = b.emit_ref(fs, h, 0, max_depth);
+      deferred = h == Builder::kDeferred;
+      if (!deferred) fs.surface_root = b.emit_ref(fs, h, 0, max_depth);
     }
+    std::vector<uint32_t> share_root;     // media that walk the surface tree (their root is known once the surface root is)
     fs.moving_first = b.moving_first;
     fs.moving_count = b.moving_count;
     lap("surface tree to device");
@@ -1138,6 +1180,7 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
       if (same_tree) {
         if (b.sah) b.assign_storage_linear(b.media[i].rtree);   // the boundary's own records keep their slots (host bookkeeping)
         dm.root = fs.surface_root;
+        share_root.push_back((uint32_t)i);
         fs.n_shared_trees++;
       } else {
         int h = b.to_device(b.media[i].rtree);
@@ -1152,6 +1195,12 @@ int32_t flatten_scene(Scene& sc, uint32_t root) {
         dm.geom_lo = g.front(); dm.geom_hi = g.back(); dm.shared = 1;
         if (O.interior_bound != 0 && b.boundary_is_closed(b.media[i].rtree)) dm.closed = 1;
       }
+    }
+    if (deferred) {   // the device writes its node pairs BEHIND the host-built ones (the media trees above): the array only grows
+      b.deferred.node_base = (uint32_t)fs.nodes.size();
+      fs.surface_root = b.deferred.node_base;
+      for (uint32_t i : share_root) fs.media[i].root = fs.surface_root;
+      fs.deferred = std::move(b.deferred);
     }
     fs.n_media = (uint32_t)b.media.size();
     fs.max_depth = max_depth;

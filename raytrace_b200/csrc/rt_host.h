@@ -33,6 +33,22 @@ struct HostNode {  // one node of the description tree, copied at add time
   std::vector<int32_t> faces;
 };
 
+// Surface tree left to the device (RtOptions.gpu_build; rt_build.cuh): rt_scene_commit stops after the reference-policy pass
+// (evaluation order) and packs the primitive records in that order; the FIRST upload builds the binned-SAH tree on the GPU,
+// reads nodes + leaf order back, permutes the host arrays once, and every later upload (other devices) is a plain copy.
+struct DeferredTree {
+  bool pending = false;        // commit deferred the tree and no device has built it yet
+  bool built = false;          // the tree in FlatScene::nodes came from the device
+  std::vector<BuildItem> items;
+  uint32_t first = 0;          // storage slots [first, first + n_prims) belong to the tree
+  uint32_t n_prims = 0;
+  uint32_t node_base = 0;      // DNode index of the root pair (= FlatScene::surface_root)
+  uint32_t collapse = 4;
+  float node_cost = 1.f;
+  uint32_t levels = 0, launches = 0;
+  double build_ms = 0, device_ms = 0;   // whole step (upload of items .. host arrays permuted) / kernels only
+};
+
 // flattened, device-ready scene (host copy)
 struct FlatScene {
   std::vector<DNode> nodes;
@@ -56,6 +72,7 @@ struct FlatScene {
   float world_lo[3] = {0, 0, 0}, world_hi[3] = {0, 0, 0};   // box of all primitives (outward rounded)
   uint32_t has_world_box = 0;
   uint32_t moving_first = 0, moving_count = 0;   // TF_MOVLIST
+  DeferredTree deferred;
   uint32_t n_shared_trees = 0;   // media whose boundary queries walk the surface tree (boundary geometry == surface geometry)
   uint64_t bytes() const;
 };
@@ -72,6 +89,7 @@ struct Scene {
   FlatScene flat;
   RtOptions opts;          // tuning / A-B options (negative field = default); the library reads no environment variables
   std::map<int, DeviceScene*> devices;
+  std::mutex build_mu;     // serialises the one device-side tree build of a deferred scene (get_device_scene)
   std::mutex devices_mu;   // uploads may race: renders of one committed scene can come from several OS threads
   Scene();
   ~Scene();

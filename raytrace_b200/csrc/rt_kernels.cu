@@ -15,6 +15,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -26,6 +27,7 @@
 
 #include "rt_host.h"
 #include "rt_shade.cuh"
+#include "rt_build.cuh"
 
 namespace rtb {
 
@@ -1278,8 +1280,166 @@ static int32_t check_device(int device) {
   return RT_OK;
 }
 
+// ---- device-side tree build (rt_build.cuh) ---------------------------------------------------------------------------
+// Scratch of the builder: one grow-only allocation per device, kept between builds (a cudaMalloc + cudaFree pair costs more
+// than the whole build of a small mesh); builds on one device are serialised by g_build_mu.
+struct BuildScratch {
+  void* mem = nullptr;
+  size_t bytes = 0;
+  size_t clean_bins = 0;       // the first `clean_bins` Bin records hold the identity (every build leaves them so)
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  uint32_t max_grid = 0;       // co-resident blocks of k_build_tree on this device
+};
+static std::mutex g_build_mu;
+static std::map<int, BuildScratch> g_build_scratch;
+
+static int32_t build_deferred_tree(Scene& s, int device) {
+  using namespace gpubuild;
+  const auto t0 = std::chrono::steady_clock::now();
+  FlatScene& f = s.flat;
+  DeferredTree& D = f.deferred;
+  const uint32_t n = (uint32_t)D.items.size();
+  std::lock_guard<std::mutex> lock(g_build_mu);
+  RT_CUDA(cudaSetDevice(device));
+  BuildScratch& S = g_build_scratch[device];
+  if (!S.stream) {
+    RT_CUDA(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking));
+    for (auto& e : S.ev) RT_CUDA(cudaEventCreate(&e));
+  }
+  BuildParams P{};
+  P.n_items = n; P.first = D.first; P.collapse = D.collapse; P.node_cost = D.node_cost;
+  P.bank_slots = n / 2u + 1u; P.node_base = D.node_base;
+  const size_t n_bins = (size_t)2 * P.bank_slots * (3 * kBins);
+  // layout (256-byte aligned sections): bins first, so that a kept scratch keeps its clean bins
+  size_t off = 0;
+  auto take = [&](size_t bytes) { const size_t at = off; off += (bytes + 255) / 256 * 256; return at; };
+  const size_t o_bins = take(n_bins * sizeof(Bin)), o_items = take((size_t)n * sizeof(BuildItem)), o_idx0 = take((size_t)n * 4),
+               o_idx1 = take((size_t)n * 4), o_nod0 = take((size_t)n * 4), o_nod1 = take((size_t)n * 4), o_off = take((size_t)n * 4),
+               o_perm = take((size_t)D.n_prims * 4), o_nodes = take((size_t)2 * n * sizeof(BNode)),
+               o_dn = take((size_t)2 * n * sizeof(DNode)), o_ctl = take(sizeof(BuildCtl));
+  if (off > S.bytes) {
+    if (S.mem) cudaFree(S.mem);
+    S.mem = nullptr; S.bytes = 0; S.clean_bins = 0;
+    cudaError_t e = cudaMalloc(&S.mem, off);
+    if (e != cudaSuccess) { set_error(std::string("device tree build: scratch allocation failed: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
+    S.bytes = off;
+  }
+  unsigned char* base = static_cast<unsigned char*>(S.mem);
+  Bin* bins = reinterpret_cast<Bin*>(base + o_bins);
+  float4* items = reinterpret_cast<float4*>(base + o_items);
+  uint32_t* idx[2] = {reinterpret_cast<uint32_t*>(base + o_idx0), reinterpret_cast<uint32_t*>(base + o_idx1)};
+  uint32_t* nod[2] = {reinterpret_cast<uint32_t*>(base + o_nod0), reinterpret_cast<uint32_t*>(base + o_nod1)};
+  uint32_t* offs = reinterpret_cast<uint32_t*>(base + o_off);
+  uint32_t* perm = reinterpret_cast<uint32_t*>(base + o_perm);
+  BNode* nodes = reinterpret_cast<BNode*>(base + o_nodes);
+  DNode* dnodes = reinterpret_cast<DNode*>(base + o_dn);
+  BuildCtl* ctl = reinterpret_cast<BuildCtl*>(base + o_ctl);
+  cudaStream_t st = S.stream;
+  const size_t had_clean = S.clean_bins;
+  S.clean_bins = 0;                      // until this build has run to its end
+  // root node and control block are prepared here; everything else happens inside ONE cooperative launch
+  BNode root{};
+  root.lo = 0; root.hi = n; root.slot = kNone; root.depth = 0; root.kind = kPending; root.bslot = 0; root.child = kNone;
+  for (int k = 0; k < 3; k++) { root.bx[k] = kEncMax; root.bx[3 + k] = kEncMin; root.cb[k] = kEncMax; root.cb[3 + k] = kEncMin; }
+  BuildCtl h{};
+  h.bslots[0] = 1;                                                 // the root owns slot 0 of bank 0
+  h.level_begin[0] = 0; h.level_end[0] = 1;
+  RT_CUDA(cudaMemcpyAsync(items, D.items.data(), (size_t)n * sizeof(BuildItem), cudaMemcpyHostToDevice, st));
+  RT_CUDA(cudaMemcpyAsync(nodes, &root, sizeof root, cudaMemcpyHostToDevice, st));
+  RT_CUDA(cudaMemcpyAsync(ctl, &h, sizeof h, cudaMemcpyHostToDevice, st));
+  RT_CUDA(cudaEventRecord(S.ev[0], st));
+  uint32_t launches = 0;
+  if (had_clean < n_bins) { k_build_fill_bins<<<592, 256, 0, st>>>(bins, n_bins); launches++; }
+  const bool unit_items = D.n_prims == n;       // a mesh: every item is one primitive, storage offset = position
+  BuildArgs A{};
+  A.items = items; A.idx[0] = idx[0]; A.idx[1] = idx[1]; A.node_of[0] = nod[0]; A.node_of[1] = nod[1];
+  A.off = unit_items ? nullptr : offs; A.perm = perm; A.nodes = nodes; A.bins = bins; A.ctl = ctl; A.dnodes = dnodes; A.P = P;
+  if (!S.max_grid) {
+    int per_sm = 0, sms = 0;
+    RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_build_tree, kBlock, 0));
+    RT_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    S.max_grid = (uint32_t)std::max(1, per_sm * sms);
+  }
+  // a persistent grid: one block per 256 items while they are all co-resident (a barrier among few blocks is cheaper), else
+  // every slot of the machine and the blocks loop
+  // (never fewer than one block per SM: the split phase works a warp per node, and the middle levels of a small tree have
+  // hundreds of nodes)
+  int sm_count = 148;
+  cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device);
+  const uint32_t grid = std::min<uint32_t>(S.max_grid, std::max<uint32_t>((n + kBlock - 1) / kBlock, (uint32_t)sm_count));
+  void* kargs[] = {&A};
+  RT_CUDA(cudaLaunchCooperativeKernel((const void*)k_build_tree, dim3(grid), dim3(kBlock), kargs, 0, st));
+  launches++;
+  RT_CUDA(cudaEventRecord(S.ev[1], st));
+  // read-back: small trees fetch the worst-case node count together with the control block (one wait); large ones ask first
+  const uint32_t max_dn = 2u * (n - 1u);
+  const bool two_step = n > 65536u;
+  std::vector<DNode> got(two_step ? 0 : max_dn);
+  std::vector<uint32_t> hperm(D.n_prims);
+  if (!two_step) RT_CUDA(cudaMemcpyAsync(got.data(), dnodes, (size_t)max_dn * sizeof(DNode), cudaMemcpyDeviceToHost, st));
+  RT_CUDA(cudaMemcpyAsync(hperm.data(), perm, (size_t)D.n_prims * 4, cudaMemcpyDeviceToHost, st));
+  RT_CUDA(cudaMemcpyAsync(&h, ctl, sizeof h, cudaMemcpyDeviceToHost, st));
+  RT_CUDA(cudaStreamSynchronize(st));
+  RT_CUDA(cudaGetLastError());
+  const uint32_t n_dn = 2u * h.n_inner;
+  if (n_dn > max_dn || (n_dn & 1u)) { set_error("device tree build: bad node count (internal error)"); return RT_ERR_CUDA; }
+  got.resize(n_dn);
+  if (two_step) {
+    RT_CUDA(cudaMemcpyAsync(got.data(), dnodes, (size_t)n_dn * sizeof(DNode), cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+  }
+  S.clean_bins = n_bins;                  // k_build_split put the identity back into every bin it consumed
+  float dev_ms = 0.f;
+  cudaEventElapsedTime(&dev_ms, S.ev[0], S.ev[1]);
+  if (h.overflow) { set_error("device tree build: a leaf holds more than 32 primitives (internal error)"); return RT_ERR_CUDA; }
+  if (h.max_depth + 1u > (uint32_t)kStackDepth) {
+    set_error("flattened BVH is deeper than the shared-memory traversal stack (32 levels)");
+    return RT_ERR_UNSUPPORTED;
+  }
+  // host arrays: node pairs behind the host-built ones; primitive records from provisional (evaluation) order to leaf order
+  if (f.nodes.size() != D.node_base) { set_error("device tree build: node base moved (internal error)"); return RT_ERR_CUDA; }
+  f.nodes.insert(f.nodes.end(), got.begin(), got.end());
+  {
+    const size_t np = D.n_prims, first = D.first;
+    std::vector<float> prims(np * 16), uv(np * 8);
+    std::vector<uint32_t> canon(np), ref(np);
+    for (size_t j = 0; j < np; j++) {
+      const size_t src = hperm[j];
+      if (src < first || src >= first + np) { set_error("device tree build: bad permutation (internal error)"); return RT_ERR_CUDA; }
+      std::memcpy(&prims[j * 16], &f.prims[src * 16], 64);
+      std::memcpy(&uv[j * 8], &f.tri_uv[src * 8], 32);
+      canon[j] = f.canonical[src];
+      ref[j] = f.ref_order[src];
+    }
+    std::memcpy(&f.prims[first * 16], prims.data(), np * 64);
+    std::memcpy(&f.tri_uv[first * 8], uv.data(), np * 32);
+    std::memcpy(&f.canonical[first], canon.data(), np * 4);
+    std::memcpy(&f.ref_order[first], ref.data(), np * 4);
+  }
+  f.max_depth = std::max(f.max_depth, h.max_depth);
+  D.levels = h.levels; D.launches = launches; D.device_ms = dev_ms;
+  D.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  D.built = true;                         // (before `pending` drops: a deferred scene never shows both flags clear)
+  D.pending = false;
+  std::vector<BuildItem>().swap(D.items);
+  if (s.opts.trace_commit > 0)
+    std::fprintf(stderr, "[rt_b200 upload] device tree build: %u items, %u node pairs, depth %u, %u levels, %u launch(es), grid %u: %.3f ms on the device, "
+                 "%.3f ms with copies and the host permutation\n", n, n_dn / 2u, h.max_depth, h.levels, launches, grid, dev_ms, D.build_ms);
+  return RT_OK;
+}
+
 static int32_t get_device_scene(Scene& s, int device, DeviceScene** out) {
   if (!s.committed) { set_error("scene not committed"); return RT_ERR_NOT_COMMITTED; }
+  if (s.flat.deferred.pending || s.flat.deferred.built) {   // a scene whose surface tree was left to the device: built by the first upload
+    int32_t st0 = check_device(device);
+    if (st0 != RT_OK) return st0;
+    std::lock_guard<std::mutex> lock(s.build_mu);
+    if (s.flat.deferred.pending) {
+      st0 = build_deferred_tree(s, device);
+      if (st0 != RT_OK) return st0;
+    }
+  }
   {
     std::lock_guard<std::mutex> lock(s.devices_mu);
     auto it = s.devices.find(device);

@@ -14,6 +14,7 @@ from raytrace_b200 import _ffi, scenes
 from raytrace_b200.ray import CompiledScene, classify_background, BG_CONSTANT, BG_YGRADIENT
 from oracle.harness import OracleScene
 from oracle import obj_oracle
+from util import check_device_tree
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -25,7 +26,7 @@ def test_library_exports_every_declared_symbol(built):
     assert declared == set(_ffi.EXPORTS), declared ^ set(_ffi.EXPORTS)
     for name in declared:
         assert hasattr(L, name), name
-    assert L.rt_version() == 0x00020000
+    assert L.rt_version() == 0x00020001
 
 
 def test_no_gpu_is_a_loud_error_not_a_fallback(built):
@@ -72,7 +73,7 @@ def test_flattened_tree_matches_reference_evaluation_order(built, name, policy):
     (storage order = evaluation order)."""
     ctor, _ = scenes.CONFIGS[name]
     s, w = ctor()
-    cs = CompiledScene(w, upload=False, options=dict(bvh_reference=int(policy == "reference")))
+    cs = CompiledScene(w, upload=False, options=dict(bvh_reference=int(policy == "reference"), gpu_build=0))     # host builders
     nodes, canon = cs.handle.get_bvh()
     ora = OracleScene(w)
     order = ora.leaf_order()
@@ -80,30 +81,34 @@ def test_flattened_tree_matches_reference_evaluation_order(built, name, policy):
     assert sorted(canon.tolist()) == sorted(cs.handle.get_eval_order().tolist())
     if policy == "reference":
         assert np.array_equal(canon[: len(order)], order)
+    check_device_tree(nodes, cs.info())
+
+
+def test_large_surface_tree_is_left_to_the_device(built):
+    """RtOptions.gpu_build (default: trees of >= 1024 items): commit stops after the reference-policy pass - the evaluation
+    order is there, the tree is not - and the first upload builds it on the GPU (tests/test_gpu_build.py).  Small trees,
+    the reference-shaped tree and gpu_build = 0 stay on the host."""
+    s, w = scenes.bunny_volume(width=8, spp=1)
+    cs = CompiledScene(w, upload=False)
     info = cs.info()
-    assert info["n_bvh_nodes"] == len(nodes) and info["max_depth"] < 32
-    # every inner node's box contains its children's boxes; leaf references address valid primitive ranges
-    lo, hi = nodes[:, 0:3], nodes[:, 4:7]
-    ref, cnt = nodes[:, 3].view(np.uint32), nodes[:, 7].view(np.uint32)
-    LEAF = 0x80000000
-    seen = np.zeros(info["n_prims"], bool)
-    for k in range(len(nodes)):
-        if ref[k] & LEAF:
-            first, c = int(ref[k] & 0x7FFFFFFF) >> 5, int(ref[k] & 31) + 1
-            assert c == cnt[k] and 1 <= c <= 32 and first + c <= info["n_prims"]
-            seen[first:first + c] = True
-        else:
-            c = int(ref[k])
-            assert c % 2 == 0 and cnt[k] == 0
-            for ch in (c, c + 1):
-                assert (lo[k] <= lo[ch] + 1e-3).all() and (hi[k] >= hi[ch] - 1e-3).all()
-    if len(nodes):                 # every primitive is reachable through some leaf (a medium whose boundary is one
-        # a leaf root is referenced from its DMedium record, not a node; a medium whose boundary IS the surface geometry walks
-        # the surface tree, so its own copies of the records (half of the primitives: pawn, bunny) hang on no leaf
-        spare = info["n_prims"] // 2 if info["n_shared_trees"] else 0
-        assert (~seen).sum() <= 32 * max(1, info["n_media"]) + spare
-        if info["n_shared_trees"]:
-            assert (~seen).sum() == spare and not seen[spare:].any()      # exactly the boundary's records, stored behind the tree's
+    assert info["gpu_build"] == 1 and info["n_bvh_nodes"] == 0 and info["surface_root"] == 0 and info["n_shared_trees"] == 1
+    with pytest.raises(_ffi.RtError) as e:
+        cs.handle.get_bvh()
+    assert e.value.status == 8 and "built on the device" in e.value.message
+    order = OracleScene(w).leaf_order()
+    assert np.array_equal(cs.handle.get_eval_order()[: len(order)], order)
+    host = CompiledScene(w, upload=False, options=dict(gpu_build=0))
+    assert host.info()["gpu_build"] == 0 and host.info()["n_bvh_nodes"] > 0
+    assert np.array_equal(host.handle.get_eval_order(), cs.handle.get_eval_order())
+    assert CompiledScene(w, upload=False, options=dict(bvh_reference=1)).info()["gpu_build"] == 0
+    s, w = scenes.demo1(width=8, spp=1)                                    # 484 items: below the default threshold
+    assert CompiledScene(w, upload=False).info()["gpu_build"] == 0
+    assert CompiledScene(w, upload=False, options=dict(gpu_build=1)).info()["gpu_build"] == 1
+    s, w = scenes.cornell_box()                                            # one scanned leaf: there is no tree to build
+    assert CompiledScene(w, upload=False, options=dict(gpu_build=1)).info()["gpu_build"] == 0
+    s, w = scenes.demo2(width=8, spp=1)                                    # the device writes its pairs behind whatever the host built
+    info = CompiledScene(w, upload=False).info()
+    assert info["gpu_build"] == 1 and info["surface_root"] == info["n_bvh_nodes"]
 
 
 def test_boundary_that_is_the_surface_shares_its_tree(built):
@@ -113,8 +118,8 @@ def test_boundary_that_is_the_surface_shares_its_tree(built):
     for name in ("pawn", "bunny_volume"):
         ctor, _ = scenes.CONFIGS[name]
         s, w = ctor()
-        a = CompiledScene(w, upload=False)
-        b = CompiledScene(w, upload=False, options=dict(shared_boundary=0))
+        a = CompiledScene(w, upload=False, options=dict(gpu_build=0))
+        b = CompiledScene(w, upload=False, options=dict(shared_boundary=0, gpu_build=0))
         ia, ib = a.info(), b.info()
         assert ia["n_shared_trees"] == 1 and ib["n_shared_trees"] == 0
         assert ia["n_prims"] == ib["n_prims"] and ia["n_bvh_nodes"] * 2 == ib["n_bvh_nodes"]      # one tree instead of two equal ones
@@ -189,7 +194,7 @@ def test_outermost_material_wins_and_shared_geometry(built):
     cs = CompiledScene(b << rt.group([inner, a << rt.sphere((3, 0, 0), 1)]), upload=False)
     assert cs.info()["n_prims"] == 2
     s, w = scenes.pawn(spp=1, width=8)           # the same mesh object is surface and medium boundary
-    nodes, canon = CompiledScene(w, upload=False).handle.get_bvh()
+    nodes, canon = CompiledScene(w, upload=False, options=dict(gpu_build=0)).handle.get_bvh()
     # surface records in the tree's leaf order, then the boundary's copies of the SAME canonical primitives (they share the
     # surface tree, so they are stored in evaluation order behind it)
     assert np.array_equal(np.sort(canon[:1200]), np.arange(1200)) and np.array_equal(np.sort(canon[1200:]), np.arange(1200))
@@ -311,7 +316,7 @@ def test_sah_builder_pathological_inputs(built, case):
         prims = [mat << rt.sphere((0, 0, -5), 1)]
     else:
         prims = [mat << rt.sphere((0.01 * k, 0, -5), 0.004) for k in range(5000)]
-    cs = CompiledScene(rt.bvhTree(prims), upload=False)
+    cs = CompiledScene(rt.bvhTree(prims), upload=False, options=dict(gpu_build=0))
     info = cs.info()
     nodes, canon = cs.handle.get_bvh()
     assert info["n_prims"] == len(prims) and info["max_depth"] < 32
