@@ -217,7 +217,7 @@ typedef struct RtOptions {
                               * default: trees of >= 1024 items; 0: never (host builder); 1: every tree with an inner node */
   double sah_node_cost;      /* cost of a node step in primitive tests (default 1.0) */
   /* ---- render time ---- */
-  int64_t pool;              /* live-path pool size (default 2^24; rounded up to 1024) */
+  int64_t pool;              /* live-path pool size (default 2^25; rounded up to 1024) */
   int64_t finish_max;        /* tail kernel takes over at <= this many live paths (0 = never, >= 2^32-1 = as soon as all paths started) */
   int32_t finish_refill;     /* tail kernel: idle lanes per warp that trigger a claim (default 4) */
   int32_t tail_batch;        /* iterations per host round trip once all paths have started (default 3) */
@@ -231,7 +231,10 @@ typedef struct RtOptions {
   int32_t count_work;        /* 1: run the instrumented traversal kernel and fill RtStats.node_pairs ... (default 0) */
   int32_t debug_sync;        /* 1: synchronise after every launch and name a faulting kernel on stderr */
   int32_t raygen_block;      /* culling k_raygen: consecutive samples of one pixel owned by a thread (default 8; 1 = one atomic triple per culled sample) */
-  int32_t reserved[7];
+  int32_t material_sampling; /* 1: a material draws the direction of the no-redirection case from its own generator - the generalisation
+                              * sketched in Material.hs:36-38; today `anisotropic g` samples its Henyey-Greenstein phase function.  Same
+                              * expectation, other samples, less variance.  Default 0: the reference's estimator, sample for sample */
+  int32_t reserved[6];
 } RtOptions;
 
 /* library */

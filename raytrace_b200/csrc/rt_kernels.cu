@@ -117,6 +117,7 @@ struct RenderArgs {
   // sample); kblock = 1: an item is (sample pass, pixel).  A bijection onto (pixel, sample) either way - the RNG is keyed by
   // (pixel, global sample), so the sample set does not depend on it.
   uint32_t shade_sort;                  // k_shade: deal the paths of a tile to the threads by material class
+  uint32_t material_sampling;           // materials draw the no-redirection direction from their own generator (Material.hs:36-38)
   uint32_t kblock, ktail;               // K; n_samples % K
   unsigned long long kfull_items;       // (n_samples / K) * K * n_pixels: items before the ragged last block of samples
 };
@@ -721,7 +722,7 @@ __device__ __forceinline__ bool shade_path(const DScene& sc, const RenderArgs& A
   const uint4 rnd = rng4(A.key, pixel, sample, meta.y, RNG_SHADE);
   f3 contrib;
   RT_ASSERT(pixel < A.n_pixels);
-  bool alive = shade_bounce(sc, A.cam, T, ray, hit, thr, origin_geom, rnd, contrib);
+  bool alive = shade_bounce(sc, A.cam, T, ray, hit, thr, origin_geom, rnd, contrib, A.material_sampling != 0u);
   // a non-finite weight (pdf underflow at a grazing light direction) must not reach the accumulators: one NaN would own
   // the pixel for the whole render
   if (!(fabsf(thr.x + thr.y + thr.z) < 3.0e38f)) { alive = false; thr = mk3(0.f, 0.f, 0.f); }
@@ -1670,7 +1671,7 @@ static int32_t ensure_workspace(Workspace& ds, uint32_t pool, size_t accum_elems
 
 static uint32_t choose_pool(const Scene& s, unsigned long long total_items) {
   uint32_t pool = s.opts.pool > 0 ? (uint32_t)std::min<int64_t>(s.opts.pool, 1ll << 30) : 0u;
-  if (pool == 0) pool = 1u << 24;   // fewer, larger iterations: launch gaps and kernel tails amortise (sweeps in profiles/); 1.9 GB
+  if (pool == 0) pool = 1u << 25;   // fewer, larger iterations: launch gaps and kernel tails amortise (profiles/r02x_sweep_pool.txt); 3.8 GB
   pool = (std::max<uint32_t>(pool, 1024) + 1023u) / 1024u * 1024u;   // whole 256-slot tiles for the TMA prefetch in k_shade
   if (total_items < pool) pool = (uint32_t)std::max<unsigned long long>(1024, (total_items + 1023) / 1024 * 1024);
   return pool;
@@ -1733,6 +1734,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
     A.shade_sort = (texk & ((1u << RT_TEX_NOISE) | (1u << RT_TEX_MARBLE) | (1u << RT_TEX_IMAGE))) != 0 ? 1u : 0u;
     if (O.shade_sort >= 0) A.shade_sort = O.shade_sort ? 1u : 0u;
   }
+  A.material_sampling = O.material_sampling > 0 ? 1u : 0u;   // off by default: parity with the reference's estimator
   // culling iterations: a k_raygen thread owns K consecutive samples of a pixel (one background atomic triple per K samples)
   A.kblock = 1u;
   if (A.cull) {

@@ -204,8 +204,36 @@ __device__ __forceinline__ float target_pdf(const DTarget& tg, f3 p, f3 dir) {
 // continues (ray / thr / origin_geom updated); `contrib` is the radiance this path adds to its pixel
 // (non-zero only when the path ends on an emitter or the background: no library material both emits
 // and scatters).
+// Material-supplied direction generator (the generalisation the reference's author sketches in Material.hs:36-38: "allowing
+// the material to specify a unit vector generator (and pdf) to use in the case of no redirection ... One issue is that it
+// would require converting a single vector into an orthonormal basis").  RtOptions.material_sampling = 1 (OFF by default: it
+// changes which samples are drawn, not what they converge to): `anisotropic g` then draws the new direction from its own
+// Henyey-Greenstein phase function about the incoming direction instead of uniformly on the sphere; the mixture pdf with the
+// redirect targets and the weight follow Ray.hs:187-224 with that generator's pdf in place of 1 / 4 pi.  Without redirect
+// targets the weight is exactly the albedo (the estimator's variance from the phase function is gone).
+__device__ __forceinline__ void onb_from(f3 n, f3& t, f3& b) {   // branch-light orthonormal basis around unit n
+  const float sg = copysignf(1.f, n.z), a = -__frcp_rn(sg + n.z), c = n.x * n.y * a;
+  t = mk3(1.f + sg * n.x * n.x * a, sg * c, -sg * n.x);
+  b = mk3(c, sg + n.y * n.y * a, -n.y);
+}
+__device__ __forceinline__ float hg_phase_4pi(float g, float mu) {   // Material.hs:124-129: phase function times 4 pi
+  const float b = 1.f + g * g - 2.f * g * mu;
+  return __fdividef(1.f - g * g, b * sqrtf(b));
+}
+__device__ __forceinline__ f3 sample_hg(f3 fwd, float g, float u1, float u2) {
+  const float q = __fdividef(1.f - g * g, 1.f - g + 2.f * g * u1);
+  const float mu = fminf(1.f, fmaxf(-1.f, __fdividef(1.f + g * g - q * q, 2.f * g)));
+  const float r = sqrtf(fmaxf(0.f, 1.f - mu * mu));
+  float sn, cs;
+  sincospif(2.f * u2, &sn, &cs);
+  f3 t, b;
+  onb_from(fwd, t, b);
+  return fma3(r * cs, t, fma3(r * sn, b, mu * fwd));
+}
+
 __device__ __forceinline__ bool shade_bounce(const DScene& sc, const DCamera& cam, const NoiseTab& T, RayT& ray,
-                                             const Hit& hit, f3& thr, uint32_t& origin_geom, uint4 rnd, f3& contrib) {
+                                             const Hit& hit, f3& thr, uint32_t& origin_geom, uint4 rnd, f3& contrib,
+                                             bool material_sampling = false) {
   contrib = mk3(0.f, 0.f, 0.f);
   if (hit.prim == kNone) {   // Ray.hs:179
     contrib = thr * background(cam, ray.d);
@@ -260,9 +288,14 @@ __device__ __forceinline__ bool shade_bounce(const DScene& sc, const DCamera& ca
       int choice = -1;
       for (int k = 0; k < cam.n_targets; k++)
         if (r < cam.targets[k].cumulative) { choice = k; break; }   // Ray.hs:150-151
+      // the material's own generator (Material.hs:36-38), used in the case of no redirection
+      const bool own = material_sampling && mat.kind == RT_MAT_ANISOTROPIC && fabsf(mat.param) > 1e-3f && fabsf(mat.param) < 0.999f;
       if (choice < 0) {
-        f3 uu = unit_vector(u01(rnd.y), u01(rnd.z));
-        dir = hemi ? s.n + uu : uu;
+        if (own) dir = sample_hg(in_dir, mat.param, u01(rnd.y), u01(rnd.z));
+        else {
+          f3 uu = unit_vector(u01(rnd.y), u01(rnd.z));
+          dir = hemi ? s.n + uu : uu;
+        }
       } else {
         const DTarget& tg = cam.targets[choice];
         f3 lp = fma3(u01(rnd.y), ld3(tg.U), fma3(u01(rnd.z), ld3(tg.V), ld3(tg.origin)));
@@ -273,7 +306,8 @@ __device__ __forceinline__ bool shade_bounce(const DScene& sc, const DCamera& ca
       dir = rsqrtf(l2) * dir;
       float pdf1 = hemi ? dot3(dir, s.n) * kInvPi : 0.25f * kInvPi;
       if (hemi && !(pdf1 > 0.f)) return false;                      // Ray.hs:197-198
-      float pdf = cam.rem_prob * pdf1;
+      const float gen = own ? pdf1 * hg_phase_4pi(mat.param, dot3(in_dir, dir)) : pdf1;   // pdf of the no-redirection generator
+      float pdf = cam.rem_prob * gen;
       for (int k = 0; k < cam.n_targets; k++) {
         // The target the direction was SAMPLED from is hit by construction (Ray.hs:199-202 finds it again with a
         // parallelogram test): its pdf is t^2 / |crs . dir| with t = |lp - p|.  Re-deriving a, b in fp32 would reject a light
@@ -289,9 +323,8 @@ __device__ __forceinline__ bool shade_bounce(const DScene& sc, const DCamera& ca
         float mu0 = -dot3(in_dir, s.n), mu1 = dot3(dir, s.n);
         w *= __fdividef(0.25f, mu0 + mu1);
       } else if (mat.kind == RT_MAT_ANISOTROPIC) {                  // Material.hs:124-129
-        float g = mat.param, mu = dot3(in_dir, dir);
-        float b = 1.f + g * g - 2.f * g * mu;
-        w *= __fdividef(1.f - g * g, b * sqrtf(b));
+        // own generator, no redirection: phase / (generator pdf x 4 pi) = 1 exactly - the weight is the albedo
+        if (!(own && cam.n_targets == 0)) w *= hg_phase_4pi(mat.param, dot3(in_dir, dir));
       }
       thr = w * (thr * f);
       break;
