@@ -69,11 +69,25 @@ def load_peaks():
 def load_ncu_metrics():
     """per (workload, kernel): issue-slot utilisation, threads per instruction, DRAM bytes per ray from the committed ncu
     captures (tools/ncu_metrics_json.py writes the file from `ncu --page raw --csv` dumps; absent entries -> None)"""
-    p = os.path.join(ROOT, "profiles", "r02_ncu_metrics.json")
+    p = os.path.join(ROOT, "profiles", "r02_ncu_metrics.json")      # one full-pool launch per kernel: steady-state issue metrics
+    res = {}
     if os.path.exists(p):
         with open(p) as f:
-            return json.load(f)
-    return {}
+            res = json.load(f)
+    # DRAM bytes per segment: `--set full` over EVERY launch of one render per workload (tools/ncu_capture_all.sh), summed and
+    # divided by the segments the instrumented pass of the same render counted
+    p2 = os.path.join(ROOT, "profiles", "r02z_ncu_metrics.json")
+    if os.path.exists(p2):
+        with open(p2) as f:
+            whole = json.load(f)
+        for wl, ks in whole.items():
+            for k, m in ks.items():
+                e = res.setdefault(wl, {}).setdefault(k, {"issue_active_pct": m.get("issue_active_pct"), "threads_per_inst": m.get("threads_per_inst"),
+                                                          "source": m.get("source")})
+                if m.get("dram_bytes_per_ray") is not None:
+                    e["dram_bytes_per_ray"] = m["dram_bytes_per_ray"]
+                    e["traffic_source"] = m.get("source")
+    return res
 
 
 def measure_aux_peaks():
@@ -375,10 +389,18 @@ class Bench:
                                   "source": m.get("source")}
                 if m.get("dram_bytes_per_ray") is not None:
                     entry["traffic"] = m["dram_bytes_per_ray"] * entry["rays_per_launch"]
+                    entry["traffic_source"] = "ncu --set full over every launch of one render: %.1f B per segment (%s)" % (
+                        m["dram_bytes_per_ray"], m.get("traffic_source"))
             return entry
 
         kernels = {}
         fused = shade_ms > 0 and trav_ms < 0.05 * shade_ms           # flat scenes: ONE fused kernel per iteration, reported as ms_shade
+        # Camera rays that miss the world box end inside k_raygen: they are path segments (Mrays/s counts them, Ray.hs:178-179)
+        # but never reach k_traverse_p / k_shade.  The kernels' bytes and rates are computed from the segments that DO reach
+        # them: the instrumented pass of the same step counts those (RtStats.rays_counted).
+        q_rays = iter_rays
+        if work and work.get("rays_counted") and work["rays"] > work["rays_finish"]:
+            q_rays = iter_rays * min(1.0, work["rays_counted"] / float(work["rays"] - work["rays_finish"]))
         if fused:
             # compulsory HBM traffic of the fused kernel: every segment except a path's first reads its 56-byte record, and
             # every path that continues writes one (new camera paths are generated in registers; no hit buffer)
@@ -403,22 +425,23 @@ class Bench:
             if shade_ms > 0:
                 # k_shade streams the wavefront state: per ray segment it reads the 56-byte path record + the 8-byte hit and
                 # writes a 56-byte record for every path that continues - compulsory HBM traffic (the queues exceed L2)
-                sh_bytes = 64.0 * iter_rays + 56.0 * (max(iter_rays - samples_rendered, 0) + fin_paths)
+                # (a culled camera ray is the first segment of its path: the number of continuing paths is iter_rays - samples either way)
+                sh_bytes = 64.0 * q_rays + 56.0 * (max(iter_rays - samples_rendered, 0) + fin_paths)
                 ach = sh_bytes / (shade_ms * 1e-3) / 1e9
                 kernels["k_shade"] = with_ncu("k_shade", {
                     "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-                    "bytes_per_ray_algorithmic": sh_bytes / max(iter_rays, 1), "avg_launch_ms": shade_ms / iter_launches,
+                    "bytes_per_ray_algorithmic": sh_bytes / max(q_rays, 1), "avg_launch_ms": shade_ms / iter_launches,
                     "ms_per_step": shade_ms / steps, "algorithmic_bytes_per_launch": sh_bytes / iter_launches,
-                    "rays_per_launch": iter_rays / iter_launches})
+                    "rays_per_launch": q_rays / iter_launches})
             if trav_ms > 0:
                 # k_traverse_p: the HBM bytes it must move are the queue records (32 B origin + direction read, 8 B hit
                 # written; media scenes read pixel + sample index as well: + 24 B); nodes and primitives come from L1 / L2
-                q_bytes = (40.0 + (24.0 if info["n_media"] else 0.0)) * iter_rays
+                q_bytes = (40.0 + (24.0 if info["n_media"] else 0.0)) * q_rays
                 ach = q_bytes / (trav_ms * 1e-3) / 1e9
                 k = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-                     "bytes_per_ray_algorithmic": q_bytes / max(iter_rays, 1), "avg_launch_ms": trav_ms / iter_launches,
+                     "bytes_per_ray_algorithmic": q_bytes / max(q_rays, 1), "avg_launch_ms": trav_ms / iter_launches,
                      "ms_per_step": trav_ms / steps, "algorithmic_bytes_per_launch": q_bytes / iter_launches,
-                     "rays_per_launch": iter_rays / iter_launches,
+                     "rays_per_launch": q_rays / iter_launches, "mrays_per_s_through_kernel": q_rays / (trav_ms * 1e-3) / 1e6,
                      "note": "HBM roofline = wavefront-queue bytes only; scene data is cache resident, see l2 / fp32 / issue for the binding limits"}
                 rc = max(work.get("rays_counted", 0), 1) if work else 1
                 if work and work.get("rays_counted"):
@@ -427,12 +450,12 @@ class Bench:
                     ex_flops = sum(FLOPS[t] * per_ray[t] for t in per_ray)
                     k["executed_per_ray"] = dict(per_ray, bytes=ex_bytes, flops=ex_flops)
                     if aux.get("l2_read_gbs"):
-                        a2 = iter_rays * ex_bytes / (trav_ms * 1e-3) / 1e9
+                        a2 = q_rays * ex_bytes / (trav_ms * 1e-3) / 1e9
                         k["l2"] = {"achieved": a2, "peak": aux["l2_read_gbs"], "unit": "GB/s", "frac": a2 / aux["l2_read_gbs"],
                                    "note": "bytes of node pairs + primitive records the traversal really fetched (device counters); an "
                                            "upper bound on L2 traffic - ncu L1 hit rate 70-80 %", "peak_source": "tools/peaks.cu (L2-resident float4 reads)"}
                     if aux.get("fp32_fma_tflops"):
-                        a32 = iter_rays * ex_flops / (trav_ms * 1e-3) / 1e12
+                        a32 = q_rays * ex_flops / (trav_ms * 1e-3) / 1e12
                         k["fp32"] = {"achieved": a32, "peak": aux["fp32_fma_tflops"], "unit": "TFLOP/s", "frac": a32 / aux["fp32_fma_tflops"],
                                      "peak_source": "tools/peaks.cu, measured in this run (FFMA chains)"}
                     if cpu:
