@@ -105,6 +105,10 @@ struct RenderArgs {
   float* sum;
   float* sumsq;
   float2* hits;                   // per queue slot: t, prim (bits)
+  // per queue slot: the free-flight bound of an interior segment (rt_trace.cuh::starts_inside_only_medium), drawn by the kernel
+  // that queued the path - k_shade, which waits on HBM and has issue slots to spare - so that the latency-bound traversal
+  // fetches 4 bytes instead of running Philox + log behind two more dependent queue loads.  Other slots: unspecified.
+  float* bound;
   int refill;                     // persistent traversal: idle lanes per warp that trigger a fetch
   int node_burst;                 // persistent traversal: node steps per vote
   uint32_t finish_max;            // k_finish takes over when at most this many paths are left (0 = never)
@@ -117,7 +121,6 @@ struct RenderArgs {
   // sample); kblock = 1: an item is (sample pass, pixel).  A bijection onto (pixel, sample) either way - the RNG is keyed by
   // (pixel, global sample), so the sample set does not depend on it.
   uint32_t shade_sort;                  // k_shade: deal the paths of a tile to the threads by material class
-  uint32_t material_sampling;           // materials draw the no-redirection direction from their own generator (Material.hs:36-38)
   uint32_t kblock, ktail;               // K; n_samples % K
   unsigned long long kfull_items;       // (n_samples / K) * K * n_pixels: items before the ragged last block of samples
 };
@@ -494,10 +497,14 @@ __global__ void __launch_bounds__(kTraverseBlock, trav_minb(F)) k_traverse_p(Ctl
                 cur = sc.surface_root;
                 break;
               }
+              const bool bounded = tmin == 0.f;
               tmin = tmin0;
               best = h;
               // the bounded query found nothing before the free-flight distance: the scatter event
               if (h.prim == kNone && h.t < inf) { best.prim = kMediumBase; best.front = true; m = sc.n_media; }
+              // ... or a surface before it: the free-flight sample of the only medium IS the bound, so no scatter event comes
+              // first (what the evaluation below would find out with a second Philox draw)
+              else if (bounded && h.prim != kNone) m = sc.n_media;
             }
             else if (pass == 0) {
               if (h.prim != kNone) {
@@ -574,6 +581,10 @@ __global__ void __launch_bounds__(kTraverseBlock, trav_minb(F)) k_traverse_p(Ctl
           const uint32_t i = base + __popc(idle & ((1u << lane) - 1u));
           if (i < n) {
             const float4 o4 = __ldcs(q.o + i), d4 = __ldcs(q.d + i);   // streaming: queue records must not evict the BVH from L1
+            float bound_i = inf;
+            if constexpr (kMedia) {                                    // (issued with the two loads above; meaningful for interior segments only)
+              if (sc.n_media == 1u && sc.media[0].closed != 0u) bound_i = __ldcs(A.bound + i);
+            }
             ray = RayT{mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w};
             origin_geom = __float_as_uint(d4.w);
             inv.x = fabsf(ray.d.x) > 1e-30f ? __frcp_rn(ray.d.x) : copysignf(1e30f, ray.d.x);
@@ -595,9 +606,8 @@ __global__ void __launch_bounds__(kTraverseBlock, trav_minb(F)) k_traverse_p(Ctl
               const bool inside = starts_inside_only_medium(sc, origin_geom);
               origin_geom = strip_inside_flag(origin_geom);
               if (inside) {
-                const uint32_t pixel = __float_as_uint(__ldcs(q.thr + i).w);
-                const uint2 meta = __ldcs(q.meta + i);
-                h.t = free_flight_bound(sc, tmin0, A.key, pixel, (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x, meta.y);
+                // free_flight_bound of this segment, drawn by the kernel that queued it (RenderArgs::bound)
+                h.t = bound_i;
                 // the origin is a scatter point or a surface the ray never re-hits (skip_a): look at (0, bound] so that a
                 // boundary crossing inside (0, tmin0] is noticed
                 if (h.t < inf) tmin = 0.f;
@@ -716,13 +726,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // Shading of ONE path segment whose closest hit is known (Ray.hs:176-198): material / texture / redirect mixture,
 // radiance into the accumulators, depth limit.  Updates ray / thr / origin_geom / meta for the next segment and returns
 // whether the path continues.  Shared by k_shade, k_trace_regions and k_finish: same RNG counters, same results.
+// HOOK: materials draw the no-redirection direction from their own generator (RtOptions.material_sampling) - a compile-time
+// switch, so that the default kernels carry none of its code (as a run-time flag it cost demo2's k_shade 7 %).
+template <bool HOOK = false>
 __device__ __forceinline__ bool shade_path(const DScene& sc, const RenderArgs& A, const NoiseTab& T, RayT& ray, const Hit& hit, f3& thr,
                                            uint32_t& origin_geom, uint32_t pixel, uint2& meta) {
   const unsigned long long sample = (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x;
   const uint4 rnd = rng4(A.key, pixel, sample, meta.y, RNG_SHADE);
   f3 contrib;
   RT_ASSERT(pixel < A.n_pixels);
-  bool alive = shade_bounce(sc, A.cam, T, ray, hit, thr, origin_geom, rnd, contrib, A.material_sampling != 0u);
+  bool alive = shade_bounce<HOOK>(sc, A.cam, T, ray, hit, thr, origin_geom, rnd, contrib);
   // a non-finite weight (pdf underflow at a grazing light direction) must not reach the accumulators: one NaN would own
   // the pixel for the whole render
   if (!(fabsf(thr.x + thr.y + thr.z) < 3.0e38f)) { alive = false; thr = mk3(0.f, 0.f, 0.f); }
@@ -755,7 +768,7 @@ __device__ __forceinline__ bool shade_path(const DScene& sc, const RenderArgs& A
 // FF != 0 (flat scenes, see k_trace_flat below): the closest-hit query runs HERE, over the constant-bank primitive list,
 // instead of being read from `hits`, and with GEN the camera rays of the refilled tail are generated here too — the whole
 // iteration is one launch, and new paths never touch the queue before their first bounce.
-template <uint32_t FF, bool GEN>
+template <uint32_t FF, bool GEN, bool BOUND = false, bool HOOK = false>   // BOUND: survivors that start inside the closed medium get their free-flight bound (RenderArgs::bound)
 __device__ __forceinline__ void shade_tiles(Ctl* __restrict__ ctl, const Queue& q, const Queue& qn, const DScene& sc, const RenderArgs& A,
                                             const FlatList* L) {
   __shared__ float s_grad[256 * 3];
@@ -884,7 +897,7 @@ __device__ __forceinline__ void shade_tiles(Ctl* __restrict__ ctl, const Queue& 
         const float2 h2 = s_h[par][src];
         hit = Hit{fabsf(h2.x), __float_as_uint(h2.y), !(h2.x < 0.f)};
       }
-      alive = shade_path(sc, A, T, ray, hit, thr, origin_geom, pixel, meta);
+      alive = shade_path<HOOK>(sc, A, T, ray, hit, thr, origin_geom, pixel, meta);
     }
     const uint32_t mask = __ballot_sync(0xFFFFFFFFu, alive);
     if (lane == 0) s_cnt[par][warp] = __popc(mask);
@@ -905,6 +918,10 @@ __device__ __forceinline__ void shade_tiles(Ctl* __restrict__ ctl, const Queue& 
       qn.d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(origin_geom));
       qn.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(pixel));
       qn.meta[slot] = meta;
+      if constexpr (BOUND) {     // the next segment starts inside the closed medium: its free-flight bound, for the traversal's fetch
+        if (starts_inside_only_medium(sc, origin_geom))
+          A.bound[slot] = free_flight_bound(sc, 1e-4f, A.key, pixel, (A.first_sample & 0xFFFFFFFF00000000ull) | meta.x, meta.y);
+      }
     }
   }
   // the last block to finish closes the iteration and prepares the next (no separate launch, no host round trip)
@@ -919,9 +936,11 @@ __device__ __forceinline__ void shade_tiles(Ctl* __restrict__ ctl, const Queue& 
   }
 }
 
+// BOUND = the scene's only medium has a closed boundary shared with the surfaces (interior segments are bounded queries)
+template <bool BOUND, bool HOOK = false>
 __global__ void __launch_bounds__(kShadeBlock, RT_SHADE_MINB) k_shade(Ctl* __restrict__ ctl, Queue q, Queue qn, const __grid_constant__ DScene sc,
                                                                       const __grid_constant__ RenderArgs A) {
-  shade_tiles<0, false>(ctl, q, qn, sc, A, nullptr);
+  shade_tiles<0, false, BOUND, HOOK>(ctl, q, qn, sc, A, nullptr);
 }
 
 // Flat scenes (no BVH, no media, no moving instances): raygen + closest hit + shading + compaction of one wavefront
@@ -1182,6 +1201,7 @@ struct Workspace {
   uint32_t pool_used = 0;   // logical pool of the current render (<= pool)
   Queue q[2]{};
   float2* hits = nullptr;
+  float* bound = nullptr;
   Ctl* ctl = nullptr;
   Ctl* h_ctl = nullptr;   // pinned, two snapshot slots
   cudaEvent_t snap_ev[2] = {nullptr, nullptr};
@@ -1631,8 +1651,8 @@ static int32_t ensure_workspace(Workspace& ds, uint32_t pool, size_t accum_elems
       ds.allocs.erase(std::remove(ds.allocs.begin(), ds.allocs.end(), p), ds.allocs.end());
     };
     for (int k = 0; k < 2; k++) { drop(ds.q[k].o); drop(ds.q[k].d); drop(ds.q[k].thr); drop(ds.q[k].meta); ds.q[k] = Queue{}; }
-    drop(ds.hits); drop(ds.ctl);
-    ds.hits = nullptr; ds.ctl = nullptr; ds.pool = 0;
+    drop(ds.hits); drop(ds.bound); drop(ds.ctl);
+    ds.hits = nullptr; ds.bound = nullptr; ds.ctl = nullptr; ds.pool = 0;
     auto grab = [&](void** p, size_t bytes) -> cudaError_t {
       cudaError_t e = cudaMalloc(p, bytes);
       if (e == cudaSuccess) ds.allocs.push_back(*p);
@@ -1645,6 +1665,7 @@ static int32_t ensure_workspace(Workspace& ds, uint32_t pool, size_t accum_elems
       RT_CUDA(grab((void**)&ds.q[k].meta, (size_t)pool * 8));
     }
     RT_CUDA(grab((void**)&ds.hits, (size_t)pool * 8));
+    RT_CUDA(grab((void**)&ds.bound, (size_t)pool * 4));
     RT_CUDA(grab((void**)&ds.ctl, sizeof(Ctl)));
     ds.pool = pool;
   }
@@ -1694,6 +1715,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   A.sum = d_sum;
   A.sumsq = d_sumsq;
   A.hits = ds.hits;
+  A.bound = ds.bound;
   A.refill = 24;
   A.node_burst = 4;
   // k_finish takes over the tail.  Flat scenes: with the constant-bank scan a lane that carries its path to the end
@@ -1704,10 +1726,14 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   const RtOptions& O = s.opts;
   // "flat scene" = the fused one-launch kernel applies: the surfaces are one short list AND nothing needs the generic
   // traversal (no media, no moving instances); a short list with media / movers runs the BVH kernels on a leaf root
-  const TraceFlatFn fused = dev.has_flat ? pick_trace_flat(s.flat.features) : nullptr;
+  // RtOptions.material_sampling (off by default: parity with the reference's estimator) lives in k_shade<., true> only: the
+  // fused flat-scene kernel and the tail kernel stand aside for it
+  const bool hook = O.material_sampling > 0;
+  const TraceFlatFn fused = dev.has_flat && !hook ? pick_trace_flat(s.flat.features) : nullptr;
   const bool flat_scene = fused != nullptr;
   A.finish_max = flat_scene ? 0xFFFFFFFFu : (cam.max_depth > 24 ? 1u << 20 : 0u);
   if (O.finish_max >= 0) A.finish_max = (uint32_t)std::min<int64_t>(O.finish_max, 0xFFFFFFFFll);
+  if (hook) A.finish_max = 0u;
   A.finish_refill = 4;
   if (O.finish_refill >= 0) A.finish_refill = std::min(32, std::max(1, (int)O.finish_refill));
   A.tile = flat_scene ? 0u : 1u;   // coherence only matters to the BVH kernels; the flat scan is the same for every ray
@@ -1734,7 +1760,6 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
     A.shade_sort = (texk & ((1u << RT_TEX_NOISE) | (1u << RT_TEX_MARBLE) | (1u << RT_TEX_IMAGE))) != 0 ? 1u : 0u;
     if (O.shade_sort >= 0) A.shade_sort = O.shade_sort ? 1u : 0u;
   }
-  A.material_sampling = O.material_sampling > 0 ? 1u : 0u;   // off by default: parity with the reference's estimator
   // culling iterations: a k_raygen thread owns K consecutive samples of a pixel (one background atomic triple per K samples)
   A.kblock = 1u;
   if (A.cull) {
@@ -1801,6 +1826,7 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
     cudaError_t e = cudaStreamSynchronize(stream);
     if (e != cudaSuccess) std::fprintf(stderr, "[rt_b200] %s (iteration %u): %s\n", what, iter, cudaGetErrorString(e));
   };
+  const bool shade_bound = dev.d.n_media == 1u && dev.d.media[0].closed != 0u;   // k_shade draws the free-flight bound of interior segments
   auto launch_iteration = [&](bool fin_check) {
     Queue& q = ds.q[cur];
     Queue& qn = ds.q[cur ^ 1];
@@ -1816,7 +1842,11 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
       traverse<<<g_trav, kTraverseBlock, stack_bytes, stream>>>(ds.ctl, q, dev.d, A);
       dbg("traverse");
       if (t_this) cudaEventRecord(ds.events[timed * 4 + 1], stream);
-      k_shade<<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
+      if (hook) {
+        if (shade_bound) k_shade<true, true><<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
+        else k_shade<false, true><<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
+      } else if (shade_bound) k_shade<true><<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
+      else k_shade<false><<<g_shade, kShadeBlock, 0, stream>>>(ds.ctl, q, qn, dev.d, A);
       dbg("k_shade");
       launches += 3;
     }

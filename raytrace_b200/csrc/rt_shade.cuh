@@ -231,9 +231,9 @@ __device__ __forceinline__ f3 sample_hg(f3 fwd, float g, float u1, float u2) {
   return fma3(r * cs, t, fma3(r * sn, b, mu * fwd));
 }
 
+template <bool material_sampling = false>
 __device__ __forceinline__ bool shade_bounce(const DScene& sc, const DCamera& cam, const NoiseTab& T, RayT& ray,
-                                             const Hit& hit, f3& thr, uint32_t& origin_geom, uint4 rnd, f3& contrib,
-                                             bool material_sampling = false) {
+                                             const Hit& hit, f3& thr, uint32_t& origin_geom, uint4 rnd, f3& contrib) {
   contrib = mk3(0.f, 0.f, 0.f);
   if (hit.prim == kNone) {   // Ray.hs:179
     contrib = thr * background(cam, ray.d);

@@ -258,6 +258,19 @@ def test_material_supplied_direction_generator(built, g, redirect):
         assert var_on < var_off
 
 
+def test_material_sampling_leaves_other_materials_alone(built):
+    """With RtOptions.material_sampling on, materials without a generator of their own draw exactly the reference's samples: a
+    flat scene (which then runs the wavefront kernels instead of the fused one) and a BVH scene render the same images."""
+    for ctor, kw, seed in ((scenes.cornell_box, dict(spp=16, width=64), 3), (scenes.demo1, dict(spp=8, width=64), 1)):
+        s, w = ctor(**kw)
+        cs = CompiledScene(w)
+        base, st0 = cs.render(s, rt.mkStdGen(seed), want_stats=True)
+        cs.handle.set_options(material_sampling=1)
+        img, st = cs.render(s, rt.mkStdGen(seed), want_stats=True)
+        assert st["rays"] == st0["rays"]
+        assert np.allclose(img, base, rtol=2e-4, atol=2e-5)
+
+
 def test_redirect_probability_one(built):
     """cs_redirectTargets whose probabilities sum to 1 (rem_prob = 0): the mixture pdf is the light pdf alone, so a
     sampled light point that fp32 would place a few ulp outside the target must still get its analytic pdf - an
