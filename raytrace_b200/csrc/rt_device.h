@@ -26,6 +26,9 @@
 // their geometry ids are consecutive too, and the flattener never splits them across leaves.
 #pragma once
 #include <stdint.h>
+#ifdef RT_CHECKED
+#include <assert.h>   // (outside the namespace: other headers use assert() too)
+#endif
 
 namespace rtb {
 
@@ -168,7 +171,6 @@ struct DScene {     // device pointers of one uploaded scene
 // asserted against the size of the array it goes into.  compute-sanitizer is not available on the GPU pool this was developed
 // on, so the checked build run through the whole GPU test suite stands in for a memcheck pass (profiles/r02u_checked_build.txt).
 #ifdef RT_CHECKED
-#include <assert.h>
 #define RT_ASSERT(c) assert(c)
 #else
 #define RT_ASSERT(c) ((void)0)
