@@ -265,8 +265,8 @@ __global__ void __launch_bounds__(kRaygenBlock) k_raygen(Ctl* __restrict__ ctl, 
   unsigned int culled = 0;
   // A thread owns K = A.kblock consecutive work items (K samples of one pixel, unless its run straddles a pixel boundary
   // because this iteration's first item is not a multiple of K): the background radiance of its culled rays is summed in
-  // registers and flushed with ONE atomic triple when the pixel changes.  Per round k the block compacts its survivors as
-  // before (ballot ranks, one atomic per 256 items), so queue order stays "256-pixel tile after tile".
+  // registers and flushed with ONE atomic triple when the pixel changes.  The block compacts the survivors of a whole chunk at
+  // once (queue order: thread after thread = pixel after pixel inside a 256-pixel tile, a pixel's samples side by side).
   const uint32_t K = max(A.kblock, 1u);
   const uint32_t chunks = (fill + K - 1u) / K;
   uint32_t acc_pixel = kNone;
@@ -293,21 +293,26 @@ __global__ void __launch_bounds__(kRaygenBlock) k_raygen(Ctl* __restrict__ ctl, 
     ItemCursor cur{};
     uint32_t cur_pixel = 0u;
     if (c < chunks) { cur = decode_item(A, item0 + (unsigned long long)c * K); cur_pixel = item_pixel(A, cur); }
+    const ItemCursor cur0 = cur;
+    const uint32_t pixel0 = cur_pixel;
+    // Pass 1: the K camera rays of the chunk against the world box.  Misses end here (background summed in registers, one
+    // atomic triple per pixel); hits only leave a bit.  No barrier, no atomic inside the loop (the first version compacted
+    // the survivors of every one of the K rounds across the block: three barriers and one slot atomic per sample).
+    unsigned long long keepmask = 0ull;
     for (uint32_t k = 0; k < K; k++) {
       const uint32_t t = c * K + k;
-      bool keep = false;
-      NewPath np{};
       if (c < chunks && t < fill) {
         if (k != 0u && advance_item(A, cur)) cur_pixel = item_pixel(A, cur);
-        np = make_camera_path(A, cur_pixel, cur.s_local());
+        const NewPath np = make_camera_path(A, cur_pixel, cur.s_local());
         f3 inv;
         inv.x = fabsf(np.ray.d.x) > 1e-30f ? __frcp_rn(np.ray.d.x) : copysignf(1e30f, np.ray.d.x);
         inv.y = fabsf(np.ray.d.y) > 1e-30f ? __frcp_rn(np.ray.d.y) : copysignf(1e30f, np.ray.d.y);
         inv.z = fabsf(np.ray.d.z) > 1e-30f ? __frcp_rn(np.ray.d.z) : copysignf(1e30f, np.ray.d.z);
         float tn;
-        keep = box_hit(wlo, whi, inv, np.ray.o * inv, 1e-4f, __int_as_float(0x7f800000), tn);
+        const bool keep = box_hit(wlo, whi, inv, np.ray.o * inv, 1e-4f, __int_as_float(0x7f800000), tn);
         RT_ASSERT(np.pixel < A.n_pixels);
-        if (!keep) {   // miss: emitted = background, path ends (throughput is still 1)
+        if (keep) keepmask |= 1ull << k;
+        else {   // miss: emitted = background, path ends (throughput is still 1)
           const f3 cbg = background(A.cam, np.ray.d);
           culled++;
           if (np.pixel != acc_pixel) { flush(); acc_pixel = np.pixel; }
@@ -315,30 +320,48 @@ __global__ void __launch_bounds__(kRaygenBlock) k_raygen(Ctl* __restrict__ ctl, 
           acc2 = acc2 + cbg * cbg;
         }
       }
-      const uint32_t mask = __ballot_sync(0xFFFFFFFFu, keep);
-      if (lane == 0) s_cnt[warp] = __popc(mask);
-      __syncthreads();
-      uint32_t before = 0, total = 0;
-#pragma unroll
-      for (int w = 0; w < kRaygenBlock / 32; w++) {
-        const uint32_t cw = s_cnt[w];
-        before += (w < (int)warp) ? cw : 0u;
-        total += cw;
-      }
-      if (threadIdx.x == 0 && total) s_base = atomicAdd(&ctl->n_gen, total);
-      __syncthreads();
-      if (keep) {
-        const uint32_t slot = lo + s_base + before + __popc(mask & ((1u << lane) - 1u));
-        RT_ASSERT(slot < ctl->pool);
-        q.o[slot] = make_float4(np.ray.o.x, np.ray.o.y, np.ray.o.z, np.ray.time);
-        q.d[slot] = make_float4(np.ray.d.x, np.ray.d.y, np.ray.d.z, __uint_as_float(kNone));
-        q.thr[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(np.pixel));
-        q.meta[slot] = make_uint2(np.sample_lo, 0u);
-      }
-      __syncthreads();   // s_cnt / s_base are reused by the next round
     }
     flush();
     acc_pixel = kNone;
+    // ONE compaction per chunk: exclusive rank of this thread's survivors in the block (warp scan + warp totals), one slot atomic
+    const uint32_t mine = (uint32_t)__popcll(keepmask);
+    uint32_t incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t up = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if ((int)lane >= o) incl += up;
+    }
+    if (lane == 31u) s_cnt[warp] = incl;
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kRaygenBlock / 32; w++) {
+      const uint32_t cw = s_cnt[w];
+      before += (w < (int)warp) ? cw : 0u;
+      total += cw;
+    }
+    if (threadIdx.x == 0 && total) s_base = atomicAdd(&ctl->n_gen, total);
+    __syncthreads();
+    // Pass 2: the survivors again (same counters -> the same rays), straight into their slots.  A thread's survivors are
+    // consecutive samples of one pixel and sit side by side in the queue.
+    if (keepmask) {
+      uint32_t slot = lo + s_base + before + (incl - mine);
+      cur = cur0;
+      cur_pixel = pixel0;
+      for (uint32_t k = 0; k < K; k++) {
+        if (k != 0u && advance_item(A, cur)) cur_pixel = item_pixel(A, cur);
+        if ((keepmask >> k) & 1ull) {
+          const NewPath np = make_camera_path(A, cur_pixel, cur.s_local());
+          RT_ASSERT(slot < ctl->pool);
+          q.o[slot] = make_float4(np.ray.o.x, np.ray.o.y, np.ray.o.z, np.ray.time);
+          q.d[slot] = make_float4(np.ray.d.x, np.ray.d.y, np.ray.d.z, __uint_as_float(kNone));
+          q.thr[slot] = make_float4(1.f, 1.f, 1.f, __uint_as_float(np.pixel));
+          q.meta[slot] = make_uint2(np.sample_lo, 0u);
+          slot++;
+        }
+      }
+    }
+    __syncthreads();   // s_cnt / s_base are reused by the next chunk
   }
   for (int o = 16; o > 0; o >>= 1) culled += __shfl_down_sync(0xFFFFFFFFu, culled, o);
   if (lane == 0 && culled) atomicAdd(&ctl->culled, culled);
