@@ -248,6 +248,13 @@ int32_t rt_scene_destroy(RtScene* scene);
 int32_t rt_scene_add_texture(RtScene* scene, const RtTextureDesc* desc, uint32_t* id);
 int32_t rt_scene_add_material(RtScene* scene, const RtMaterialDesc* desc, uint32_t* id);
 int32_t rt_scene_add_node(RtScene* scene, const RtNodeDesc* desc, uint32_t* id);
+/* A whole description in ONE call: n_textures + n_materials + n_nodes records, added in array order exactly as the three
+ * calls above would (textures first, then materials, then nodes; ids are consecutive, children before parents, so a front
+ * end that marshals an immutable world once - the constructors of Geometry.hs / Material.hs / Texture.hs evaluated into
+ * these records - can hand the same arrays to every scene it creates).  first_ids[3]: id of textures[0], materials[0],
+ * nodes[0].  Stops at the first invalid record (the scene keeps what was added before it). */
+int32_t rt_scene_add_batch(RtScene* scene, const RtTextureDesc* textures, uint32_t n_textures, const RtMaterialDesc* materials,
+                           uint32_t n_materials, const RtNodeDesc* nodes, uint32_t n_nodes, uint32_t* first_ids /*3*/);
 /* Perlin tables of Noise.hs:52-92; the three permutation tables default to the reference's
  * literals, the gradient table to a SplitMix restatement of `mkStdGen 666` (parity unpinned). */
 int32_t rt_scene_set_noise_tables(RtScene* scene, const int32_t* perm_x, const int32_t* perm_y,

@@ -131,7 +131,7 @@ class RtOptions(C.Structure):
 EXPORTS = [
     "rt_version", "rt_last_error", "rt_device_count",
     "rt_scene_create", "rt_scene_destroy", "rt_scene_add_texture", "rt_scene_add_material",
-    "rt_scene_add_node", "rt_scene_set_noise_tables", "rt_scene_commit", "rt_scene_info", "rt_scene_get_eval_order",
+    "rt_scene_add_node", "rt_scene_add_batch", "rt_scene_set_noise_tables", "rt_scene_commit", "rt_scene_info", "rt_scene_get_eval_order",
     "rt_scene_get_bvh", "rt_scene_upload", "rt_image_height", "rt_render", "rt_render_device",
     "rt_probe_primary", "rt_probe_surface", "rt_set_pool_size", "rt_tonemap_u8",
     "rt_obj_parse", "rt_mesh_sizes", "rt_mesh_data", "rt_mesh_destroy", "rt_host_alloc", "rt_host_free", "rt_reduce_image",
@@ -163,6 +163,7 @@ def lib() -> C.CDLL:
     L.rt_scene_add_texture.argtypes = [vp, C.POINTER(RtTextureDesc), u32p]
     L.rt_scene_add_material.argtypes = [vp, C.POINTER(RtMaterialDesc), u32p]
     L.rt_scene_add_node.argtypes = [vp, C.POINTER(RtNodeDesc), u32p]
+    L.rt_scene_add_batch.argtypes = [vp, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, u32p]
     L.rt_scene_set_noise_tables.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                             C.POINTER(C.c_int32), C.POINTER(C.c_double)]
     L.rt_scene_commit.argtypes = [vp, C.c_uint32]
@@ -252,6 +253,7 @@ class SceneHandle:
         self._mat_ids: Dict[int, int] = {}
         self._node_ids: Dict[int, int] = {}
         self._keep: List[object] = []   # keep numpy buffers alive until commit
+        self._rec = None                # first serialisation of a world into a fresh scene: the records in add order
         self.uploaded = set()
         self.committed = False
 
@@ -298,6 +300,8 @@ class SceneHandle:
             d.image = img.ctypes.data_as(C.POINTER(C.c_float))
         out = C.c_uint32()
         check(self._L.rt_scene_add_texture(self._h, C.byref(d), C.byref(out)))
+        if self._rec is not None:
+            self._rec[0].append(d)
         self._keep.append(tex)
         self._tex_ids[key] = out.value
         return out.value
@@ -314,6 +318,8 @@ class SceneHandle:
         d.texture = self.add_texture(mat.texture) if mat.texture is not None else 0
         out = C.c_uint32()
         check(self._L.rt_scene_add_material(self._h, C.byref(d), C.byref(out)))
+        if self._rec is not None:
+            self._rec[1].append(d)
         self._keep.append(mat)
         self._mat_ids[key] = out.value
         return out.value
@@ -354,6 +360,8 @@ class SceneHandle:
             d.material = self.add_material(g.material)
         out = C.c_uint32()
         check(self._L.rt_scene_add_node(self._h, C.byref(d), C.byref(out)))
+        if self._rec is not None:
+            self._rec[2].append(d)
         self._keep.append(g)
         self._node_ids[key] = out.value
         return out.value
@@ -373,7 +381,33 @@ class SceneHandle:
         check(self._L.rt_scene_set_noise_tables(self._h, ip(perm_x), ip(perm_y), ip(perm_z), g))
 
     def commit(self, world) -> None:
-        root = self.add_node(world)
+        # A world is immutable, and in a FRESH scene ids are handed out in add order from 0: the records of its first
+        # serialisation (textures, materials, nodes - child / material / texture ids and array pointers included) are
+        # kept on the world as three C arrays and go to every later scene in ONE rt_scene_add_batch call instead of a
+        # Python walk with one ctypes call per object (demo2: 3.9 -> 0.3 ms per `raytrace` call).
+        fresh = not (self._tex_ids or self._mat_ids or self._node_ids)
+        flat = world.__dict__.get("_rt_flat") if fresh else None
+        if flat is not None:
+            tex, mat, nodes, root, keep = flat
+            first = (C.c_uint32 * 3)()
+            check(self._L.rt_scene_add_batch(self._h, tex, len(tex), mat, len(mat), nodes, len(nodes), first))
+            if tuple(first) != (0, 0, 0):
+                raise RtError("rt_scene_add_batch: the scene was not empty")
+            self._keep.append(flat)
+            self._node_ids[id(world)] = root
+        else:
+            self._rec = ([], [], []) if fresh else None
+            try:
+                root = self.add_node(world)
+                if self._rec is not None:
+                    t, m, n = self._rec
+                    flat = ((RtTextureDesc * len(t))(*t), (RtMaterialDesc * len(m))(*m), (RtNodeDesc * len(n))(*n), root, list(self._keep))
+                    try:
+                        object.__setattr__(world, "_rt_flat", flat)
+                    except (AttributeError, TypeError):
+                        pass
+            finally:
+                self._rec = None
         check(self._L.rt_scene_commit(self._h, root))
         self.committed = True
 

@@ -243,6 +243,23 @@ int32_t rt_scene_add_node(RtScene* sp, const RtNodeDesc* d, uint32_t* id) {
   return RT_OK;
 }
 
+int32_t rt_scene_add_batch(RtScene* sp, const RtTextureDesc* tex, uint32_t n_tex, const RtMaterialDesc* mat, uint32_t n_mat,
+                           const RtNodeDesc* nodes, uint32_t n_nodes, uint32_t* first_ids) {
+  if (!sp || !first_ids || (n_tex && !tex) || (n_mat && !mat) || (n_nodes && !nodes)) { set_error("rt_scene_add_batch: null argument"); return RT_ERR_INVALID_ARG; }
+  Scene& s = *reinterpret_cast<Scene*>(sp);
+  first_ids[0] = (uint32_t)s.textures.size();
+  first_ids[1] = (uint32_t)s.materials.size();
+  first_ids[2] = (uint32_t)s.nodes.size();
+  s.textures.reserve(s.textures.size() + n_tex);
+  s.materials.reserve(s.materials.size() + n_mat);
+  s.nodes.reserve(s.nodes.size() + n_nodes);
+  uint32_t id = 0;
+  for (uint32_t k = 0; k < n_tex; k++) { const int32_t st = rt_scene_add_texture(sp, tex + k, &id); if (st != RT_OK) return st; }
+  for (uint32_t k = 0; k < n_mat; k++) { const int32_t st = rt_scene_add_material(sp, mat + k, &id); if (st != RT_OK) return st; }
+  for (uint32_t k = 0; k < n_nodes; k++) { const int32_t st = rt_scene_add_node(sp, nodes + k, &id); if (st != RT_OK) return st; }
+  return RT_OK;
+}
+
 int32_t rt_scene_set_noise_tables(RtScene* sp, const int32_t* px, const int32_t* py, const int32_t* pz, const double* g) {
   if (!sp) { set_error("null scene"); return RT_ERR_INVALID_ARG; }
   Scene& s = *reinterpret_cast<Scene*>(sp);

@@ -188,6 +188,35 @@ def test_error_codes(built):
     L.rt_scene_destroy(h)
 
 
+def test_batched_description_equals_the_object_walk(built):
+    """rt_scene_add_batch: the records of a world's first serialisation, kept on the (immutable) world, give every later scene
+    the same description in one call - same flattened scene, same device tree - and a bad record stops the batch with the
+    error the single call reports."""
+    for name in ("demo1", "demo2", "cornell"):
+        ctor, _ = scenes.CONFIGS[name]
+        s, w = ctor()
+        w.__dict__.pop("_rt_flat", None)
+        a = CompiledScene(w, upload=False, options=dict(gpu_build=0))        # walks the objects, leaves the arrays on the world
+        assert "_rt_flat" in w.__dict__
+        b = CompiledScene(w, upload=False, options=dict(gpu_build=0))        # one rt_scene_add_batch call
+        ia, ib = a.info(), b.info()
+        assert ia == ib and ia["n_prims"] > 0
+        (na, ca), (nb, cb) = a.handle.get_bvh(), b.handle.get_bvh()
+        assert np.array_equal(na, nb) and np.array_equal(ca, cb)
+    L = _ffi.lib()
+    h = ctypes.c_void_p()
+    assert L.rt_scene_create(ctypes.byref(h)) == 0
+    nodes = (_ffi.RtNodeDesc * 2)()
+    nodes[0].kind, nodes[1].kind = 1, 77                                       # a sphere, then an unknown kind
+    nodes[0].s[0] = 1.0
+    first = (ctypes.c_uint32 * 3)()
+    assert L.rt_scene_add_batch(h, None, 0, None, 0, nodes, 2, first) == 1 and b"unknown node kind" in L.rt_last_error()
+    assert tuple(first) == (0, 0, 0)
+    assert L.rt_scene_add_batch(h, None, 0, None, 0, nodes, 1, first) == 0 and first[2] == 1   # the sphere of the failed batch stayed
+    assert L.rt_scene_add_batch(h, None, 3, None, 0, None, 0, first) == 1                    # a count without an array
+    L.rt_scene_destroy(h)
+
+
 def test_outermost_material_wins_and_shared_geometry(built):
     a, b = rt.lambertian(rt.constantTexture(0.1)), rt.mirror(rt.constantTexture(0.9))
     inner = a << rt.sphere((0, 0, 0), 1)
