@@ -20,8 +20,9 @@ if name:
     blocks[name] = cur
 demangled = subprocess.run(["c++filt"], input="\n".join(blocks), capture_output=True, text=True).stdout.splitlines()
 by_name = dict(zip(demangled, blocks.values()))
-WANT = {"k_shade": "rtb::k_shade<false>(", "k_trace_flat_2": "rtb::k_trace_flat<2u>(", "k_traverse_p_10": "rtb::k_traverse_p<10u, false>(",
-        "k_traverse_p_31": "rtb::k_traverse_p<31u, false>(", "k_reduce_multimem": "rtb::k_reduce_multimem(", "k_raygen": "rtb::k_raygen("}
+WANT = {"k_shade": "rtb::k_shade<false, false>(", "k_trace_flat_2": "rtb::k_trace_flat<2u>(", "k_traverse_p_10": "rtb::k_traverse_p<10u, false>(",
+        "k_traverse_p_31": "rtb::k_traverse_p<31u, false>(", "k_reduce_multimem": "rtb::k_reduce_multimem(", "k_raygen": "rtb::k_raygen(",
+        "k_shade_bound": "rtb::k_shade<true, false>(", "k_build_tree": "rtb::gpubuild::k_build_tree("}
 KEY = ["UBLKCP", "SYNCS", "LDG.E.ENL2.256", "LDG.E.128", "LDGMC", "ATOMG", "RED.E", "ATOMS", "STG.E.128", "STG.E.EF", "LDS", "STS", "FFMA", "MUFU",
        "SHFL", "VOTE", "BAR.SYNC", "BSSY", "HMMA", "UTCMMA", "UTCHMMA", "TCGEN", "LDTM", "DFMA", "DADD", "DMUL"]
 rows = []
