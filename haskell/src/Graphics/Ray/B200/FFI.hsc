@@ -155,7 +155,12 @@ foreign import ccall safe   "rt_context_create"         c_context_create :: Ptr 
 foreign import ccall safe   "rt_context_destroy"        c_context_destroy :: Ptr RtContext -> IO Int32
 foreign import ccall safe   "rt_render_multi"           c_render_multi   :: Ptr RtContext -> Ptr RtScene -> Ptr () -> Word64
                                                                          -> Ptr CFloat -> Ptr CFloat -> Ptr () -> IO Int32
--- tuning / A-B options are a struct (RtOptions), never environment variables
+-- a whole marshalled world in one call: three arrays of records, ids consecutive from the scene's current counts (a world is
+-- immutable, so its arrays can be marshalled once and handed to every scene)
+foreign import ccall safe   "rt_scene_add_batch"        c_scene_add_batch :: Ptr RtScene -> Ptr () -> Word32 -> Ptr () -> Word32 -> Ptr () -> Word32
+                                                                         -> Ptr Word32 -> IO Int32
+foreign import ccall safe   "rt_tonemap_u8_static"      c_tonemap_u8_static :: Int32 -> Ptr CFloat -> Int32 -> Int32 -> Ptr Word8 -> Ptr () -> IO Int32
+-- tuning / A-B options are a struct (RtOptions: gpu_build, material_sampling, ...), never environment variables
 foreign import ccall unsafe "rt_options_init"           c_options_init   :: Ptr () -> IO Int32
 foreign import ccall safe   "rt_scene_set_options"      c_scene_set_options :: Ptr RtScene -> Ptr () -> IO Int32
 foreign import ccall safe   "rt_host_alloc"             c_host_alloc     :: CSize -> Ptr (Ptr ()) -> IO Int32
