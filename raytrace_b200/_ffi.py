@@ -120,11 +120,11 @@ class RtOptions(C.Structure):
                 ("finish_refill", C.c_int32), ("tail_batch", C.c_int32), ("node_burst", C.c_int32),
                 ("refill", C.c_int32), ("trav_blocks", C.c_int32), ("tile", C.c_int32),
                 ("primary_cull", C.c_int32), ("shade_sort", C.c_int32), ("timing", C.c_int32),
-                ("count_work", C.c_int32), ("debug_sync", C.c_int32), ("raygen_block", C.c_int32), ("material_sampling", C.c_int32), ("reserved", C.c_int32 * 6)]
+                ("count_work", C.c_int32), ("debug_sync", C.c_int32), ("raygen_block", C.c_int32), ("material_sampling", C.c_int32), ("smem_carveout", C.c_int32), ("reserved", C.c_int32 * 5)]
 
     NAMES = ("bvh_reference", "leaf_max", "collapse", "aggregate_boxes", "shared_boundary", "interior_bound", "world_box",
              "split_moving", "trace_commit", "gpu_build", "sah_node_cost", "pool", "finish_max", "finish_refill", "tail_batch",
-             "node_burst", "refill", "trav_blocks", "tile", "primary_cull", "shade_sort", "timing", "count_work", "debug_sync", "raygen_block", "material_sampling")
+             "node_burst", "refill", "trav_blocks", "tile", "primary_cull", "shade_sort", "timing", "count_work", "debug_sync", "raygen_block", "material_sampling", "smem_carveout")
 
 
 # every symbol include/rt_b200.h declares (tests check that the .so exports all of them)

@@ -1822,6 +1822,33 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
     else cudaGetLastError();
   }
   if (O.trav_blocks >= 0) g_trav = dev.sm_count * std::max(1, (int)O.trav_blocks);
+  // L1 / shared-memory split of the traversal kernels (RtOptions.smem_carveout, OFF by default).  Left alone, the driver gives
+  // k_traverse_p a 132 KB shared-memory carve-out for the 63 KB its nine resident blocks use (ncu: launch__shared_mem_config_size
+  // 135 KB), i.e. 124 KB of L1 for a kernel whose node pairs and primitive records are fetched by divergent lanes.  Asking for
+  // less (the hint is rounded UP to the next supported size: 28 % came back as 100 KB) raised pawn's L1 hit rate to 80 % and
+  // took 1.5 % off its traversal - and put 5 % ON bunny's, whose carve-out stayed at 132 KB (profiles/r02zc_sweep_smem_carveout.txt):
+  // not understood, so the driver's choice stays.  > 0: that percentage; -2: the smallest supported size that holds the stacks.
+  if (O.smem_carveout > 0 || O.smem_carveout == -2) {
+    int max_smem = 233472;
+    cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev.device);
+    const size_t need = (size_t)(g_trav / std::max(1, dev.sm_count)) * (stack_bytes + 1024);
+    // the carve-outs an sm_100 SM supports; the percentage is a hint the driver rounds to one of them (a request just above
+    // 64 KB came back as 64 KB and cost bunny two resident blocks), so name the smallest that fits exactly
+    size_t config = (size_t)max_smem;
+    for (size_t kb : {8u, 16u, 32u, 64u, 100u, 132u, 164u, 196u, 228u})
+      if (kb * 1024 >= need) { config = kb * 1024; break; }
+    int pct = O.smem_carveout > 0 ? std::min(100, (int)O.smem_carveout) : (int)std::min<size_t>(100, config * 100 / (size_t)max_smem);
+    static std::mutex carve_mu;
+    static std::map<std::pair<const void*, int>, int> carve_set;      // (function, device) -> percentage in force
+    std::lock_guard<std::mutex> lock(carve_mu);
+    for (const void* fn : {(const void*)traverse, (const void*)finish}) {
+      int& have = carve_set[{fn, dev.device}];
+      if (have != pct + 1) {
+        if (cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, pct) == cudaSuccess) have = pct + 1;
+        else cudaGetLastError();
+      }
+    }
+  }
   uint64_t launches = 0;
   size_t timed = 0;
   std::vector<char> has_fin(timing ? kMaxTimed : 0, 0);   // iteration k was followed by a (timed) k_finish launch
