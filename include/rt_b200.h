@@ -234,10 +234,10 @@ typedef struct RtOptions {
   int32_t material_sampling; /* 1: a material draws the direction of the no-redirection case from its own generator - the generalisation
                               * sketched in Material.hs:36-38; today `anisotropic g` samples its Henyey-Greenstein phase function.  Same
                               * expectation, other samples, less variance.  Default 0: the reference's estimator, sample for sample */
-  int32_t smem_carveout;     /* shared-memory carve-out asked for the traversal kernels, % of the SM's maximum: > 0 that percentage,
-                              * -2 the smallest supported size that holds the resident blocks' stacks (the rest of the 256 KB is L1);
-                              * default / 0: the driver's own choice (132 KB for 63 KB used; measured: pawn -1.5 %, bunny +5 % when
-                              * changed, so it stays) */
+  int32_t smem_carveout;     /* shared-memory carve-out asked for the traversal kernels: default = the smallest supported size that holds
+                              * the resident blocks' stacks (the rest of the 256 KB is L1 for node pairs and primitive records; pawn
+                              * traversal -4 %); 0: the attribute is never touched (the driver's choice: 132 KB for 63 KB used);
+                              * > 0: that percentage of the SM's maximum as the hint */
   int32_t reserved[5];
 } RtOptions;
 

@@ -1814,32 +1814,32 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
   const TraverseFn finish = pick_by_features<FinishK>(s.flat.features);
   const FinishFlatFn finish_flat = fused ? pick_finish_flat(s.flat.features) : nullptr;
   const size_t stack_bytes = (size_t)(s.flat.max_depth + 1) * kTraverseBlock * sizeof(uint32_t);
-  int g_trav = dev.sm_count * 8, g_shade = dev.sm_count * 8, g_gen = dev.sm_count * 4;
-  {   // the persistent traversal grid = exactly the blocks that are resident at once (8 or 9 per SM, by specialisation)
-    int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse, kTraverseBlock, stack_bytes) == cudaSuccess && per_sm > 0)
-      g_trav = dev.sm_count * per_sm;
-    else cudaGetLastError();
-  }
-  if (O.trav_blocks >= 0) g_trav = dev.sm_count * std::max(1, (int)O.trav_blocks);
-  // L1 / shared-memory split of the traversal kernels (RtOptions.smem_carveout, OFF by default).  Left alone, the driver gives
-  // k_traverse_p a 132 KB shared-memory carve-out for the 63 KB its nine resident blocks use (ncu: launch__shared_mem_config_size
-  // 135 KB), i.e. 124 KB of L1 for a kernel whose node pairs and primitive records are fetched by divergent lanes.  Asking for
-  // less (the hint is rounded UP to the next supported size: 28 % came back as 100 KB) raised pawn's L1 hit rate to 80 % and
-  // took 1.5 % off its traversal - and put 5 % ON bunny's, whose carve-out stayed at 132 KB (profiles/r02zc_sweep_smem_carveout.txt):
-  // not understood, so the driver's choice stays.  > 0: that percentage; -2: the smallest supported size that holds the stacks.
-  if (O.smem_carveout > 0 || O.smem_carveout == -2) {
+  // L1 / shared-memory split of the traversal kernels (RtOptions.smem_carveout).  Left alone, the driver gives k_traverse_p a
+  // 132 KB shared-memory carve-out for the 63 KB its nine resident blocks use on pawn (ncu: launch__shared_mem_config_size
+  // 135 KB), i.e. 124 KB of L1 for a kernel whose node pairs and primitive records are fetched by divergent lanes at L1
+  // latency or ten times that.  Default: ask for the smallest supported carve-out that holds the resident blocks' stacks
+  // (the hint sits halfway between that size and the next smaller one: the driver's rounding at the edges is not what the
+  // percentages suggest - 28 % came back as 100 KB).  pawn (64 KB): L1 hit rate 72 -> 80 %+, traversal -4 %.  The attribute
+  // belongs to the FUNCTION, not the scene: it is set again whenever the size a render needs differs from the one in force
+  // (a 64 KB carve-out left behind by pawn cost bunny, same specialisation, two resident blocks and 5 %).
+  // 0: never touch the attribute; > 0: that percentage as the hint.  profiles/r02zc_sweep_smem_carveout.txt
+  if (O.smem_carveout != 0) {
     int max_smem = 233472;
     cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev.device);
-    const size_t need = (size_t)(g_trav / std::max(1, dev.sm_count)) * (stack_bytes + 1024);
-    // the carve-outs an sm_100 SM supports; the percentage is a hint the driver rounds to one of them (a request just above
-    // 64 KB came back as 64 KB and cost bunny two resident blocks), so name the smallest that fits exactly
-    size_t config = (size_t)max_smem;
-    for (size_t kb : {8u, 16u, 32u, 64u, 100u, 132u, 164u, 196u, 228u})
-      if (kb * 1024 >= need) { config = kb * 1024; break; }
-    int pct = O.smem_carveout > 0 ? std::min(100, (int)O.smem_carveout) : (int)std::min<size_t>(100, config * 100 / (size_t)max_smem);
+    // resident blocks as the REGISTERS allow (no dynamic shared memory in the query: the answer must not depend on the
+    // carve-out a previous scene left on the function - the query below, with the stacks, runs after the attribute is set)
+    int by_regs = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&by_regs, traverse, kTraverseBlock, 0) != cudaSuccess || by_regs <= 0) { cudaGetLastError(); by_regs = 9; }
+    if (O.trav_blocks >= 0) by_regs = std::max(1, (int)O.trav_blocks);
+    const size_t need = (size_t)by_regs * (stack_bytes + 1024);
+    size_t prev = 0, hint = (size_t)max_smem;
+    for (size_t kb : {32u, 64u, 100u, 132u, 164u, 196u, 228u}) {      // (never below 32 KB: the register-limited query above must stay unconstrained)
+      if (kb * 1024 >= need) { hint = (prev + kb * 1024) / 2; break; }
+      prev = kb * 1024;
+    }
+    const int pct = O.smem_carveout > 0 ? std::min(100, (int)O.smem_carveout) : (int)std::min<size_t>(100, hint * 100 / (size_t)max_smem);
     static std::mutex carve_mu;
-    static std::map<std::pair<const void*, int>, int> carve_set;      // (function, device) -> percentage in force
+    static std::map<std::pair<const void*, int>, int> carve_set;      // (function, device) -> hint in force + 1
     std::lock_guard<std::mutex> lock(carve_mu);
     for (const void* fn : {(const void*)traverse, (const void*)finish}) {
       int& have = carve_set[{fn, dev.device}];
@@ -1849,6 +1849,14 @@ static int32_t run_wavefront_range(Scene& s, DeviceScene& dev, Workspace& ds, co
       }
     }
   }
+  int g_trav = dev.sm_count * 8, g_shade = dev.sm_count * 8, g_gen = dev.sm_count * 4;
+  {   // the persistent traversal grid = exactly the blocks that are resident at once (8 or 9 per SM, by specialisation)
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, traverse, kTraverseBlock, stack_bytes) == cudaSuccess && per_sm > 0)
+      g_trav = dev.sm_count * per_sm;
+    else cudaGetLastError();
+  }
+  if (O.trav_blocks >= 0) g_trav = dev.sm_count * std::max(1, (int)O.trav_blocks);
   uint64_t launches = 0;
   size_t timed = 0;
   std::vector<char> has_fin(timing ? kMaxTimed : 0, 0);   // iteration k was followed by a (timed) k_finish launch
