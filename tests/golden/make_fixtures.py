@@ -16,7 +16,9 @@ Nothing in tests/, smoke() or bench.py reads /root/reference at run time; they r
                                        example_image (README scene, seed 100, 50 spp, writeImage),
                                        cornell_box_noisy / cornell_box_redirect (200 spp, writeImageSqrt),
                                        pawn_demo (500x500, 400 spp, depth 20, writeImage),
-                                       demo2 (800x800, scene from mkStdGen 1234, writeImageSqrt; spp / depth unrecorded)
+                                       demo2 (800x800, scene from mkStdGen 1234, writeImageSqrt; spp / depth unrecorded),
+                                       demo1 (1200x675, small spheres from newStdGen - only the camera, the ground, the sky and the
+                                       three big spheres are deterministic; writeImageSqrt)
 """
 import os
 import sys
@@ -48,7 +50,7 @@ def main():
     img = np.asarray(Image.open(f"{REF}/images/earthmap.jpg").convert("RGB"), dtype=np.uint8)
     np.savez_compressed(os.path.join(HERE, "assets", "earthmap.npz"), rgb8=img)
     print("earthmap", img.shape)
-    for name in ("example_image", "cornell_box_noisy", "cornell_box_redirect", "pawn_demo", "demo2"):
+    for name in ("example_image", "cornell_box_noisy", "cornell_box_redirect", "pawn_demo", "demo2", "demo1"):
         a = np.asarray(Image.open(f"{REF}/{name}.png").convert("RGB"), dtype=np.uint8)
         np.savez_compressed(os.path.join(HERE, "png", f"{name}.npz"), rgb8=a)
         print(name, a.shape)

@@ -179,3 +179,40 @@ def test_demo2_matches_golden(built):
         m = ((ids == pid) & stable).reshape(400, 2, 400, 2).all(axis=(1, 3))
         assert m.sum() > 2000
         assert np.abs(g2[m].mean(axis=0) - oc[m].mean(axis=0)).max() < tol, (pid, g2[m].mean(axis=0), oc[m].mean(axis=0))
+
+
+def test_demo1_matches_golden(built):
+    """demo1 (test/Main.hs:136-186; README's demo1.png: 1200x675, writeImageSqrt).  The ~480 small spheres come from
+    `newStdGen`, but the camera (vfov 20, defocus 0.6 deg at focus distance 10), the sky, the ground and the three big
+    spheres - glass, lambertian (0.4, 0.2, 0.1), mirror (0.7, 0.6, 0.5) - are deterministic, and they pin `scenes.demo1`:
+      * the big spheres' silhouettes: where the oracle's primary rays see them, the golden shows them (edge positions);
+      * the horizon row (camera pitch, ground sphere of radius 1000);
+      * mean linear colours of sky, brown, mirror and glass sphere against a 16-spp oracle render (the small spheres only
+        enter through reflections and bounce light: 1 - 3 %)."""
+    from scipy.ndimage import binary_erosion
+    g = _golden("demo1")
+    assert g.shape == (675, 1200, 3)
+    gl = (g.astype(np.float64) / 255) ** 2                     # undo writeImageSqrt
+    lum = lambda a: 0.2126 * a[..., 0] + 0.7152 * a[..., 1] + 0.0722 * a[..., 2]   # noqa: E731
+    s, w = scenes.demo1(width=1200, spp=1)
+    ids, _, stable = OracleScene(w).probe_stable(s, delta=0.5, t_tol=float("inf"))
+    GROUND, GLASS, BROWN, MIRROR, MISS = 0, 1, 2, 3, 0xFFFFFFFF           # bigSpheres come first in the bvhTree list
+    # silhouettes (pixel-centre rays; the lens blurs the golden's edges by a few pixels)
+    L = lum(gl)
+    for x in (50, 150, 250, 1100):                                         # horizon: first non-sky row of the golden / first hit row
+        assert abs(int(np.argmax(L[:, x] < 0.55)) - int(np.argmax(ids[:, x] != MISS))) <= 3
+    assert abs(int(np.argmax(gl[120, :, 2] < 0.5)) - int(np.argmax(ids[120] == BROWN))) <= 3    # left edge of the brown sphere against the sky
+    top = int(np.argmax((ids == MIRROR).any(axis=1)))
+    x_top = int(np.median(np.where(ids[top] == MIRROR)[0]))
+    assert abs(int(np.argmax(L[:, x_top] < 0.8)) - top) <= 4                # top of the mirror sphere against the sky
+    # colours: half resolution, golden 2x2-averaged in linear space
+    s2, w2 = scenes.demo1(width=600, spp=16)
+    img, _ = OracleScene(w2).render(s2, 1)
+    g2 = gl[:674].reshape(337, 2, 600, 2, 3).mean(axis=(1, 3))
+    ids2, img = ids[:674:2, ::2], img[:337]
+    upper = np.arange(337)[:, None] < 60
+    for name, k, it, tol, extra in (("sky", MISS, 6, 0.02, upper), ("brown", BROWN, 8, 0.06, True), ("mirror", MIRROR, 8, 0.04, True), ("glass", GLASS, 8, 0.06, True)):
+        m = binary_erosion(ids2 == k, iterations=it) & extra
+        assert m.sum() > 1000, name
+        a, b = g2[m].mean(axis=0), img[m].mean(axis=0)
+        assert (np.abs(a - b) <= tol * a).all(), (name, a, b)
