@@ -166,6 +166,20 @@ def cpu_baseline_block(name, world, settings, seed):
             "flops_per_ray_survey_8d": 24 * n_node + 24 * n_sph + 64 * n_pl}
 
 
+def arm_config(desc, settings, n_gpus, pool=None):
+    """`config` of the JSON line - the same dict in both arms (the reference arm runs ON this arm's config): the workload, and how
+    the GPU arm is measured (sample sharding, L2 policy, live-path pool of one GPU's share)."""
+    from raytrace_b200.ray import imageHeight
+    W, H, spp = settings.cs_imageWidth, imageHeight(settings), settings.cs_samplesPerPixel
+    if pool is None:
+        items = W * H * ((spp + n_gpus - 1) // n_gpus)
+        pool = min(1 << 25, (max(items, 1024) + 1023) // 1024 * 1024)
+    return {"workload": desc, "image": [W, H], "spp": spp, "max_depth": settings.cs_maxRecursionDepth,
+            "parallelism": f"sample-sharded x{n_gpus}" if n_gpus > 1 else "single GPU",
+            "l2": "256 MiB flush between timed steps", "pool": int(pool),
+            "why_this_workload": "largest single-GPU configuration of BASELINE.json (configs[4]); the other configs are in per_scene"}
+
+
 def run_reference(args, rank):
     """Reference arm: the reference's algorithm on the host cores (CPU oracle port; no GHC here)."""
     if rank != 0:
@@ -197,9 +211,9 @@ def run_reference(args, rank):
         "impl": "reference", "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": desc, "image": [settings.cs_imageWidth, imageHeight(settings)], "spp": settings.cs_samplesPerPixel,
-                   "max_depth": settings.cs_maxRecursionDepth,
-                   "note": "CPU oracle (C++ port of the Haskell reference; GHC absent), all host threads"},
+        "config": arm_config(desc, settings, args.gpus),
+        "reference_note": "CPU oracle (C++ port of the Haskell reference; GHC absent), all host threads; `config` is the GPU arm's",
+
         "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": cnt["threads"], "kind": "port",
                          "sample": f"{spp} of {settings.cs_samplesPerPixel} spp per step, full resolution"},
         "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -545,6 +559,7 @@ def main():
     b = Bench(rank, local_rank, world_size)
     want_cpu = (not args.no_cpu_baseline) and world_size == 1
     main_res = b.measure(args.scene, args.steps, max(args.warmup, 3), max(1, min(args.steps, 5)), want_cpu, clocks=True)
+    main_settings = build_workload(args.scene)[0]
     per_scene = {}
     if not args.no_per_scene:
         for name in WORKLOADS:
@@ -579,10 +594,7 @@ def main():
         "metric": "Msamples/s", "value": r["value"], "unit": "Msamples/s", "n_gpus": world_size, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": r["workload"], "image": r["image"], "spp": r["spp"], "max_depth": r["max_depth"],
-                   "parallelism": f"sample-sharded x{world_size}" if b.distributed else "single GPU",
-                   "l2": "256 MiB flush between timed steps", "pool": r["pool"],
-                   "why_this_workload": "largest single-GPU configuration of BASELINE.json (configs[4]); the other configs are in per_scene"},
+        "config": arm_config(r["workload"], main_settings, world_size, pool=r["pool"]),
         "mrays_per_s": r["mrays_per_s"], "rays_per_sample": r["rays_per_sample"], "kernel_ms_per_step": r["kernel_ms_per_step"],
         "gpu_launches": r["gpu_launches"], "e2e": r["e2e"], "roofline": r["roofline"], "cpu_baseline": r["cpu_baseline"],
         "vs_cpu_baseline": r.get("vs_cpu_baseline"), "clocks": r["clocks"], "mean_radiance": r["mean_radiance"], "wall_s": r["wall_s"],
